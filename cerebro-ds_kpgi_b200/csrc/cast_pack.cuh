@@ -1,0 +1,79 @@
+// cast_pack.cuh — consumer-side casts of the decoded partition.
+//
+//   one-hot int16 row -> int64 class index   np.argmax(dependent_var[idx])
+//                                             /root/reference/cerebro_gpdb/run_pytorchddp_da.py:55
+//   NHWC f32 -> NCHW f32                      np.rollaxis(image, 2, 0) + DataLoader collate
+//                                             /root/reference/cerebro_gpdb/run_pytorchddp_da.py:56-58
+//   f32 -> bf16 (RNE)                         optional training-buffer dtype (not in the reference)
+#pragma once
+#include <cuda_bf16.h>
+
+#include "cds_common.cuh"
+
+namespace cds {
+
+// One warp per row; first maximum wins, as np.argmax.
+__global__ void __launch_bounds__(256)
+k_onehot_argmax_i16(const int16_t *__restrict__ onehot, unsigned long long n_rows, uint32_t classes,
+                    long long *__restrict__ labels)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const unsigned long long w0 = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const unsigned long long nw = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+    for (unsigned long long r = w0; r < n_rows; r += nw) {
+        const int16_t *row = onehot + r * classes;
+        int best = -32769;
+        uint32_t best_i = 0xFFFFFFFFu;
+        for (uint32_t c = lane; c < classes; c += 32) {
+            const int v = row[c];
+            if (v > best) { best = v; best_i = c; }
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const int ov = __shfl_xor_sync(0xffffffffu, best, d);
+            const uint32_t oi = __shfl_xor_sync(0xffffffffu, best_i, d);
+            if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+        }
+        if (lane == 0) labels[r] = (long long)best_i;
+    }
+}
+
+// dst[n][c][p] = src[n][p][c].  Thread per destination element: coalesced stores; the strided
+// loads of one warp stay inside 32*channels*4 contiguous bytes and are served by L1.
+__global__ void __launch_bounds__(256)
+k_nhwc_to_nchw_f32(const float *__restrict__ src, unsigned long long n, uint32_t hw, uint32_t ch,
+                   float *__restrict__ dst)
+{
+    const unsigned long long per = (unsigned long long)hw * ch, total = n * per;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const unsigned long long img = i / per;
+        const uint32_t rem = (uint32_t)(i - img * per);
+        const uint32_t c = rem / hw, p = rem - c * hw;
+        dst[i] = src[img * per + (unsigned long long)p * ch + c];
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_f32_to_bf16(const float *__restrict__ src, unsigned long long n, __nv_bfloat16 *__restrict__ dst)
+{
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long n4 = n >> 2;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 7u) == 0);
+    if (aligned) {
+        for (unsigned long long i = tid; i < n4; i += stride) {
+            const float4 v = reinterpret_cast<const float4 *>(src)[i];
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            uint2 o;
+            o.x = *reinterpret_cast<uint32_t *>(&lo);
+            o.y = *reinterpret_cast<uint32_t *>(&hi);
+            reinterpret_cast<uint2 *>(dst)[i] = o;
+        }
+        for (unsigned long long i = (n4 << 2) + tid; i < n; i += stride) dst[i] = __float2bfloat16_rn(src[i]);
+    } else {
+        for (unsigned long long i = tid; i < n; i += stride) dst[i] = __float2bfloat16_rn(src[i]);
+    }
+}
+
+}  // namespace cds

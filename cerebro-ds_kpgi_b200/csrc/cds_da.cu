@@ -1,0 +1,556 @@
+// cds_da.cu — C ABI of libcds_da.so (include/cds_da.h): handle management and kernel sequencing.
+//
+// The decode of one segment is a fixed sequence of launches on the caller's stream with no host
+// round trip in between: page index -> row parse -> value index -> TOAST walk -> plan (ranks and
+// prefix sums) -> resolve (checks + copy descriptors) -> gather -> pglz.  Counts stay on the
+// device; cds_finish() reads them back once.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "cast_pack.cuh"
+#include "cds_common.cuh"
+#include "page_scan.cuh"
+#include "pglz_decode.cuh"
+#include "toast_gather.cuh"
+
+using namespace cds;
+
+static thread_local char g_last_error[512] = "";
+
+static int cuda_fail(cudaError_t e, const char *what)
+{
+    snprintf(g_last_error, sizeof(g_last_error), "%s: %s", what, cudaGetErrorString(e));
+    return CDS_ERR_CUDA;
+}
+#define CU(call)                                              \
+    do {                                                      \
+        cudaError_t e__ = (call);                             \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+    } while (0)
+
+struct cds_segment {
+    int device = 0;
+    int num_sms = 148;
+    uint64_t cap_heap_pages = 0, cap_toast_pages = 0, cap_rows = 0, cap_chunks = 0, cap_scratch = 0;
+    uint32_t hmask = 0;
+    // inputs of the current decode
+    const uint8_t *d_heap = nullptr, *d_toast = nullptr;
+    uint64_t n_heap_pages = 0, n_toast_pages = 0;
+    bool have_rows = false, have_chunks = false, have_plan = false;
+    // device buffers
+    uint8_t *stage_heap = nullptr, *stage_toast = nullptr;
+    uint32_t *heap_base = nullptr, *toast_base = nullptr, *rows = nullptr;
+    unsigned long long *htab = nullptr;
+    uint2 *dir_id = nullptr, *dir_loc = nullptr;
+    uint32_t *dir_ref = nullptr, *chunk_flag = nullptr;
+    uint32_t *vfirst = nullptr, *vcount = nullptr, *vseq0 = nullptr;
+    unsigned long long *vbytes = nullptr, *vscr = nullptr;
+    uint32_t *inline_flag = nullptr, *row_first = nullptr, *pos_of_row = nullptr, *row_at_pos = nullptr;
+    unsigned long long *ind_len = nullptr, *dep_len = nullptr, *pos_ind = nullptr, *pos_dep = nullptr;
+    unsigned long long *row_ind_off = nullptr, *row_dep_off = nullptr;
+    CopyOp *ops = nullptr;
+    PglzJob *jobs = nullptr;
+    uint8_t *scratch = nullptr;
+    DevState *state = nullptr;
+    DevState *h_state = nullptr;   // pinned
+};
+
+// ---- library -----------------------------------------------------------------------------------
+
+extern "C" int cds_version(void) { return 100; }
+
+extern "C" const char *cds_status_str(int s)
+{
+    switch (s) {
+    case CDS_OK: return "ok";
+    case CDS_ERR_PARTIAL_PAGE: return "FATAL";
+    case CDS_ERR_ITEMID_ALIGN: return "Item identifier length do not match";
+    case CDS_ERR_TOAST_SPECIAL: return "THERE SHALL NOT BE INDICES";
+    case CDS_ERR_TUPLE: return "tuple does not fit its page";
+    case CDS_ERR_RAWSIZE: return "raw size does not match!";
+    case CDS_ERR_CHUNK_COUNT: return "chunk count does not match va_extsize";
+    case CDS_ERR_CHUNK_EXTENDED: return "chunk header is extended";
+    case CDS_ERR_MAX_CHUNK: return "max chunk size error";
+    case CDS_ERR_CHUNK_SIZE: return "unexpected chunk size";
+    case CDS_ERR_FINAL_SIZE: return "final size does not match";
+    case CDS_ERR_PGLZ_CORRUPT: return "compressed data is corrupt";
+    case CDS_ERR_SHAPE: return "decoded size does not match the sample shape";
+    case CDS_ERR_CATALOG_MISS: return "chunk id matches no external pointer";
+    case CDS_ERR_MISSING_VALUE: return "a value has no chunks";
+    case CDS_ERR_CUDA: return "CUDA error";
+    case CDS_ERR_ARG: return "bad argument";
+    case CDS_ERR_CAPACITY: return "capacity exceeded";
+    case CDS_ERR_NO_DEVICE: return "no CUDA device";
+    default: return "unknown";
+    }
+}
+
+extern "C" const char *cds_last_error(void) { return g_last_error; }
+
+extern "C" int cds_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int cds_host_alloc(void **ptr, uint64_t bytes)
+{
+    if (!ptr) return CDS_ERR_ARG;
+    if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
+    CU(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocPortable));
+    return CDS_OK;
+}
+
+extern "C" int cds_host_free(void *ptr)
+{
+    if (ptr) CU(cudaFreeHost(ptr));
+    return CDS_OK;
+}
+
+// ---- handle ------------------------------------------------------------------------------------
+
+template <typename T>
+static cudaError_t dalloc(T **p, uint64_t n)
+{
+    return cudaMalloc(reinterpret_cast<void **>(p), sizeof(T) * (n ? n : 1));
+}
+
+extern "C" int cds_segment_destroy(cds_segment *s)
+{
+    if (!s) return CDS_OK;
+    cudaSetDevice(s->device);
+    void *bufs[] = {s->stage_heap, s->stage_toast, s->heap_base, s->toast_base, s->rows, s->htab, s->dir_id, s->dir_loc,
+                    s->dir_ref, s->chunk_flag, s->vfirst, s->vcount, s->vseq0, s->vbytes, s->vscr, s->inline_flag,
+                    s->row_first, s->pos_of_row, s->row_at_pos, s->ind_len, s->dep_len, s->pos_ind, s->pos_dep,
+                    s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch, s->state};
+    for (void *b : bufs) if (b) cudaFree(b);
+    if (s->h_state) cudaFreeHost(s->h_state);
+    delete s;
+    return CDS_OK;
+}
+
+extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_heap_pages, uint64_t max_toast_pages,
+                                  uint64_t max_chunks, uint64_t scratch_bytes, int stage_pages)
+{
+    if (!out || max_heap_pages == 0) return CDS_ERR_ARG;
+    if (max_heap_pages > 0x7FFFFFFFull / 430 || max_toast_pages > 0x7FFFFFFFull / 8) return CDS_ERR_ARG;
+    int ndev = cds_device_count();
+    if (ndev == 0) return CDS_ERR_NO_DEVICE;
+    if (device < 0 || device >= ndev) return CDS_ERR_ARG;
+    CU(cudaSetDevice(device));
+    cds_segment *s = new (std::nothrow) cds_segment();
+    if (!s) return CDS_ERR_ARG;
+    s->device = device;
+    cudaDeviceGetAttribute(&s->num_sms, cudaDevAttrMultiProcessorCount, device);
+    s->cap_heap_pages = max_heap_pages;
+    s->cap_toast_pages = max_toast_pages;
+    s->cap_rows = max_heap_pages * 430;   // (32768-24) / (4-byte ItemId + 24+48-byte minimal tuple)
+    s->cap_chunks = max_chunks ? max_chunks : max_toast_pages * 6 + 4096;
+    s->cap_scratch = scratch_bytes == ~0ull ? max_toast_pages * (uint64_t)kPage : scratch_bytes;
+    uint64_t hsize = 1024;
+    while (hsize < s->cap_rows * 4) hsize <<= 1;   // 2 values per row, load factor <= 0.5
+    s->hmask = (uint32_t)(hsize - 1);
+    const uint64_t R = s->cap_rows, V = 2 * R, C = s->cap_chunks;
+    cudaError_t e = cudaSuccess;
+#define A(ptr, n) if (e == cudaSuccess) e = dalloc(&s->ptr, (n))
+    A(heap_base, max_heap_pages + 1); A(toast_base, max_toast_pages + 1); A(rows, R * kRowWords);
+    A(htab, hsize); A(dir_id, C); A(dir_loc, C); A(dir_ref, C); A(chunk_flag, C + 1);
+    A(vfirst, V); A(vcount, V); A(vseq0, V); A(vbytes, V); A(vscr, V + 1);
+    A(inline_flag, R + 1); A(row_first, R); A(pos_of_row, R); A(row_at_pos, R);
+    A(ind_len, R); A(dep_len, R); A(pos_ind, R + 1); A(pos_dep, R + 1); A(row_ind_off, R); A(row_dep_off, R);
+    A(ops, C); A(jobs, V); A(scratch, s->cap_scratch + 16); A(state, 1);
+    if (stage_pages) { A(stage_heap, max_heap_pages * (uint64_t)kPage); A(stage_toast, max_toast_pages * (uint64_t)kPage); }
+#undef A
+    if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&s->h_state), sizeof(DevState), cudaHostAllocPortable);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_toast_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGatherSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
+    if (e != cudaSuccess) {
+        int rc = cuda_fail(e, "cds_segment_create");
+        cds_segment_destroy(s);
+        return rc;
+    }
+    *out = s;
+    return CDS_OK;
+}
+
+// ---- steps -------------------------------------------------------------------------------------
+
+static inline uint32_t small_grid(const cds_segment *s) { return (uint32_t)s->num_sms * 4u; }
+
+static int reset_state(cds_segment *s, cudaStream_t st)
+{
+    DevState init;
+    memset(&init, 0, sizeof(init));
+    init.err_key = kNoErr;
+    *s->h_state = init;
+    CU(cudaMemcpyAsync(s->state, s->h_state, sizeof(DevState), cudaMemcpyHostToDevice, st));
+    s->have_rows = s->have_chunks = s->have_plan = false;
+    return CDS_OK;
+}
+
+static int index_values(cds_segment *s, cudaStream_t st)
+{
+    CU(cudaMemsetAsync(s->htab, 0xFF, sizeof(unsigned long long) * ((uint64_t)s->hmask + 1), st));
+    k_index_values<<<small_grid(s), 256, 0, st>>>(s->rows, s->state, s->htab, s->hmask, s->vfirst, s->vcount, s->vbytes, s->vseq0);
+    CU(cudaGetLastError());
+    s->have_rows = true;
+    return CDS_OK;
+}
+
+extern "C" int cds_heap_scan(cds_segment *s, const void *d_heap_pages, uint64_t n_pages, void *stream)
+{
+    if (!s || (!d_heap_pages && n_pages)) return CDS_ERR_ARG;
+    if (n_pages > s->cap_heap_pages) return CDS_ERR_CAPACITY;
+    if (reinterpret_cast<uintptr_t>(d_heap_pages) & 15u) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    int rc = reset_state(s, st);
+    if (rc) return rc;
+    s->d_heap = static_cast<const uint8_t *>(d_heap_pages);
+    s->n_heap_pages = n_pages;
+    k_page_index<<<1, 1024, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->state, 0, (uint32_t)s->cap_rows);
+    CU(cudaGetLastError());
+    if (n_pages) {
+        uint32_t grid = (uint32_t)(n_pages < small_grid(s) ? n_pages : small_grid(s));
+        k_heap_rows<<<grid, 128, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->rows, s->state);
+        CU(cudaGetLastError());
+    }
+    return index_values(s, st);
+}
+
+extern "C" int cds_set_rows(cds_segment *s, const uint32_t *h_rows, uint64_t n_rows, const void *d_inline_blob, void *stream)
+{
+    if (!s || (!h_rows && n_rows)) return CDS_ERR_ARG;
+    if (n_rows > s->cap_rows) return CDS_ERR_CAPACITY;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    int rc = reset_state(s, st);
+    if (rc) return rc;
+    s->h_state->n_rows = (uint32_t)n_rows;
+    CU(cudaMemcpyAsync(s->state, s->h_state, sizeof(DevState), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s->rows, h_rows, n_rows * kRowWords * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));   // h_rows is the caller's (pageable) memory
+    s->d_heap = static_cast<const uint8_t *>(d_inline_blob);
+    s->n_heap_pages = 0;
+    return index_values(s, st);
+}
+
+extern "C" int cds_toast_scan(cds_segment *s, const void *d_toast_pages, uint64_t n_pages, void *stream)
+{
+    if (!s || (!d_toast_pages && n_pages) || !s->have_rows) return CDS_ERR_ARG;
+    if (n_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
+    if (reinterpret_cast<uintptr_t>(d_toast_pages) & 15u) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    s->d_toast = static_cast<const uint8_t *>(d_toast_pages);
+    s->n_toast_pages = n_pages;
+    k_page_index<<<1, 1024, 0, st>>>(s->d_toast, (uint32_t)n_pages, s->toast_base, s->state, 1, (uint32_t)s->cap_chunks);
+    CU(cudaGetLastError());
+    if (n_pages) {
+        k_toast_walk<<<(uint32_t)((n_pages + 127) / 128), 128, 0, st>>>(
+            s->d_toast, (uint32_t)n_pages, s->toast_base, s->htab, s->hmask, s->dir_id, s->dir_loc, s->dir_ref,
+            s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state);
+        CU(cudaGetLastError());
+    }
+    s->have_chunks = true;
+    return CDS_OK;
+}
+
+__global__ void k_set_sample_bytes(DevState *st, uint32_t isb, uint32_t dsb)
+{
+    st->ind_sample_bytes = isb;
+    st->dep_sample_bytes = dsb;
+}
+
+extern "C" int cds_plan(cds_segment *s, uint32_t ind_sample_bytes, uint32_t dep_sample_bytes, void *stream)
+{
+    if (!s || !s->have_rows || !s->have_chunks) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    const uint32_t g = small_grid(s);
+    k_set_sample_bytes<<<1, 1, 0, st>>>(s->state, ind_sample_bytes, dep_sample_bytes);
+    k_plan_rows<<<g, 256, 0, st>>>(s->rows, s->d_toast, s->dir_loc, s->vfirst, s->vcount, s->vseq0, s->inline_flag,
+                                   s->chunk_flag, s->row_first, s->ind_len, s->dep_len, s->vscr, s->state);
+    k_plan_scan1<<<2, 1024, 0, st>>>(s->inline_flag, s->chunk_flag, s->state);
+    k_assign_pos<<<g, 256, 0, st>>>(s->rows, s->inline_flag, s->chunk_flag, s->row_first, s->ind_len, s->dep_len,
+                                    s->pos_of_row, s->row_at_pos, s->pos_ind, s->pos_dep, s->state);
+    k_plan_scan2<<<3, 1024, 0, st>>>(s->pos_ind, s->pos_dep, s->vscr, s->state);
+    k_row_offsets<<<g, 256, 0, st>>>(s->pos_of_row, s->pos_ind, s->pos_dep, s->row_ind_off, s->row_dep_off, s->state);
+    CU(cudaGetLastError());
+    s->have_plan = true;
+    return CDS_OK;
+}
+
+extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap, void *d_out_dep, uint64_t dep_cap,
+                               void *stream)
+{
+    if (!s || !s->have_plan) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    k_resolve<<<small_grid(s), 256, 0, st>>>(
+        s->rows, s->d_heap, s->dir_id, s->dir_loc, s->dir_ref, s->vfirst, s->vcount, s->vbytes, s->vscr, s->pos_of_row,
+        s->row_ind_off, s->row_dep_off, s->ind_len, s->dep_len, static_cast<uint8_t *>(d_out_ind), ind_cap,
+        static_cast<uint8_t *>(d_out_dep), dep_cap, s->scratch, s->cap_scratch, s->ops, s->jobs, s->state);
+    CU(cudaGetLastError());
+    if (s->n_toast_pages) {
+        uint32_t grid = (uint32_t)(s->n_toast_pages < (uint64_t)s->num_sms ? s->n_toast_pages : (uint64_t)s->num_sms);
+        k_toast_gather<<<grid, kGatherThreads, kGatherSmemBytes, st>>>(s->d_toast, (uint32_t)s->n_toast_pages,
+                                                                       s->toast_base, s->ops);
+        CU(cudaGetLastError());
+    }
+    // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
+    k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(s->jobs, &s->state->n_rows, 2u, 0u,
+                                                                                     nullptr, s->state);
+    CU(cudaGetLastError());
+    return CDS_OK;
+}
+
+static void decode_key(unsigned long long key, cds_summary *sum)
+{
+    if (key == kNoErr) { sum->status = CDS_OK; sum->err_stage = 0; sum->err_where = 0; return; }
+    sum->status = (uint32_t)(key & 0xFFu);
+    sum->err_stage = (uint32_t)(key >> 61);
+    sum->err_where = (key >> 28) & 0x1FFFFFFFFull;
+}
+
+extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
+{
+    if (!s) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    cds_summary local;
+    memset(&local, 0, sizeof(local));
+    const DevState &h = *s->h_state;
+    local.n_rows = h.n_rows; local.n_positions = h.n_pos; local.ind_bytes = h.ind_bytes; local.dep_bytes = h.dep_bytes;
+    local.n_chunks = h.n_chunks; local.n_inline = h.n_inline; local.scratch_bytes = h.scratch_bytes;
+    decode_key(h.err_key, &local);
+    if (sum) *sum = local;
+    return (int)local.status;
+}
+
+extern "C" int cds_decode_device(cds_segment *s, const void *d_heap, uint64_t n_heap_pages, const void *d_toast,
+                                 uint64_t n_toast_pages, uint32_t isb, uint32_t dsb, void *d_out_ind, uint64_t ind_cap,
+                                 void *d_out_dep, uint64_t dep_cap, void *stream, cds_summary *sum)
+{
+    int rc = cds_heap_scan(s, d_heap, n_heap_pages, stream);
+    if (rc) return rc;
+    if ((rc = cds_toast_scan(s, d_toast, n_toast_pages, stream))) return rc;
+    if ((rc = cds_plan(s, isb, dsb, stream))) return rc;
+    if ((rc = cds_materialize(s, d_out_ind, ind_cap, d_out_dep, dep_cap, stream))) return rc;
+    return sum ? cds_finish(s, stream, sum) : CDS_OK;
+}
+
+extern "C" int cds_decode_host(cds_segment *s, const void *h_heap, uint64_t n_heap_pages, const void *h_toast,
+                               uint64_t n_toast_pages, uint32_t isb, uint32_t dsb, void *d_out_ind, uint64_t ind_cap,
+                               void *d_out_dep, uint64_t dep_cap, void *stream, cds_summary *sum)
+{
+    if (!s || !s->stage_heap || !s->stage_toast) return CDS_ERR_ARG;
+    if (n_heap_pages > s->cap_heap_pages || n_toast_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    CU(cudaMemcpyAsync(s->stage_heap, h_heap, n_heap_pages * (uint64_t)kPage, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s->stage_toast, h_toast, n_toast_pages * (uint64_t)kPage, cudaMemcpyHostToDevice, st));
+    return cds_decode_device(s, s->stage_heap, n_heap_pages, s->stage_toast, n_toast_pages, isb, dsb, d_out_ind, ind_cap,
+                             d_out_dep, dep_cap, stream, sum);
+}
+
+// ---- exports for the Python mirror -------------------------------------------------------------
+
+extern "C" int cds_export_rows(cds_segment *s, uint32_t *h_rows, uint64_t cap_rows, uint64_t *n_rows, void *stream)
+{
+    if (!s || !n_rows || !s->have_rows) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    *n_rows = s->h_state->n_rows;
+    if (*n_rows > cap_rows) return CDS_ERR_CAPACITY;
+    if (*n_rows && h_rows) CU(cudaMemcpy(h_rows, s->rows, *n_rows * kRowWords * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    return CDS_OK;
+}
+
+extern "C" int cds_export_layout(cds_segment *s, uint64_t *h_order, uint64_t *h_ind_off, uint64_t *h_dep_off,
+                                 uint64_t *h_ind_len, uint64_t *h_dep_len, uint64_t cap_rows, void *stream)
+{
+    if (!s || !s->have_plan) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const uint64_t n_rows = s->h_state->n_rows, n_pos = s->h_state->n_pos;
+    if (n_rows > cap_rows) return CDS_ERR_CAPACITY;
+    if (n_pos && h_order) {
+        uint32_t *tmp = (uint32_t *)malloc(sizeof(uint32_t) * n_pos);
+        if (!tmp) return CDS_ERR_ARG;
+        cudaError_t e = cudaMemcpy(tmp, s->row_at_pos, sizeof(uint32_t) * n_pos, cudaMemcpyDeviceToHost);
+        for (uint64_t i = 0; e == cudaSuccess && i < n_pos; i++) h_order[i] = tmp[i];
+        free(tmp);
+        if (e != cudaSuccess) return cuda_fail(e, "export order");
+    }
+    if (n_rows) {
+        if (h_ind_off) CU(cudaMemcpy(h_ind_off, s->row_ind_off, 8 * n_rows, cudaMemcpyDeviceToHost));
+        if (h_dep_off) CU(cudaMemcpy(h_dep_off, s->row_dep_off, 8 * n_rows, cudaMemcpyDeviceToHost));
+        if (h_ind_len) CU(cudaMemcpy(h_ind_len, s->ind_len, 8 * n_rows, cudaMemcpyDeviceToHost));
+        if (h_dep_len) CU(cudaMemcpy(h_dep_len, s->dep_len, 8 * n_rows, cudaMemcpyDeviceToHost));
+    }
+    return CDS_OK;
+}
+
+extern "C" int cds_export_chunks(cds_segment *s, uint32_t *h_id, uint32_t *h_seq, uint64_t *h_off, uint32_t *h_len,
+                                 uint64_t cap_chunks, uint64_t *n_chunks, void *stream)
+{
+    if (!s || !n_chunks || !s->have_chunks) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const uint64_t n = s->h_state->n_chunks;
+    *n_chunks = n;
+    if (n > cap_chunks) return CDS_ERR_CAPACITY;
+    if (n == 0) return CDS_OK;
+    uint2 *a = (uint2 *)malloc(sizeof(uint2) * n), *b = (uint2 *)malloc(sizeof(uint2) * n);
+    if (!a || !b) { free(a); free(b); return CDS_ERR_ARG; }
+    cudaError_t e = cudaMemcpy(a, s->dir_id, sizeof(uint2) * n, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(b, s->dir_loc, sizeof(uint2) * n, cudaMemcpyDeviceToHost);
+    for (uint64_t i = 0; e == cudaSuccess && i < n; i++) {
+        if (h_id) h_id[i] = a[i].x;
+        if (h_seq) h_seq[i] = a[i].y;
+        if (h_off) h_off[i] = (uint64_t)b[i].x * kPage + (b[i].y & 0xFFFFu);
+        if (h_len) h_len[i] = b[i].y >> 16;
+    }
+    free(a); free(b);
+    if (e != cudaSuccess) return cuda_fail(e, "export chunks");
+    return CDS_OK;
+}
+
+// ---- pglz on its own ---------------------------------------------------------------------------
+
+extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_src_off, void *d_dst,
+                                         const uint64_t *h_dst_off, uint64_t n, int32_t *h_status, void *stream)
+{
+    if (n == 0) return CDS_OK;
+    if (!d_src || !h_src_off || !d_dst || !h_dst_off || n > 0x7FFFFFFFull) return CDS_ERR_ARG;
+    if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(device));
+    // headers are read on the host side of the call: fetch the 8 header bytes of every datum
+    PglzJob *h_jobs = (PglzJob *)malloc(sizeof(PglzJob) * n);
+    int32_t *h_stat = (int32_t *)calloc(n, sizeof(int32_t));
+    if (!h_jobs || !h_stat) { free(h_jobs); free(h_stat); return CDS_ERR_ARG; }
+    const uint8_t *src = static_cast<const uint8_t *>(d_src);
+    uint8_t *dst = static_cast<uint8_t *>(d_dst);
+    cudaError_t e = cudaSuccess;
+    for (uint64_t i = 0; i < n && e == cudaSuccess; i++) {
+        PglzJob &j = h_jobs[i];
+        j.src = 0; j.dst = 0; j.slen = kNone; j.rawsize = 0; j.err_key = 0;
+        const uint64_t avail = h_src_off[i + 1] - h_src_off[i], room = h_dst_off[i + 1] - h_dst_off[i];
+        uint8_t hdr[8];
+        if (avail < 8) { h_stat[i] = CDS_ERR_PGLZ_CORRUPT; continue; }
+        e = cudaMemcpyAsync(hdr, src + h_src_off[i], 8, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) break;
+        const uint32_t varsize = (((uint32_t)hdr[0] << 24) | ((uint32_t)hdr[1] << 16) | ((uint32_t)hdr[2] << 8) | hdr[3]) & 0x3FFFFFFFu;
+        const uint32_t rawsize = (uint32_t)hdr[4] | ((uint32_t)hdr[5] << 8) | ((uint32_t)hdr[6] << 16) | ((uint32_t)hdr[7] << 24);
+        if (varsize < 8 || varsize > avail || rawsize > room) { h_stat[i] = CDS_ERR_PGLZ_CORRUPT; continue; }
+        j.src = (unsigned long long)(src + h_src_off[i] + 8);
+        j.dst = (unsigned long long)(dst + h_dst_off[i]);
+        j.slen = varsize - 8;
+        j.rawsize = rawsize;
+    }
+    PglzJob *d_jobs = nullptr;
+    int32_t *d_stat = nullptr;
+    if (e == cudaSuccess) e = dalloc(&d_jobs, n);
+    if (e == cudaSuccess) e = dalloc(&d_stat, n);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_jobs, h_jobs, sizeof(PglzJob) * n, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_stat, h_stat, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
+    if (e == cudaSuccess) {
+        uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
+        if (grid > 148u * 7u) grid = 148u * 7u;
+        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, 0u, (uint32_t)n, d_stat, nullptr);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_stat, d_stat, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess && h_status) memcpy(h_status, h_stat, sizeof(int32_t) * n);
+    if (d_jobs) cudaFree(d_jobs);
+    if (d_stat) cudaFree(d_stat);
+    free(h_jobs); free(h_stat);
+    if (e != cudaSuccess) return cuda_fail(e, "cds_pglz_decompress_batch");
+    return CDS_OK;
+}
+
+extern "C" void pglz_decompress(const void *source, char *dest)
+{
+    // Same contract as pg_lzcompress.c:49-50: the caller sized `dest` from the rawsize field.
+    const uint8_t *h = static_cast<const uint8_t *>(source);
+    const uint32_t varsize = (((uint32_t)h[0] << 24) | ((uint32_t)h[1] << 16) | ((uint32_t)h[2] << 8) | h[3]) & 0x3FFFFFFFu;
+    const uint32_t rawsize = (uint32_t)h[4] | ((uint32_t)h[5] << 8) | ((uint32_t)h[6] << 16) | ((uint32_t)h[7] << 24);
+    int dev = 0;
+    if (cds_device_count() == 0 || cudaGetDevice(&dev) != cudaSuccess) {
+        fprintf(stderr, "pglz_decompress: no CUDA device (libcds_da has no CPU path)\n");
+        abort();
+    }
+    uint8_t *d_src = nullptr, *d_dst = nullptr;
+    int32_t status = CDS_ERR_CUDA;
+    cudaError_t e = dalloc(&d_src, (uint64_t)varsize + 16);
+    if (e == cudaSuccess) e = dalloc(&d_dst, (uint64_t)rawsize + 16);
+    if (e == cudaSuccess) e = cudaMemcpy(d_src, h, varsize < 8 ? 8 : varsize, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        uint64_t so[2] = {0, varsize < 8 ? 8u : varsize}, dof[2] = {0, rawsize};
+        int rc = cds_pglz_decompress_batch(dev, d_src, so, d_dst, dof, 1, &status, nullptr);
+        if (rc != CDS_OK) status = rc;
+    }
+    if (e == cudaSuccess && rawsize) e = cudaMemcpy(dest, d_dst, rawsize, cudaMemcpyDeviceToHost);
+    if (d_src) cudaFree(d_src);
+    if (d_dst) cudaFree(d_dst);
+    if (e != cudaSuccess) {
+        fprintf(stderr, "pglz_decompress: %s\n", cudaGetErrorString(e));
+        abort();
+    }
+    if (status != CDS_OK) printf("compressed data is corrupt");   // pg_lzcompress.c:138-139
+}
+
+// ---- consumer casts ----------------------------------------------------------------------------
+
+extern "C" int cds_onehot_argmax_i16(const void *d_onehot, uint64_t n_rows, uint32_t classes, void *d_labels, void *stream)
+{
+    if (n_rows == 0) return CDS_OK;
+    if (!d_onehot || !d_labels || classes == 0) return CDS_ERR_ARG;
+    uint64_t blocks = (n_rows + 7) / 8;
+    if (blocks > 148ull * 16) blocks = 148ull * 16;
+    k_onehot_argmax_i16<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const int16_t *>(d_onehot), n_rows, classes,
+                                                                           static_cast<long long *>(d_labels));
+    CU(cudaGetLastError());
+    return CDS_OK;
+}
+
+extern "C" int cds_nhwc_to_nchw_f32(const void *d_src, uint64_t n, uint32_t hw, uint32_t ch, void *d_dst, void *stream)
+{
+    if (n == 0) return CDS_OK;
+    if (!d_src || !d_dst || hw == 0 || ch == 0) return CDS_ERR_ARG;
+    uint64_t total = n * hw * ch, blocks = (total + 255) / 256;
+    if (blocks > 148ull * 32) blocks = 148ull * 32;
+    k_nhwc_to_nchw_f32<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const float *>(d_src), n, hw, ch,
+                                                                          static_cast<float *>(d_dst));
+    CU(cudaGetLastError());
+    return CDS_OK;
+}
+
+extern "C" int cds_f32_to_bf16(const void *d_src, uint64_t n_elems, void *d_dst, void *stream)
+{
+    if (n_elems == 0) return CDS_OK;
+    if (!d_src || !d_dst) return CDS_ERR_ARG;
+    uint64_t blocks = (n_elems / 4 + 255) / 256 + 1;
+    if (blocks > 148ull * 32) blocks = 148ull * 32;
+    k_f32_to_bf16<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const float *>(d_src), n_elems,
+                                                                     static_cast<__nv_bfloat16 *>(d_dst));
+    CU(cudaGetLastError());
+    return CDS_OK;
+}

@@ -1,0 +1,429 @@
+// page_scan.cuh — page / ItemId / tuple scan kernels and the detoast plan.
+//
+// Replaces, on the device (paths relative to /root/reference/cerebro_gpdb/):
+//   deserialize_page_header    pg_page_reader.py:253-269
+//   deserialize_item           pg_page_reader.py:285-305
+//   desirialize_tupdata        pg_page_reader.py:328-351
+//   generator_page(toast=True) pg_page_reader.py:385-422
+//   read_toast_all_bytes       pg_page_reader.py:497-524
+//   detoast bookkeeping        pg_page_reader.py:527-612 (order of results, size checks)
+//
+// All of this is metadata work: it touches a few sectors per 32 KB page (< 1 % of the bytes);
+// the bulk traffic is in toast_gather.cuh.
+#pragma once
+#include "cds_common.cuh"
+
+namespace cds {
+
+// Shared by the heap and the TOAST relation: item count per page from pd_lower, exclusive scan
+// into base[0..n_pages], validation of the header.  ONE block of 1024 threads.
+//   toast != 0 additionally asserts pd_special == BLCKSZ (ppr:388-389).
+__global__ void __launch_bounds__(1024, 1)
+k_page_index(const uint8_t *__restrict__ pages, uint32_t n_pages, uint32_t *__restrict__ base,
+             DevState *st, int toast, uint32_t cap_items)
+{
+    __shared__ uint32_t sh[33];
+    uint32_t carry = 0;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t stage = toast ? 1u : 0u;
+    for (uint32_t b = 0; b < n_pages; b += 1024) {
+        uint32_t p = b + threadIdx.x;
+        uint32_t cnt = 0;
+        if (p < n_pages) {
+            const uint8_t *pg = pages + (size_t)p * kPage;
+            // pd_lower, pd_upper, pd_special live at bytes 12..17 of the header (ppr:629-638)
+            uint2 w = *reinterpret_cast<const uint2 *>(pg + 8);   // bytes 8..15
+            uint32_t pd_lower = w.y & 0xFFFFu;
+            uint32_t w2 = *reinterpret_cast<const uint32_t *>(pg + 16);
+            uint32_t pd_special = w2 & 0xFFFFu;
+            if (pd_lower < kPageHdr || ((pd_lower - kPageHdr) & 3u)) {
+                report(st, stage, p, 0, 0, CDS_ERR_ITEMID_ALIGN);
+            } else if (pd_lower > kPage) {
+                report(st, stage, p, 0, 1, CDS_ERR_TUPLE);
+            } else if (toast && pd_special != kPage) {
+                report(st, stage, p, 0, 2, CDS_ERR_TOAST_SPECIAL);
+            } else {
+                cnt = (pd_lower - kPageHdr) >> 2;
+            }
+        }
+        uint32_t inc = warp_inclusive_scan(cnt);
+        if (lane == 31) sh[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = sh[lane];
+            uint32_t winc = warp_inclusive_scan(w);
+            sh[lane] = winc - w;
+            if (lane == 31) sh[32] = winc;
+        }
+        __syncthreads();
+        if (p < n_pages) base[p] = carry + sh[warp] + inc - cnt;
+        carry += sh[32];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        if (carry > cap_items) {
+            // refuse everything: downstream kernels see zero items
+            report(st, stage, 0, 0, 0, CDS_ERR_CAPACITY);
+            carry = 0;
+            for (uint32_t p = 0; p < n_pages; p++) base[p] = 0;
+        }
+        base[n_pages] = carry;
+        if (toast) st->n_chunks = carry; else st->n_rows = carry;
+    }
+}
+
+// One block per heap page (grid-stride), one thread per ItemId: parse the MADlib packed row and
+// write its 16-word descriptor in table order.
+__global__ void __launch_bounds__(128)
+k_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *__restrict__ base,
+            uint32_t *__restrict__ rows, DevState *st)
+{
+    for (uint32_t p = blockIdx.x; p < n_pages; p += gridDim.x) {
+        const uint8_t *pg = heap + (size_t)p * kPage;
+        const uint32_t r0 = base[p], n = base[p + 1] - r0;
+        for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+            uint32_t *row = rows + (size_t)(r0 + i) * kRowWords;
+            uint32_t iid = *reinterpret_cast<const uint32_t *>(pg + kPageHdr + 4u * i);
+            uint32_t lp_off = iid & 0x7FFFu, lp_len = iid >> 17;            // ppr:287-300
+            uint32_t end = min(lp_off + lp_len, kPage);                      // python slices clamp
+            bool bad = end < lp_off + kItemHdr;
+            uint32_t t_hoff = bad ? 0u : pg[lp_off + 22];                    // ppr:272-276
+            bad = bad || (lp_off + t_hoff > end);
+            uint32_t tdlen = bad ? 0u : end - (lp_off + t_hoff);
+            bad = bad || tdlen < 44u;                                        // unpack of tupdata[24:44]
+            if (bad) {
+                report(st, 0, p, 1, i, CDS_ERR_TUPLE);
+                for (uint32_t k = 0; k < kRowWords; k++) row[k] = 0;
+                row[RW_INLINE_LEN] = kNone;                                  // marks the row unusable
+                continue;
+            }
+            const uint8_t *td = pg + lp_off + t_hoff;
+            row[RW_DIST_KEY] = ld_u32(td);
+            row[RW_BUFFER_ID] = ld_u32(td + tdlen - 4);                      // ppr:330
+#pragma unroll
+            for (int k = 0; k < 5; k++) row[RW_IND + k] = ld_u32(td + 4 + 4 * k);    // ppr:337
+#pragma unroll
+            for (int k = 0; k < 5; k++) row[RW_DEP + k] = ld_u32(td + 24 + 4 * k);   // ppr:342
+            // extended && !external && compressed  <=>  (first byte & 0xC0) == 0x40   (ppr:343)
+            row[RW_DEP_EXTERNAL] = ((td[24] & 0xC0u) == 0x40u) ? 0u : 1u;
+            unsigned long long off = (unsigned long long)(td + 24 - heap);
+            row[RW_INLINE_OFF_LO] = (uint32_t)off;
+            row[RW_INLINE_OFF_HI] = (uint32_t)(off >> 32);
+            row[RW_INLINE_LEN] = tdlen - 24u;
+        }
+    }
+}
+
+// Build the va_valueid -> value hash table from the row descriptors and reset per-value stats.
+// value index v = 2*row + (0 independent_var | 1 dependent_var) = the row number in df_toast.
+__global__ void __launch_bounds__(256)
+k_index_values(const uint32_t *__restrict__ rows, const DevState *st, unsigned long long *htab,
+               uint32_t hmask, uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes,
+               uint32_t *vseq0)
+{
+    const uint32_t n_rows = st->n_rows;
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
+        const uint32_t *row = rows + (size_t)r * kRowWords;
+#pragma unroll
+        for (uint32_t a = 0; a < 2; a++) {
+            uint32_t v = 2 * r + a;
+            vfirst[v] = kNone; vcount[v] = 0; vbytes[v] = 0; vseq0[v] = kNone;
+        }
+        if (row[RW_INLINE_LEN] == kNone) continue;
+        htab_insert(htab, hmask, row[RW_IND + 3], 2 * r);                    // always external (ppr:348)
+        // an inline dependent_var still contributes the bytes at its va_valueid position to the
+        // reference's chunk filter (ppr:516); mark it so a hit is reported the way .iloc[0] fails
+        htab_insert(htab, hmask, row[RW_DEP + 3], (row[RW_DEP_EXTERNAL] ? 0u : 0x80000000u) | (2 * r + 1));
+    }
+}
+
+// One thread per TOAST page: physical walk upward from pd_upper (ppr:391-414).
+__global__ void __launch_bounds__(128)
+k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t *__restrict__ base,
+             const unsigned long long *__restrict__ htab, uint32_t hmask,
+             uint2 *__restrict__ dir_id, uint2 *__restrict__ dir_loc, uint32_t *__restrict__ dir_ref,
+             uint32_t *__restrict__ chunk_flag,
+             uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0, DevState *st)
+{
+    uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pages) return;
+    const uint8_t *pg = toast + (size_t)p * kPage;
+    const uint32_t g0 = base[p], n = base[p + 1] - g0;
+    uint32_t lp = ld_u16(pg + 14);                                           // pd_upper
+    bool dead = false;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t g = g0 + i;
+        uint32_t id = 0, seq = 0, loc_off = 0, loc_len = 0, ref = kNone, hdr0 = 0;
+        if (!dead) {
+            lp = (lp + 7u) & ~7u;                                            // MAX_ALIGN (ppr:394)
+            if (lp + kItemHdr > kPage) dead = true;
+        }
+        if (!dead) {
+            uint32_t t_hoff = pg[lp + 22];
+            uint32_t hdr = lp + t_hoff + 8u;                                 // ppr:399-403
+            if (hdr + 4u > kPage) dead = true;
+            else {
+                uint32_t chunksize = ld_u32be(pg + hdr) & 0x3FFFFFFFu;       // VARSIZE (ppr:130-131,404)
+                if (chunksize < 4u || hdr + chunksize > kPage) dead = true;
+                else {
+                    id = ld_u32(pg + lp + t_hoff);
+                    seq = ld_u32(pg + lp + t_hoff + 4);
+                    loc_off = hdr + 4u;
+                    loc_len = chunksize - 4u;
+                    hdr0 = pg[hdr];
+                    lp += t_hoff + 8u + chunksize;                           // ppr:405-414
+                }
+            }
+            if (dead) report(st, 1, p, 1, i, CDS_ERR_TUPLE);
+        }
+        if (!dead) {
+            ref = htab_find(htab, hmask, id);                                // ppr:516
+            if (ref != kNone) {
+                if (ref & 0x80000000u) {
+                    // only a non-external row carries this id: the reference dies in detoast (ppr:563-564)
+                    report(st, 3, g, 0, 0, CDS_ERR_CATALOG_MISS);
+                    ref = kNone;
+                } else {
+                    atomicMin(&vfirst[ref], g);
+                    atomicAdd(&vcount[ref], 1u);
+                    atomicAdd(&vbytes[ref], (unsigned long long)loc_len);
+                    if (seq == 0) atomicMin(&vseq0[ref], g);
+                }
+            }
+        }
+        dir_id[g] = make_uint2(id, seq);
+        dir_loc[g] = make_uint2(p, loc_off | (loc_len << 16));
+        dir_ref[g] = (ref == kNone) ? kNone : (ref | ((hdr0 & 0xC0u) ? 0x40000000u : 0u));
+        chunk_flag[g] = 0;
+    }
+}
+
+// Per row: decoded lengths, whether the row enters the result in the inline phase, and the
+// first-seen chunk of its external values.
+__global__ void __launch_bounds__(256)
+k_plan_rows(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ toast,
+            const uint2 *__restrict__ dir_loc, const uint32_t *__restrict__ vfirst,
+            const uint32_t *__restrict__ vcount, const uint32_t *__restrict__ vseq0,
+            uint32_t *__restrict__ inline_flag, uint32_t *__restrict__ chunk_flag,
+            uint32_t *__restrict__ row_first, unsigned long long *__restrict__ ind_len,
+            unsigned long long *__restrict__ dep_len, unsigned long long *__restrict__ vscr, DevState *st)
+{
+    const uint32_t n_rows = st->n_rows;
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
+        const uint32_t *row = rows + (size_t)r * kRowWords;
+        unsigned long long len[2] = {0, 0};
+        uint32_t first = kNone;
+        const bool usable = row[RW_INLINE_LEN] != kNone;
+        const bool is_inline = usable && row[RW_DEP_EXTERNAL] == 0;
+        for (uint32_t a = 0; a < 2; a++) {
+            const uint32_t v = 2 * r + a;
+            vscr[v] = 0;
+            if (!usable) continue;
+            const uint32_t *ptr = row + (a ? RW_DEP : RW_IND);
+            if (a == 1 && is_inline) {
+                // inline pglz varlena: rawsize is the LE word after the BE length word (ppr:538)
+                len[1] = ptr[1];
+                continue;
+            }
+            if (vcount[v] == 0) continue;                                   // value has no chunks
+            first = min(first, vfirst[v]);
+            const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
+            if (va_extsize == va_rawsize - 4u) {
+                len[a] = va_extsize;                                         // stored uncompressed
+            } else {
+                // compressed: rawsize is the first LE word of the stored payload (ppr:240, 574-594)
+                uint32_t g = vseq0[v];
+                if (g != kNone) {
+                    uint2 loc = dir_loc[g];
+                    if ((loc.y >> 16) >= 4u)
+                        len[a] = ld_u32(toast + (size_t)loc.x * kPage + (loc.y & 0xFFFFu));
+                }
+                vscr[v] = ((unsigned long long)va_extsize + 15ull) & ~15ull;
+            }
+        }
+        ind_len[r] = len[0];
+        dep_len[r] = len[1];
+        inline_flag[r] = is_inline ? 1u : 0u;
+        row_first[r] = first;
+        if (!is_inline && first != kNone) chunk_flag[first] = 1u;
+    }
+}
+
+// Block 0: rank of inline rows (table order).  Block 1: rank of first-seen chunks.
+__global__ void __launch_bounds__(1024, 1)
+k_plan_scan1(uint32_t *inline_flag, uint32_t *chunk_flag, DevState *st)
+{
+    __shared__ uint32_t sh[33];
+    if (blockIdx.x == 0) {
+        uint32_t tot = block_exclusive_scan<uint32_t, uint32_t>(inline_flag, inline_flag, st->n_rows, sh);
+        if (threadIdx.x == 0) st->n_inline = tot;
+    } else {
+        uint32_t n = st->n_chunks;
+        uint32_t tot = block_exclusive_scan<uint32_t, uint32_t>(chunk_flag, chunk_flag, n, sh);
+        if (threadIdx.x == 0) chunk_flag[n] = tot;
+    }
+}
+
+// Result position of every row: inline rows first in table order (ppr:532-552), then rows in
+// the order their first external chunk is met (ppr:553-611; an existing entry keeps its place).
+__global__ void __launch_bounds__(256)
+k_assign_pos(const uint32_t *__restrict__ rows, const uint32_t *__restrict__ inline_rank,
+             const uint32_t *__restrict__ chunk_rank, const uint32_t *__restrict__ row_first,
+             const unsigned long long *__restrict__ ind_len, const unsigned long long *__restrict__ dep_len,
+             uint32_t *__restrict__ pos_of_row, uint32_t *__restrict__ row_at_pos,
+             unsigned long long *__restrict__ pos_ind, unsigned long long *__restrict__ pos_dep, DevState *st)
+{
+    const uint32_t n_rows = st->n_rows, n_inline = st->n_inline, n_chunks = st->n_chunks;
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->n_pos = n_inline + chunk_rank[n_chunks];
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
+        const uint32_t *row = rows + (size_t)r * kRowWords;
+        const bool usable = row[RW_INLINE_LEN] != kNone;
+        const bool is_inline = usable && row[RW_DEP_EXTERNAL] == 0;
+        uint32_t pos = kNone;
+        if (is_inline) pos = inline_rank[r];
+        else if (row_first[r] != kNone) pos = n_inline + chunk_rank[row_first[r]];
+        pos_of_row[r] = pos;
+        if (pos == kNone) continue;     // no chunk of this row exists: the reference never emits it
+        row_at_pos[pos] = r;
+        pos_ind[pos] = ind_len[r];
+        pos_dep[pos] = dep_len[r];
+        if (ind_len[r] == 0 || dep_len[r] == 0) report(st, 4, pos, 0, 0, CDS_ERR_MISSING_VALUE);
+        const uint32_t isb = st->ind_sample_bytes, dsb = st->dep_sample_bytes;
+        if (isb && dsb && ind_len[r] && dep_len[r]) {
+            if (ind_len[r] % isb || dep_len[r] % dsb || ind_len[r] / isb != dep_len[r] / dsb)
+                report(st, 4, pos, 1, 0, CDS_ERR_SHAPE);
+        }
+    }
+}
+
+// Three independent 64-bit exclusive scans, one block each: output offsets of the two value
+// streams in result order, and staging offsets of compressed external values.
+__global__ void __launch_bounds__(1024, 1)
+k_plan_scan2(unsigned long long *pos_ind, unsigned long long *pos_dep, unsigned long long *vscr, DevState *st)
+{
+    __shared__ unsigned long long sh[33];
+    if (blockIdx.x == 0) {
+        unsigned long long t = block_exclusive_scan<unsigned long long, unsigned long long>(pos_ind, pos_ind, st->n_pos, sh);
+        if (threadIdx.x == 0) st->ind_bytes = t;
+    } else if (blockIdx.x == 1) {
+        unsigned long long t = block_exclusive_scan<unsigned long long, unsigned long long>(pos_dep, pos_dep, st->n_pos, sh);
+        if (threadIdx.x == 0) st->dep_bytes = t;
+    } else {
+        unsigned long long t = block_exclusive_scan<unsigned long long, unsigned long long>(vscr, vscr, 2u * st->n_rows, sh);
+        if (threadIdx.x == 0) st->scratch_bytes = t;
+    }
+}
+
+// Per-row output offsets (exported to the host mirror and used by the decode kernels).
+__global__ void __launch_bounds__(256)
+k_row_offsets(const uint32_t *__restrict__ pos_of_row, const unsigned long long *__restrict__ pos_ind,
+              const unsigned long long *__restrict__ pos_dep, unsigned long long *__restrict__ row_ind_off,
+              unsigned long long *__restrict__ row_dep_off, const DevState *st)
+{
+    const uint32_t n_rows = st->n_rows;
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
+        uint32_t pos = pos_of_row[r];
+        row_ind_off[r] = pos == kNone ? ~0ull : pos_ind[pos];
+        row_dep_off[r] = pos == kNone ? ~0ull : pos_dep[pos];
+    }
+}
+
+// One thread per chunk: the reference's per-chunk checks (ppr:570-596) and the copy descriptor.
+// Also one pglz job per value (inline datums and compressed external values).
+__global__ void __launch_bounds__(256)
+k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
+          const uint2 *__restrict__ dir_id, const uint2 *__restrict__ dir_loc, const uint32_t *__restrict__ dir_ref,
+          const uint32_t *__restrict__ vfirst, const uint32_t *__restrict__ vcount,
+          const unsigned long long *__restrict__ vbytes, const unsigned long long *__restrict__ vscr,
+          const uint32_t *__restrict__ pos_of_row,
+          const unsigned long long *__restrict__ row_ind_off, const unsigned long long *__restrict__ row_dep_off,
+          const unsigned long long *__restrict__ ind_len, const unsigned long long *__restrict__ dep_len,
+          uint8_t *out_ind, unsigned long long cap_ind, uint8_t *out_dep, unsigned long long cap_dep,
+          uint8_t *scratch, unsigned long long cap_scratch,
+          CopyOp *__restrict__ ops, PglzJob *__restrict__ jobs, DevState *st)
+{
+    const uint32_t n_chunks = st->n_chunks, n_rows = st->n_rows;
+    const bool fits = st->ind_bytes <= cap_ind && st->dep_bytes <= cap_dep && st->scratch_bytes <= cap_scratch;
+    if (!fits && blockIdx.x == 0 && threadIdx.x == 0) report(st, 4, 0, 2, 0, CDS_ERR_CAPACITY);
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+
+    for (uint32_t g = tid; g < n_chunks; g += nth) {
+        CopyOp op;
+        op.dst = 0; op.src_off = 0; op.len = 0;
+        const uint32_t ref = dir_ref[g];
+        if (ref != kNone) {
+            const uint32_t v = ref & 0x3FFFFFFFu, r = v >> 1, a = v & 1u;
+            const uint32_t *ptr = rows + (size_t)r * kRowWords + (a ? RW_DEP : RW_IND);
+            const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
+            const uint32_t numchunks = va_extsize ? (va_extsize - 1u) / kChunkMax + 1u : 0u;   // ppr:155-156
+            const uint32_t first = vfirst[v];
+            const uint2 id = dir_id[g], loc = dir_loc[g];
+            const uint32_t idx = id.y, size = loc.y >> 16;
+            bool ok = true;
+            if (vcount[v] != numchunks) {                                   // ppr:570-572
+                if (g == first) report(st, 3, first, 0, 0, CDS_ERR_CHUNK_COUNT);
+                ok = false;
+            }
+            if (ref & 0x40000000u) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_EXTENDED); ok = false; }       // ppr:580
+            if (idx == 0 && size < va_extsize && size != kChunkMax) { report(st, 3, first, 1, idx, CDS_ERR_MAX_CHUNK); ok = false; }   // ppr:584-586
+            if (numchunks && idx < numchunks - 1u && size != kChunkMax) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_SIZE); ok = false; }   // ppr:587-588
+            if (numchunks && idx == numchunks - 1u && (unsigned long long)idx * kChunkMax + size != va_extsize) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_SIZE); ok = false; }   // ppr:589-591
+            if (idx >= numchunks) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_SIZE); ok = false; }   // outside the pointer's extent
+            if (g == first && vbytes[v] != va_extsize) { report(st, 3, first, 2, 0, CDS_ERR_FINAL_SIZE); }  // ppr:595-596
+            if (ok && vbytes[v] == va_extsize && fits && pos_of_row[r] != kNone) {
+                const bool compressed = va_extsize != va_rawsize - 4u;
+                unsigned long long dst;
+                if (compressed) dst = (unsigned long long)(scratch + vscr[v]);
+                else dst = a ? (unsigned long long)(out_dep + row_dep_off[r]) : (unsigned long long)(out_ind + row_ind_off[r]);
+                op.dst = dst + (unsigned long long)idx * kChunkMax;
+                op.src_off = loc.y & 0xFFFFu;
+                op.len = size;
+            }
+        }
+        ops[g] = op;
+    }
+
+    for (uint32_t v = tid; v < 2u * n_rows; v += nth) {
+        PglzJob job;
+        job.src = 0; job.dst = 0; job.slen = kNone; job.rawsize = 0; job.err_key = 0;
+        const uint32_t r = v >> 1, a = v & 1u;
+        const uint32_t *row = rows + (size_t)r * kRowWords;
+        const uint32_t pos = pos_of_row[r];
+        if (fits && pos != kNone && row[RW_INLINE_LEN] != kNone) {
+            if (a == 1 && row[RW_DEP_EXTERNAL] == 0) {
+                // inline datum: tupdata[24:] starts with the 8-byte PGLZ header (ppr:344, 537-543)
+                const uint8_t *src = heap + (((unsigned long long)row[RW_INLINE_OFF_HI] << 32) | row[RW_INLINE_OFF_LO]);
+                const uint32_t avail = row[RW_INLINE_LEN];
+                const uint32_t varsize = ld_u32be(src) & 0x3FFFFFFFu;
+                job.err_key = make_err_key(2, r, 0, 0, CDS_ERR_PGLZ_CORRUPT);
+                if (avail < 8u || varsize < 8u || varsize > avail) {
+                    atomicMin(&st->err_key, job.err_key);
+                } else {
+                    job.src = (unsigned long long)(src + 8);
+                    job.slen = varsize - 8u;
+                    job.rawsize = (uint32_t)dep_len[r];
+                    job.dst = (unsigned long long)(out_dep + row_dep_off[r]);
+                }
+            } else if (vcount[v] != 0) {
+                const uint32_t *ptr = row + (a ? RW_DEP : RW_IND);
+                const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
+                if (va_extsize != va_rawsize - 4u) {
+                    const unsigned long long len = a ? dep_len[r] : ind_len[r];
+                    job.err_key = make_err_key(3, vfirst[v], 3, 0, CDS_ERR_PGLZ_CORRUPT);
+                    if (va_extsize < 4u) {
+                        atomicMin(&st->err_key, job.err_key);
+                    } else {
+                        // staged payload = LE rawsize + stream (ppr:574-594 builds header + payload)
+                        job.src = (unsigned long long)(scratch + vscr[v] + 4);
+                        job.slen = va_extsize - 4u;
+                        job.rawsize = (uint32_t)len;
+                        job.dst = a ? (unsigned long long)(out_dep + row_dep_off[r]) : (unsigned long long)(out_ind + row_ind_off[r]);
+                    }
+                }
+            }
+        }
+        jobs[v] = job;
+    }
+}
+
+}  // namespace cds

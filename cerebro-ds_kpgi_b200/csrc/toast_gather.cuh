@@ -1,0 +1,166 @@
+// toast_gather.cuh — the bulk kernel: TOAST chunk payloads -> contiguous values.
+//
+// Replaces the chunk reassembly of detoast (/root/reference/cerebro_gpdb/pg_page_reader.py:577-594:
+// sort by chunk_seq, strip the 4-byte chunk header, b''.join) fused with the typed
+// reinterpretation (pg_page_reader.py:165-182, which is a byte copy), writing straight into the
+// caller's output tensor (uncompressed values) or into the pglz staging area (compressed values).
+//
+// Shape of the work: every 32 KB page is read exactly once and every payload byte written
+// exactly once -> HBM-bound.  Payloads start at page offset = 4 (mod 8) and are 8140 = 12 (mod 16)
+// bytes long, so source and destination are never mutually 16-byte aligned.  Design:
+//   * persistent CTAs, one per SM; a producer warp streams whole pages into a shared-memory ring
+//     with TMA bulk copies (cp.async.bulk ... mbarrier::complete_tx), kStages pages in flight;
+//   * the producer warp also prefetches the page's copy descriptors into shared memory;
+//   * consumer warps realign in shared memory (two aligned LDS.128 + word select) and emit
+//     aligned, coalesced, streaming 16-byte global stores.
+#pragma once
+#include "cds_common.cuh"
+
+namespace cds {
+
+constexpr int kGatherStages = 6;
+constexpr int kGatherConsumerWarps = 16;
+constexpr int kGatherThreads = 32 * (1 + kGatherConsumerWarps);
+constexpr int kGatherMaxStageOps = 48;
+constexpr size_t kGatherSmemBytes =
+    (size_t)kGatherStages * kPage + 16 /* realign over-read pad */ +
+    (size_t)kGatherStages * kGatherMaxStageOps * sizeof(CopyOp) +
+    (size_t)kGatherStages * 2 * sizeof(uint32_t) + (size_t)kGatherStages * 2 * sizeof(unsigned long long) + 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void tma_load_page(void *smem_dst, const void *gsrc, uint32_t bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void st_stream_v4(void *gdst, uint4 v)
+{
+    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(gdst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// Copy `len` bytes from shared `src` to global `dst` with the consumer threads (tid of nth).
+__device__ __forceinline__ void copy_payload(const uint8_t *src, uint8_t *dst, uint32_t len, uint32_t tid, uint32_t nth)
+{
+    const uint32_t sa = smem_u32(src);
+    const uintptr_t da = reinterpret_cast<uintptr_t>(dst);
+    if (((sa | (uint32_t)da) & 3u) != 0) {
+        for (uint32_t i = tid; i < len; i += nth) dst[i] = src[i];          // odd alignment: bytes
+        return;
+    }
+    uint32_t head = (16u - (uint32_t)(da & 15u)) & 15u;                      // bytes up to a 16-byte line
+    if (head > (len & ~3u)) head = len & ~3u;
+    const uint32_t body = (len - head) >> 4;                                 // whole 16-byte stores
+    const uint32_t done = head + (body << 4);
+    if (tid < (head >> 2))
+        *reinterpret_cast<uint32_t *>(dst + 4u * tid) = *reinterpret_cast<const uint32_t *>(src + 4u * tid);
+    const uint8_t *sb = src + head;
+    const uint32_t r = smem_u32(sb) & 15u;                                   // 0, 4, 8 or 12
+    const uint4 *s16 = reinterpret_cast<const uint4 *>(sb - r);
+    uint4 *d16 = reinterpret_cast<uint4 *>(dst + head);
+    if (r == 0) {
+        for (uint32_t j = tid; j < body; j += nth) st_stream_v4(d16 + j, s16[j]);
+    } else {
+        for (uint32_t j = tid; j < body; j += nth) {
+            const uint4 a = s16[j], b = s16[j + 1];
+            uint4 o;
+            if (r == 4)       o = make_uint4(a.y, a.z, a.w, b.x);
+            else if (r == 8)  o = make_uint4(a.z, a.w, b.x, b.y);
+            else              o = make_uint4(a.w, b.x, b.y, b.z);
+            st_stream_v4(d16 + j, o);
+        }
+    }
+    const uint32_t tail_words = (len - done) >> 2;
+    if (tid < tail_words)
+        *reinterpret_cast<uint32_t *>(dst + done + 4u * tid) = *reinterpret_cast<const uint32_t *>(src + done + 4u * tid);
+    const uint32_t rem = done + (tail_words << 2);
+    if (tid < len - rem) dst[rem + tid] = src[rem + tid];
+}
+
+__global__ void __launch_bounds__(kGatherThreads, 1)
+k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32_t *__restrict__ base,
+               const CopyOp *__restrict__ ops)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *stage_buf = smem;
+    CopyOp *stage_ops = reinterpret_cast<CopyOp *>(smem + (size_t)kGatherStages * kPage + 16);
+    uint32_t *stage_g0 = reinterpret_cast<uint32_t *>(stage_ops + kGatherStages * kGatherMaxStageOps);
+    uint32_t *stage_n = stage_g0 + kGatherStages;
+    unsigned long long *full = reinterpret_cast<unsigned long long *>(stage_n + kGatherStages);
+    unsigned long long *empty = full + kGatherStages;
+
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kGatherStages; s++) {
+            mbar_init(&full[s], 2);                       // expect_tx arrival + descriptor arrival
+            mbar_init(&empty[s], kGatherConsumerWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (blockIdx.x >= n_pages) return;
+    const uint32_t my_pages = (n_pages - blockIdx.x + gridDim.x - 1) / gridDim.x;
+
+    if (warp == 0) {
+        // ---- producer: page p of this CTA's strided sequence goes to ring slot it % kStages
+        for (uint32_t it = 0; it < my_pages; it++) {
+            const uint32_t s = it % kGatherStages, round = it / kGatherStages;
+            const uint32_t p = blockIdx.x + it * gridDim.x;
+            if (round > 0) mbar_wait(&empty[s], (round - 1) & 1u);
+            if (lane == 0) {
+                mbar_arrive_expect_tx(&full[s], kPage);
+                tma_load_page(stage_buf + (size_t)s * kPage, pages + (size_t)p * kPage, kPage, &full[s]);
+            }
+            const uint32_t g0 = base[p], n = base[p + 1] - g0;
+            for (uint32_t j = lane; j < n && j < (uint32_t)kGatherMaxStageOps; j += 32)
+                stage_ops[s * kGatherMaxStageOps + j] = ops[g0 + j];
+            if (lane == 0) { stage_g0[s] = g0; stage_n[s] = n; }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full[s]);
+        }
+    } else {
+        // ---- consumers
+        const uint32_t ctid = threadIdx.x - 32, cnth = 32 * kGatherConsumerWarps;
+        for (uint32_t it = 0; it < my_pages; it++) {
+            const uint32_t s = it % kGatherStages, round = it / kGatherStages;
+            mbar_wait(&full[s], round & 1u);
+            const uint32_t n = stage_n[s], g0 = stage_g0[s];
+            const uint8_t *pg = stage_buf + (size_t)s * kPage;
+            for (uint32_t j = 0; j < n; j++) {
+                const CopyOp op = j < (uint32_t)kGatherMaxStageOps ? stage_ops[s * kGatherMaxStageOps + j] : ops[g0 + j];
+                if (op.dst == 0 || op.len == 0) continue;
+                copy_payload(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len, ctid, cnth);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+        }
+    }
+}
+
+}  // namespace cds

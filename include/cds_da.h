@@ -1,0 +1,181 @@
+/*
+ * cds_da.h — C ABI of libcds_da.so: the B200 (sm_100a) Direct-Access reader for Cerebro-DS.
+ *
+ * Every entry point is plain `extern "C"`: pointers, sizes, an `int` status.  No torch types.
+ * Device pointers are raw CUDA device addresses (e.g. tensor.data_ptr()); `stream` is a
+ * cudaStream_t passed as void* (NULL = the legacy default stream).
+ *
+ * Each declaration names the reference code it replaces; paths are relative to
+ * /root/reference/cerebro_gpdb/ ("ppr" = pg_page_reader.py).  The reference's own FFI for this
+ * path is ctypes (ppr:47-57: wrap_function(lib, 'pglz_decompress', None, [c_char_p, c_char_p]));
+ * INTEGRATION.md shows the ctypes stubs a maintainer of the reference would add.
+ */
+#ifndef CDS_DA_H
+#define CDS_DA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CDS_BLCKSZ 32768u               /* ppr:34  BLOCK_SIZE                */
+#define CDS_TOAST_MAX_CHUNK_SIZE 8140u  /* ppr:44  TOAST_MAX_CHUNK_SIZE      */
+#define CDS_ROW_WORDS 16u               /* u32 words per exported heap row   */
+
+/* Status codes.  1..14 are data errors and map one-to-one onto what the reference raises
+ * (the Python shim re-raises the same exception type and message); >=100 are infrastructure. */
+enum cds_status {
+    CDS_OK = 0,
+    CDS_ERR_PARTIAL_PAGE = 1,   /* Exception("FATAL")                               ppr:375-377 */
+    CDS_ERR_ITEMID_ALIGN = 2,   /* Exception("Item identifier length do not match") ppr:262-265 */
+    CDS_ERR_TOAST_SPECIAL = 3,  /* AssertionError("THERE SHALL NOT BE INDICES")     ppr:388-389 */
+    CDS_ERR_TUPLE = 4,          /* struct.error: tuple/chunk does not fit its page  ppr:273,404  */
+    CDS_ERR_RAWSIZE = 5,        /* AssertionError('raw size does not match!')       ppr:539      */
+    CDS_ERR_CHUNK_COUNT = 6,    /* AssertionError (numchunks)                       ppr:572      */
+    CDS_ERR_CHUNK_EXTENDED = 7, /* AssertionError (chunk header is extended)        ppr:580      */
+    CDS_ERR_MAX_CHUNK = 8,      /* Exception("max chunk size error")                ppr:584-586  */
+    CDS_ERR_CHUNK_SIZE = 9,     /* Exception("unexpected chunk size")               ppr:587-591  */
+    CDS_ERR_FINAL_SIZE = 10,    /* AssertionError("final size does not match")      ppr:595-596  */
+    CDS_ERR_PGLZ_CORRUPT = 11,  /* Exception("compressed data is corrupt")          ppr:229-230  */
+    CDS_ERR_SHAPE = 12,         /* ValueError (array size vs. catalog shape)        ppr:167,173  */
+    CDS_ERR_CATALOG_MISS = 13,  /* IndexError (.iloc[0] on an empty frame)          ppr:563-564  */
+    CDS_ERR_MISSING_VALUE = 14, /* a pointer whose value has no chunks (reference: None entry)  */
+    CDS_ERR_CUDA = 100,         /* a CUDA runtime call failed: see cds_last_error()             */
+    CDS_ERR_ARG = 101,          /* bad argument                                                  */
+    CDS_ERR_CAPACITY = 102,     /* rows / chunks / scratch / output larger than the capacity    */
+    CDS_ERR_NO_DEVICE = 103     /* no CUDA device: this library has no CPU path                  */
+};
+
+typedef struct cds_segment cds_segment; /* one per (GPU, segment being decoded); not thread-safe */
+
+typedef struct cds_summary {
+    uint64_t n_rows;        /* heap tuples (packed buffers) seen                            */
+    uint64_t n_positions;   /* entries of the result dict                                   */
+    uint64_t ind_bytes;     /* decoded bytes of all independent_var values                  */
+    uint64_t dep_bytes;     /* decoded bytes of all dependent_var values                    */
+    uint64_t n_chunks;      /* TOAST tuples walked                                          */
+    uint64_t n_inline;      /* rows whose dependent_var is inline-compressed                */
+    uint64_t scratch_bytes; /* staging bytes used by compressed external values             */
+    uint64_t err_where;     /* page / row / chunk index the first error refers to           */
+    uint32_t status;        /* first data error in the reference's processing order, or 0   */
+    uint32_t err_stage;     /* 0 heap scan, 1 TOAST scan, 2 inline rows, 3 external, 4 plan */
+} cds_summary;
+
+/* ---- library ------------------------------------------------------------------------------ */
+int cds_version(void);
+const char *cds_status_str(int status);
+const char *cds_last_error(void);               /* text of the last CUDA failure in this thread */
+int cds_device_count(void);
+
+/* Pinned host memory for page staging (async H2D needs it).  Free with cds_host_free. */
+int cds_host_alloc(void **ptr, uint64_t bytes);
+int cds_host_free(void *ptr);
+
+/* ---- segment handle ------------------------------------------------------------------------
+ * All device memory the decode needs is allocated here, once: capacities are in pages.
+ * max_chunks = 0 -> 6 per TOAST page + 4096.  scratch_bytes = ~0 -> as many bytes as the TOAST
+ * capacity (always enough); 0 -> none (segments with compressed external values are refused).
+ * stage_pages != 0 also allocates device page buffers so that cds_decode_host can be used. */
+int cds_segment_create(cds_segment **out, int device, uint64_t max_heap_pages, uint64_t max_toast_pages,
+                       uint64_t max_chunks, uint64_t scratch_bytes, int stage_pages);
+int cds_segment_destroy(cds_segment *seg);
+
+/* ---- the path, step by step (each enqueues on `stream` and returns; no host sync) ---------- */
+
+/* table_page_read (ppr:451-494): page header (ppr:253-269), ItemId (ppr:285-305), tuple header
+ * (ppr:272-276) and MADlib packed-row parse (ppr:328-351) of `n_pages` heap pages on the device. */
+int cds_heap_scan(cds_segment *seg, const void *d_heap_pages, uint64_t n_pages, void *stream);
+
+/* Alternative to cds_heap_scan for callers that already hold the rows (toast_page_read takes a
+ * df_toast argument, ppr:615): upload `n_rows` rows in the cds_export_rows layout; inline datums
+ * are addressed relative to `d_inline_blob`. */
+int cds_set_rows(cds_segment *seg, const uint32_t *h_rows, uint64_t n_rows, const void *d_inline_blob,
+                 void *stream);
+
+/* read_toast_all_bytes (ppr:497-524) over generator_page(toast=True) (ppr:385-422): physical
+ * tuple walk of `n_pages` TOAST pages, chunk directory, chunk_id -> pointer matching. */
+int cds_toast_scan(cds_segment *seg, const void *d_toast_pages, uint64_t n_pages, void *stream);
+
+/* Bookkeeping half of detoast (ppr:527-612): result order (inline rows in table order, then
+ * external values in first-seen order), decoded sizes, output offsets.  *_sample_bytes may be 0;
+ * when both are set every buffer must hold equally many samples in both values
+ * (run_da_cerebro_standalone.py:43). */
+int cds_plan(cds_segment *seg, uint32_t ind_sample_bytes, uint32_t dep_sample_bytes, void *stream);
+
+/* Data half of detoast: chunk checks (ppr:570-596), chunk gather, pglz decode (ppr:191-231 ==
+ * pg_lzcompress.c:49-143) and the typed reinterpretation (ppr:165-182, a byte copy) straight
+ * into caller-owned device buffers: values back to back in result order. */
+int cds_materialize(cds_segment *seg, void *d_out_ind, uint64_t ind_cap_bytes, void *d_out_dep,
+                    uint64_t dep_cap_bytes, void *stream);
+
+/* Wait for everything enqueued for this segment on `stream` and fetch counts + first error.
+ * Returns summary->status (a data error) or an infrastructure error. */
+int cds_finish(cds_segment *seg, void *stream, cds_summary *summary);
+
+/* ---- the path, whole ------------------------------------------------------------------------ */
+
+/* da.input_fn (da.py:55-58) with pages already in HBM: heap_scan + toast_scan + plan +
+ * materialize.  summary == NULL: enqueue only (call cds_finish later). */
+int cds_decode_device(cds_segment *seg, const void *d_heap_pages, uint64_t n_heap_pages,
+                      const void *d_toast_pages, uint64_t n_toast_pages,
+                      uint32_t ind_sample_bytes, uint32_t dep_sample_bytes,
+                      void *d_out_ind, uint64_t ind_cap_bytes, void *d_out_dep, uint64_t dep_cap_bytes,
+                      void *stream, cds_summary *summary);
+
+/* Same with HOST page buffers (pinned for async copies): H2D over `stream`, then the device
+ * path.  Needs a handle created with stage_pages != 0. */
+int cds_decode_host(cds_segment *seg, const void *h_heap_pages, uint64_t n_heap_pages,
+                    const void *h_toast_pages, uint64_t n_toast_pages,
+                    uint32_t ind_sample_bytes, uint32_t dep_sample_bytes,
+                    void *d_out_ind, uint64_t ind_cap_bytes, void *d_out_dep, uint64_t dep_cap_bytes,
+                    void *stream, cds_summary *summary);
+
+/* ---- results for the Python mirror of the reader interface (synchronous, small) ------------ */
+
+/* df_data / df_toast material (ppr:477-492).  Row = 16 u32: dist_key, buffer_id,
+ * independent_var {header bytes, va_rawsize, va_extsize, va_valueid, va_toastrelid},
+ * dependent_var {same five}, dep_external, inline_off_lo, inline_off_hi, inline_len
+ * (byte offset/length of tupdata[24:] inside the heap buffer, ppr:344). */
+int cds_export_rows(cds_segment *seg, uint32_t *h_rows, uint64_t cap_rows, uint64_t *n_rows, void *stream);
+
+/* Result layout after cds_plan: order[p] = row at dict position p; per ROW byte offset/length of
+ * its values inside the two output buffers.  Arrays hold n_positions / n_rows entries. */
+int cds_export_layout(cds_segment *seg, uint64_t *h_order, uint64_t *h_ind_off, uint64_t *h_dep_off,
+                      uint64_t *h_ind_len, uint64_t *h_dep_len, uint64_t cap_rows, void *stream);
+
+/* Chunk directory after cds_toast_scan, in the reference's yield order (ppr:412-422):
+ * chunk_id, chunk_seq, byte offset of the payload inside the TOAST buffer, payload length. */
+int cds_export_chunks(cds_segment *seg, uint32_t *h_chunk_id, uint32_t *h_chunk_seq, uint64_t *h_payload_off,
+                      uint32_t *h_payload_len, uint64_t cap_chunks, uint64_t *n_chunks, void *stream);
+
+/* ---- pglz on its own ------------------------------------------------------------------------ */
+
+/* Batch pglz_decompress (ppr:191-231, pg_lzcompress.c:49-143) on device buffers: datum i is the
+ * varlena (8-byte header + stream) at d_src + src_off[i], src_off[i+1]-src_off[i] bytes long,
+ * decoded to d_dst + dst_off[i] (dst_off[i+1]-dst_off[i] bytes of room).  h_status[i] receives
+ * CDS_OK or CDS_ERR_PGLZ_CORRUPT.  Offsets are host arrays of n+1 entries.  Synchronous. */
+int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_src_off, void *d_dst,
+                              const uint64_t *h_dst_off, uint64_t n, int32_t *h_status, void *stream);
+
+/* The reference's own symbol and call shape (pg_lzcompress.c:49-50; ctypes binding at ppr:47-49,
+ * destination from ctypes.create_string_buffer(rawsize), ppr:247-248): HOST pointers, no status
+ * (the C reference printf()s on corruption; this prints the same text to stdout).  Runs on the
+ * current CUDA device — there is no CPU decoder in this library. */
+void pglz_decompress(const void *source, char *dest);
+
+/* ---- consumer-side casts (a14) -------------------------------------------------------------- */
+
+/* np.argmax(dependent_var[idx]) (run_pytorchddp_da.py:55): first maximum of each int16 row. */
+int cds_onehot_argmax_i16(const void *d_onehot, uint64_t n_rows, uint32_t classes, void *d_labels_i64,
+                          void *stream);
+/* np.rollaxis(image, 2, 0) per sample + collate (run_pytorchddp_da.py:56-58): NHWC -> NCHW. */
+int cds_nhwc_to_nchw_f32(const void *d_src, uint64_t n, uint32_t hw, uint32_t channels, void *d_dst,
+                         void *stream);
+/* Optional training-buffer dtype (not in the reference; round-to-nearest-even). */
+int cds_f32_to_bf16(const void *d_src, uint64_t n_elems, void *d_dst, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CDS_DA_H */
