@@ -57,6 +57,9 @@ PROTOTYPES = {
                                  ctypes.POINTER(Summary)]),
     "cds_decode_host": (_int, [_vp, _vp, _u64, _vp, _u64, _u32, _u32, _vp, _u64, _vp, _u64, _vp,
                                ctypes.POINTER(Summary)]),
+    "cds_launch_count": (ctypes.c_ulonglong, []),
+    "cds_timing_enable": (_int, [_vp, _u32]),
+    "cds_timing_read": (_int, [_vp, _vp, _u32, _pu32]),
     "cds_export_rows": (_int, [_vp, _vp, _u64, _pu64, _vp]),
     "cds_export_layout": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "cds_export_chunks": (_int, [_vp, _vp, _vp, _vp, _vp, _u64, _pu64, _vp]),

@@ -19,6 +19,8 @@
 using namespace cds;
 
 static thread_local char g_last_error[512] = "";
+static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py reports it)
+#define LAUNCHED(n) (g_launches += (n))
 
 static int cuda_fail(cudaError_t e, const char *what)
 {
@@ -56,6 +58,9 @@ struct cds_segment {
     uint8_t *scratch = nullptr;
     DevState *state = nullptr;
     DevState *h_state = nullptr;   // pinned
+    // optional CUDA-event timing of the gather kernel (cds_timing_enable)
+    cudaEvent_t *ev = nullptr;
+    uint32_t ev_cap = 0, ev_used = 0;
 };
 
 // ---- library -----------------------------------------------------------------------------------
@@ -129,6 +134,10 @@ extern "C" int cds_segment_destroy(cds_segment *s)
                     s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch, s->state};
     for (void *b : bufs) if (b) cudaFree(b);
     if (s->h_state) cudaFreeHost(s->h_state);
+    if (s->ev) {
+        for (uint32_t i = 0; i < 2 * s->ev_cap; i++) cudaEventDestroy(s->ev[i]);
+        free(s->ev);
+    }
     delete s;
     return CDS_OK;
 }
@@ -197,6 +206,7 @@ static int index_values(cds_segment *s, cudaStream_t st)
     CU(cudaMemsetAsync(s->htab, 0xFF, sizeof(unsigned long long) * ((uint64_t)s->hmask + 1), st));
     k_index_values<<<small_grid(s), 256, 0, st>>>(s->rows, s->state, s->htab, s->hmask, s->vfirst, s->vcount, s->vbytes, s->vseq0);
     CU(cudaGetLastError());
+    LAUNCHED(1);
     s->have_rows = true;
     return CDS_OK;
 }
@@ -214,10 +224,12 @@ extern "C" int cds_heap_scan(cds_segment *s, const void *d_heap_pages, uint64_t 
     s->n_heap_pages = n_pages;
     k_page_index<<<1, 1024, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->state, 0, (uint32_t)s->cap_rows);
     CU(cudaGetLastError());
+    LAUNCHED(1);
     if (n_pages) {
         uint32_t grid = (uint32_t)(n_pages < small_grid(s) ? n_pages : small_grid(s));
         k_heap_rows<<<grid, 128, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->rows, s->state);
         CU(cudaGetLastError());
+        LAUNCHED(1);
     }
     return index_values(s, st);
 }
@@ -250,11 +262,13 @@ extern "C" int cds_toast_scan(cds_segment *s, const void *d_toast_pages, uint64_
     s->n_toast_pages = n_pages;
     k_page_index<<<1, 1024, 0, st>>>(s->d_toast, (uint32_t)n_pages, s->toast_base, s->state, 1, (uint32_t)s->cap_chunks);
     CU(cudaGetLastError());
+    LAUNCHED(1);
     if (n_pages) {
         k_toast_walk<<<(uint32_t)((n_pages + 127) / 128), 128, 0, st>>>(
             s->d_toast, (uint32_t)n_pages, s->toast_base, s->htab, s->hmask, s->dir_id, s->dir_loc, s->dir_ref,
             s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state);
         CU(cudaGetLastError());
+        LAUNCHED(1);
     }
     s->have_chunks = true;
     return CDS_OK;
@@ -281,6 +295,7 @@ extern "C" int cds_plan(cds_segment *s, uint32_t ind_sample_bytes, uint32_t dep_
     k_plan_scan2<<<3, 1024, 0, st>>>(s->pos_ind, s->pos_dep, s->vscr, s->state);
     k_row_offsets<<<g, 256, 0, st>>>(s->pos_of_row, s->pos_ind, s->pos_dep, s->row_ind_off, s->row_dep_off, s->state);
     CU(cudaGetLastError());
+    LAUNCHED(6);
     s->have_plan = true;
     return CDS_OK;
 }
@@ -298,14 +313,19 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
     CU(cudaGetLastError());
     if (s->n_toast_pages) {
         uint32_t grid = (uint32_t)(s->n_toast_pages < (uint64_t)s->num_sms ? s->n_toast_pages : (uint64_t)s->num_sms);
+        const bool timed = s->ev && s->ev_used < s->ev_cap;
+        if (timed) CU(cudaEventRecord(s->ev[2 * s->ev_used], st));
         k_toast_gather<<<grid, kGatherThreads, kGatherSmemBytes, st>>>(s->d_toast, (uint32_t)s->n_toast_pages,
                                                                        s->toast_base, s->ops);
         CU(cudaGetLastError());
+        LAUNCHED(1);
+        if (timed) { CU(cudaEventRecord(s->ev[2 * s->ev_used + 1], st)); s->ev_used++; }
     }
     // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
     k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(s->jobs, &s->state->n_rows, 2u, 0u,
                                                                                      nullptr, s->state);
     CU(cudaGetLastError());
+    LAUNCHED(2);
     return CDS_OK;
 }
 
@@ -358,6 +378,42 @@ extern "C" int cds_decode_host(cds_segment *s, const void *h_heap, uint64_t n_he
     CU(cudaMemcpyAsync(s->stage_toast, h_toast, n_toast_pages * (uint64_t)kPage, cudaMemcpyHostToDevice, st));
     return cds_decode_device(s, s->stage_heap, n_heap_pages, s->stage_toast, n_toast_pages, isb, dsb, d_out_ind, ind_cap,
                              d_out_dep, dep_cap, stream, sum);
+}
+
+// ---- measurement hooks ---------------------------------------------------------------------------
+
+extern "C" unsigned long long cds_launch_count(void) { return g_launches; }
+
+extern "C" int cds_timing_enable(cds_segment *s, uint32_t max_samples)
+{
+    if (!s) return CDS_ERR_ARG;
+    CU(cudaSetDevice(s->device));
+    if (s->ev) {
+        for (uint32_t i = 0; i < 2 * s->ev_cap; i++) cudaEventDestroy(s->ev[i]);
+        free(s->ev);
+        s->ev = nullptr;
+    }
+    s->ev_cap = s->ev_used = 0;
+    if (max_samples == 0) return CDS_OK;
+    s->ev = (cudaEvent_t *)calloc(2 * (size_t)max_samples, sizeof(cudaEvent_t));
+    if (!s->ev) return CDS_ERR_ARG;
+    for (uint32_t i = 0; i < 2 * max_samples; i++) CU(cudaEventCreate(&s->ev[i]));
+    s->ev_cap = max_samples;
+    return CDS_OK;
+}
+
+extern "C" int cds_timing_read(cds_segment *s, float *h_ms, uint32_t cap, uint32_t *n)
+{
+    if (!s || !n) return CDS_ERR_ARG;
+    CU(cudaSetDevice(s->device));
+    uint32_t k = s->ev_used < cap ? s->ev_used : cap;
+    for (uint32_t i = 0; i < k; i++) {
+        CU(cudaEventSynchronize(s->ev[2 * i + 1]));
+        CU(cudaEventElapsedTime(&h_ms[i], s->ev[2 * i], s->ev[2 * i + 1]));
+    }
+    *n = k;
+    s->ev_used = 0;
+    return CDS_OK;
 }
 
 // ---- exports for the Python mirror -------------------------------------------------------------
@@ -528,6 +584,7 @@ extern "C" int cds_onehot_argmax_i16(const void *d_onehot, uint64_t n_rows, uint
     k_onehot_argmax_i16<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const int16_t *>(d_onehot), n_rows, classes,
                                                                            static_cast<long long *>(d_labels));
     CU(cudaGetLastError());
+    LAUNCHED(1);
     return CDS_OK;
 }
 
@@ -540,6 +597,7 @@ extern "C" int cds_nhwc_to_nchw_f32(const void *d_src, uint64_t n, uint32_t hw, 
     k_nhwc_to_nchw_f32<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const float *>(d_src), n, hw, ch,
                                                                           static_cast<float *>(d_dst));
     CU(cudaGetLastError());
+    LAUNCHED(1);
     return CDS_OK;
 }
 
@@ -552,5 +610,6 @@ extern "C" int cds_f32_to_bf16(const void *d_src, uint64_t n_elems, void *d_dst,
     k_f32_to_bf16<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const float *>(d_src), n_elems,
                                                                      static_cast<__nv_bfloat16 *>(d_dst));
     CU(cudaGetLastError());
+    LAUNCHED(1);
     return CDS_OK;
 }

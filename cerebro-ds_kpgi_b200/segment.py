@@ -137,6 +137,16 @@ class DeviceSegment:
         _lib.check(rc)
         return s if sync else None
 
+    # ---- measurement ----------------------------------------------------------------------
+    def timing_enable(self, max_samples):
+        _lib.check(self.L.cds_timing_enable(self._h, int(max_samples)))
+
+    def timing_read(self, cap=4096):
+        ms = np.zeros(cap, dtype=np.float32)
+        n = ctypes.c_uint32()
+        _lib.check(self.L.cds_timing_read(self._h, _ptr(ms), cap, ctypes.byref(n)))
+        return ms[:n.value].copy()
+
     # ---- exports --------------------------------------------------------------------------
     def rows(self, stream=None):
         out = np.zeros((self.cap_rows, ROW_WORDS), dtype=np.uint32)
@@ -213,7 +223,7 @@ def pglz_decompress_batch(datums, device=None):
     src_off = np.zeros(n + 1, dtype=np.uint64)
     dst_off = np.zeros(n + 1, dtype=np.uint64)
     for i, d in enumerate(datums):
-        src_off[i + 1] = src_off[i] + ((len(d) + 15) & ~15)
+        src_off[i + 1] = src_off[i] + len(d)            # exact: `avail` bounds the header's length word
         raw = struct.unpack_from("<I", d, 4)[0] if len(d) >= 8 else 0
         dst_off[i + 1] = dst_off[i] + ((raw + 15) & ~15)
     blob = np.zeros(int(src_off[-1]) + 16, dtype=np.uint8)
@@ -223,7 +233,7 @@ def pglz_decompress_batch(datums, device=None):
     with torch.cuda.device(device):
         d_src = torch.from_numpy(blob).cuda()
         d_dst = torch.zeros(int(dst_off[-1]) + 16, dtype=torch.uint8, device="cuda")
-        # slots are padded to 16 bytes; the pad only loosens the `avail` / room bounds
+        # output slots are padded to 16 bytes; the pad only loosens the room bound
         _lib.check(L.cds_pglz_decompress_batch(int(device), _ptr(d_src), _ptr(src_off), _ptr(d_dst), _ptr(dst_off), n,
                                                _ptr(status), _stream_ptr()))
         host = d_dst.cpu().numpy()

@@ -131,6 +131,16 @@ int cds_decode_host(cds_segment *seg, const void *h_heap_pages, uint64_t n_heap_
                     void *d_out_ind, uint64_t ind_cap_bytes, void *d_out_dep, uint64_t dep_cap_bytes,
                     void *stream, cds_summary *summary);
 
+/* ---- measurement hooks (bench.py) ------------------------------------------------------------ */
+
+/* Kernels launched by this library in this process so far. */
+unsigned long long cds_launch_count(void);
+/* Record a CUDA-event pair on the launching stream around the gather kernel of the next
+ * `max_samples` cds_materialize calls (0 disables); cds_timing_read waits for them and returns the
+ * durations in milliseconds, then rearms. */
+int cds_timing_enable(cds_segment *seg, uint32_t max_samples);
+int cds_timing_read(cds_segment *seg, float *h_ms, uint32_t cap, uint32_t *n);
+
 /* ---- results for the Python mirror of the reader interface (synchronous, small) ------------ */
 
 /* df_data / df_toast material (ppr:477-492).  Row = 16 u32: dist_key, buffer_id,
