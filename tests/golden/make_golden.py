@@ -104,6 +104,37 @@ def segment_cases(ref_da):
     save_case("seg_multichunk_shuffled", seg, run_reference(ref_da, seg))
 
 
+def frame_case(ref_reader):
+    """df_data / df_toast of table_page_read (ppr:451-494) and the chunk stream of
+    generator_page(toast=True) (ppr:385-422) for the small mixed segment."""
+    z = np.load(os.path.join(HERE, "seg_small_mixed.npz"))
+    root = tempfile.mkdtemp(prefix="golden_")
+    hp, tp = os.path.join(root, "heap"), os.path.join(root, "toast")
+    open(hp, "wb").write(z["heap"].tobytes())
+    open(tp, "wb").write(z["toast"].tobytes())
+    with contextlib.redirect_stdout(io.StringIO()):
+        df_data, df_toast = ref_reader.table_page_read(hp)
+        chunks = [(a, b, bytes(c)) for a, b, c, _ in ref_reader.generator_page(tp, toast=True)]
+    bytea = [b if b is not None else b"" for b in df_toast["bytea"].values]
+    arrays = {c: df_toast[c].values.astype(np.int64) for c in
+              ("va_rawsize", "va_extsize", "va_valueid", "va_toastrelid", "dist_key", "buffer_id")}
+    arrays["external"] = df_toast["external"].values.astype(np.bool_)
+    arrays["attname"] = np.array([str(x) for x in df_toast["attname"].values])
+    arrays["bytea"] = np.frombuffer(b"".join(bytea), dtype=np.uint8)
+    arrays["bytea_len"] = np.array([len(b) for b in bytea], dtype=np.int64)
+    arrays["data_columns"] = np.array(list(df_data.columns))
+    arrays["toast_columns"] = np.array(list(df_toast.columns))
+    arrays["ind_tuple_headers"] = np.array([list(t[:4]) for t in df_data["independent_var_tuple"].values], dtype=np.int64)
+    arrays["dep_tuple_headers"] = np.array([list(t[:4]) for t in df_data["dependent_var_tuple"].values], dtype=np.int64)
+    arrays["chunk_id"] = np.array([c[0] for c in chunks], dtype=np.int64)
+    arrays["chunk_seq"] = np.array([c[1] for c in chunks], dtype=np.int64)
+    arrays["chunk_len"] = np.array([len(c[2]) for c in chunks], dtype=np.int64)
+    arrays["chunk_data"] = np.frombuffer(b"".join(c[2] for c in chunks), dtype=np.uint8)
+    path = os.path.join(HERE, "frames_small_mixed.npz")
+    np.savez_compressed(path, **arrays)
+    print("frames_small_mixed: %d df_toast rows, %d chunks -> %d KB" % (len(df_toast), len(chunks), os.path.getsize(path) // 1024))
+
+
 def pglz_cases(ref_reader):
     """Known-answer vectors: (varlena incl. 8-byte header) -> bytes, decoded by BOTH reference decoders."""
     import ctypes
@@ -236,5 +267,6 @@ def error_cases(ref_reader, ref_da):
 if __name__ == "__main__":
     ref_reader, ref_da = import_reference()
     segment_cases(ref_da)
+    frame_case(ref_reader)
     pglz_cases(ref_reader)
     error_cases(ref_reader, ref_da)
