@@ -76,4 +76,37 @@ k_f32_to_bf16(const float *__restrict__ src, unsigned long long n, __nv_bfloat16
     }
 }
 
+// Batch assembly for the torch consumer: DADataset.__getitem__ + DataLoader collate
+// (/root/reference/cerebro_gpdb/run_pytorchddp_da.py:51-62, run_pytorchddp.py:397-425) as one kernel:
+//   i = indices[b] % n_samples      (train mode pads the epoch by wrapping, run_pytorchddp_da.py:52-53)
+//   out[b][c][p] = images[i][p][c]  (np.rollaxis(image, 2, 0)), optionally rounded to bf16
+//   out_labels[b] = labels[i]       (np.argmax(dependent_var[idx]), precomputed once per partition)
+// channels == 1 degenerates to a row gather (Criteo features).
+template <typename TOut>
+__global__ void __launch_bounds__(256)
+k_batch_assemble(const float *__restrict__ images, unsigned long long n_samples, uint32_t hw, uint32_t ch,
+                 const long long *__restrict__ labels, const long long *__restrict__ indices, uint32_t batch,
+                 TOut *__restrict__ out, long long *__restrict__ out_labels)
+{
+    const unsigned long long per = (unsigned long long)hw * ch, total = (unsigned long long)batch * per;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (unsigned long long i = tid; i < total; i += stride) {
+        const uint32_t b = (uint32_t)(i / per);
+        const uint32_t rem = (uint32_t)(i - (unsigned long long)b * per);
+        const uint32_t c = rem / hw, p = rem - c * hw;
+        long long s = indices[b] % (long long)n_samples;
+        if (s < 0) s += (long long)n_samples;
+        const float v = images[(unsigned long long)s * per + (unsigned long long)p * ch + c];
+        if constexpr (sizeof(TOut) == 2) out[i] = __float2bfloat16_rn(v); else out[i] = v;
+    }
+    if (labels && out_labels) {
+        for (unsigned long long b = tid; b < batch; b += stride) {
+            long long s = indices[b] % (long long)n_samples;
+            if (s < 0) s += (long long)n_samples;
+            out_labels[b] = labels[s];
+        }
+    }
+}
+
 }  // namespace cds

@@ -14,6 +14,7 @@ constexpr uint32_t kChunkMax = CDS_TOAST_MAX_CHUNK_SIZE;
 constexpr uint32_t kRowWords = CDS_ROW_WORDS;
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr unsigned long long kNoErr = ~0ull;
+constexpr uint32_t kFlagRowOverflow = 1u, kFlagChunkOverflow = 2u;
 
 // row words (cds_export_rows layout)
 enum RowWord : uint32_t {
@@ -24,8 +25,9 @@ enum RowWord : uint32_t {
 };
 
 // Device-resident scalars of one decode; mirrored to pinned host memory by cds_finish.
+// A decode starts from an all-zero state (one cudaMemsetAsync).
 struct DevState {
-    unsigned long long err_key;   // smallest error key seen (see make_err_key); kNoErr = none
+    unsigned long long err_inv;   // ~(smallest error key seen), see make_err_key; 0 = no error
     unsigned long long ind_bytes;
     unsigned long long dep_bytes;
     unsigned long long scratch_bytes;
@@ -33,9 +35,8 @@ struct DevState {
     uint32_t n_chunks;
     uint32_t n_inline;
     uint32_t n_pos;
-    uint32_t ind_sample_bytes;
-    uint32_t dep_sample_bytes;
-    uint32_t pad0, pad1;
+    uint32_t flags;               // kFlagRowOverflow | kFlagChunkOverflow
+    uint32_t pad0, pad1, pad2;
 };
 
 // One TOAST chunk -> one copy.  dst == 0: chunk not referenced (or refused); nothing is copied.
@@ -68,8 +69,9 @@ __host__ __device__ inline unsigned long long make_err_key(uint32_t stage, unsig
 __device__ inline void report(DevState *st, uint32_t stage, unsigned long long primary, uint32_t sub,
                               uint32_t secondary, uint32_t code)
 {
-    atomicMin(&st->err_key, make_err_key(stage, primary, sub, secondary, code));
+    atomicMax(&st->err_inv, ~make_err_key(stage, primary, sub, secondary, code));
 }
+__device__ inline void report_key(DevState *st, unsigned long long key) { atomicMax(&st->err_inv, ~key); }
 
 __device__ inline uint32_t ld_u16(const uint8_t *p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8); }
 __device__ inline uint32_t ld_u32(const uint8_t *p)
@@ -82,7 +84,7 @@ __device__ inline uint32_t ld_u32be(const uint8_t *p) { return __byte_perm(ld_u3
 // valueid -> value index hash table: 64-bit entries, key in the high word, min(value ref) in the low.
 // value ref = (garbage << 31) | (2*row + att); garbage marks the bytes the reference parses as a
 // va_valueid out of an inline datum (ppr:342,516).
-constexpr unsigned long long kEmptySlot = ~0ull;
+constexpr unsigned long long kEmptySlot = 0ull;   // entries are stored +1 so that a zeroed table is empty
 __device__ inline uint32_t hash_u32(uint32_t x)
 {
     x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
@@ -90,7 +92,7 @@ __device__ inline uint32_t hash_u32(uint32_t x)
 }
 __device__ inline void htab_insert(unsigned long long *tab, uint32_t mask, uint32_t key, uint32_t ref)
 {
-    unsigned long long entry = ((unsigned long long)key << 32) | ref;
+    unsigned long long entry = (((unsigned long long)key << 32) | ref) + 1ull;
     uint32_t slot = hash_u32(key) & mask;
     for (;;) {
         unsigned long long cur = tab[slot];
@@ -99,7 +101,7 @@ __device__ inline void htab_insert(unsigned long long *tab, uint32_t mask, uint3
             if (prev == kEmptySlot) return;
             cur = prev;
         }
-        if ((uint32_t)(cur >> 32) == key) { atomicMin(&tab[slot], entry); return; }
+        if ((uint32_t)((cur - 1ull) >> 32) == key) { atomicMin(&tab[slot], entry); return; }
         slot = (slot + 1) & mask;
     }
 }
@@ -109,12 +111,27 @@ __device__ inline uint32_t htab_find(const unsigned long long *tab, uint32_t mas
     for (;;) {
         unsigned long long cur = tab[slot];
         if (cur == kEmptySlot) return kNone;
-        if ((uint32_t)(cur >> 32) == key) return (uint32_t)cur;
+        if ((uint32_t)((cur - 1ull) >> 32) == key) return (uint32_t)(cur - 1ull);
         slot = (slot + 1) & mask;
     }
 }
 
-// ---- block-wide exclusive scan over a long array by ONE block (plans are small) -------------
+// ---- device-wide exclusive scan: single pass, decoupled look-back ---------------------------------
+// Tiles of kScanTile elements are handed out by a ticket counter (so a tile only ever waits for
+// tiles whose blocks are already running); each tile publishes its aggregate, then looks back over
+// its predecessors' aggregates / inclusive prefixes, 32 at a time.  The workspace (ticket + status
+// words) must be zero when the kernel starts; one cudaMemsetAsync per decode clears all of them.
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 16;
+constexpr uint32_t kScanTile = kScanThreads * kScanItems;
+
+struct ScanWs {
+    uint32_t *ticket;             // 1 word, zeroed
+    uint32_t *status;             // per tile: 0 nothing, 1 aggregate published, 2 inclusive prefix published
+    unsigned long long *agg;      // per tile
+    unsigned long long *incl;     // per tile
+};
+
 template <typename T>
 __device__ inline T warp_inclusive_scan(T v)
 {
@@ -126,31 +143,111 @@ __device__ inline T warp_inclusive_scan(T v)
     return v;
 }
 
-// out[i] = sum(in[0..i)), returns the grand total to every thread.  in/out may alias.
-// Needs blockDim.x == 1024 and a __shared__ T[33] scratch.
-template <typename T, typename TIn>
-__device__ inline T block_exclusive_scan(const TIn *in, T *out, uint32_t n, T *sh)
+__device__ inline uint32_t ld_volatile_u32(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
+__device__ inline unsigned long long ld_volatile_u64(const unsigned long long *p)
 {
-    T carry = 0;
+    return *reinterpret_cast<const volatile unsigned long long *>(p);
+}
+
+// out[i] = sum_{j<i} load(j) for i in [0, n); out[n] = total when write_total_at_n.  Every block of
+// the launch must call this (blockDim.x == kScanThreads).  Returns the grand total to the block that
+// processed the last tile (others get 0) through *is_last.
+template <typename T, typename LoadFn>
+__device__ inline T device_exclusive_scan(LoadFn load, T *out, uint32_t n, ScanWs ws, bool write_total_at_n, bool *is_last)
+{
+    __shared__ unsigned long long sh_warp[kScanThreads / 32];
+    __shared__ unsigned long long sh_prefix;
+    __shared__ uint32_t sh_tile;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (uint32_t base = 0; base < n; base += 1024) {
-        uint32_t i = base + threadIdx.x;
-        T v = i < n ? (T)in[i] : (T)0;
-        T inc = warp_inclusive_scan(v);
-        if (lane == 31) sh[warp] = inc;
+    const uint32_t num_tiles = (n + kScanTile - 1) / kScanTile;
+    *is_last = false;
+    T grand = 0;
+    if (n == 0) {
+        if (blockIdx.x == 0 && threadIdx.x == 0 && write_total_at_n) out[0] = 0;
+        *is_last = (blockIdx.x == 0);
+        return 0;
+    }
+    for (;;) {
+        if (threadIdx.x == 0) sh_tile = atomicAdd(ws.ticket, 1u);
         __syncthreads();
+        const uint32_t tile = sh_tile;
+        if (tile >= num_tiles) break;
+        const uint32_t base = tile * kScanTile + threadIdx.x * kScanItems;
+        T v[kScanItems];
+        T tsum = 0;
+#pragma unroll
+        for (int k = 0; k < kScanItems; k++) {
+            const uint32_t i = base + k;
+            v[k] = i < n ? (T)load(i) : (T)0;
+            tsum += v[k];
+        }
+        const T winc = warp_inclusive_scan(tsum);
+        if (lane == 31) sh_warp[warp] = (unsigned long long)winc;
+        __syncthreads();
+        T warp_off = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kScanThreads / 32; w++) {
+            const T x = (T)sh_warp[w];
+            if (w < (int)warp) warp_off += x;
+            total += x;
+        }
         if (warp == 0) {
-            T w = sh[lane];
-            T winc = warp_inclusive_scan(w);
-            sh[lane] = winc - w;
-            if (lane == 31) sh[32] = winc;
+            unsigned long long prefix = 0;
+            if (tile == 0) {
+                if (lane == 0) {
+                    ws.incl[0] = (unsigned long long)total;
+                    __threadfence();
+                    *reinterpret_cast<volatile uint32_t *>(&ws.status[0]) = 2u;
+                }
+            } else {
+                if (lane == 0) {
+                    ws.agg[tile] = (unsigned long long)total;
+                    __threadfence();
+                    *reinterpret_cast<volatile uint32_t *>(&ws.status[tile]) = 1u;
+                }
+                int j = (int)tile - 1;
+                for (;;) {
+                    const int t = j - (int)lane;
+                    uint32_t st = 2u;
+                    unsigned long long val = 0;
+                    if (t >= 0) {
+                        do { st = ld_volatile_u32(&ws.status[t]); } while (st == 0u);
+                        __threadfence();
+                        val = st == 2u ? ld_volatile_u64(&ws.incl[t]) : ld_volatile_u64(&ws.agg[t]);
+                    }
+                    const uint32_t done = __ballot_sync(0xffffffffu, st == 2u);   // lanes past tile 0 count as done
+                    const uint32_t first = (uint32_t)__ffs((int)done) - 1u;       // nearest tile with a full prefix
+                    unsigned long long part = lane <= first ? val : 0ull;
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+                    prefix += part;
+                    if (done) break;
+                    j -= 32;
+                }
+                if (lane == 0) {
+                    ws.incl[tile] = prefix + (unsigned long long)total;
+                    __threadfence();
+                    *reinterpret_cast<volatile uint32_t *>(&ws.status[tile]) = 2u;
+                }
+            }
+            if (lane == 0) sh_prefix = prefix;
         }
         __syncthreads();
-        if (i < n) out[i] = carry + sh[warp] + inc - v;
-        carry += sh[32];
+        T run = (T)sh_prefix + warp_off + (winc - tsum);
+#pragma unroll
+        for (int k = 0; k < kScanItems; k++) {
+            const uint32_t i = base + k;
+            if (i < n) out[i] = run;
+            run += v[k];
+        }
+        if (tile == num_tiles - 1) {
+            grand = (T)sh_prefix + total;
+            *is_last = true;
+            if (write_total_at_n && threadIdx.x == 0) out[n] = grand;
+        }
         __syncthreads();
     }
-    return carry;
+    return grand;
 }
 
 }  // namespace cds

@@ -56,6 +56,11 @@ struct cds_segment {
     CopyOp *ops = nullptr;
     PglzJob *jobs = nullptr;
     uint8_t *scratch = nullptr;
+    // one allocation cleared by ONE memset per decode: [DevState][scan tickets+status][hash table]
+    uint8_t *zero_region = nullptr;
+    uint64_t zero_bytes = 0;
+    unsigned long long *scan_vals = nullptr;   // aggregates / inclusive prefixes of the scans (not cleared)
+    ScanWs ws[7];                               // heap index, TOAST index, inline rank, chunk rank, ind, dep, staging
     DevState *state = nullptr;
     DevState *h_state = nullptr;   // pinned
     // optional CUDA-event timing of the gather kernel (cds_timing_enable)
@@ -128,10 +133,10 @@ extern "C" int cds_segment_destroy(cds_segment *s)
 {
     if (!s) return CDS_OK;
     cudaSetDevice(s->device);
-    void *bufs[] = {s->stage_heap, s->stage_toast, s->heap_base, s->toast_base, s->rows, s->htab, s->dir_id, s->dir_loc,
+    void *bufs[] = {s->stage_heap, s->stage_toast, s->heap_base, s->toast_base, s->rows, s->zero_region, s->scan_vals, s->dir_id, s->dir_loc,
                     s->dir_ref, s->chunk_flag, s->vfirst, s->vcount, s->vseq0, s->vbytes, s->vscr, s->inline_flag,
                     s->row_first, s->pos_of_row, s->row_at_pos, s->ind_len, s->dep_len, s->pos_ind, s->pos_dep,
-                    s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch, s->state};
+                    s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch};
     for (void *b : bufs) if (b) cudaFree(b);
     if (s->h_state) cudaFreeHost(s->h_state);
     if (s->ev) {
@@ -167,11 +172,34 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
     cudaError_t e = cudaSuccess;
 #define A(ptr, n) if (e == cudaSuccess) e = dalloc(&s->ptr, (n))
     A(heap_base, max_heap_pages + 1); A(toast_base, max_toast_pages + 1); A(rows, R * kRowWords);
-    A(htab, hsize); A(dir_id, C); A(dir_loc, C); A(dir_ref, C); A(chunk_flag, C + 1);
+    A(dir_id, C); A(dir_loc, C); A(dir_ref, C); A(chunk_flag, C + 1);
     A(vfirst, V); A(vcount, V); A(vseq0, V); A(vbytes, V); A(vscr, V + 1);
     A(inline_flag, R + 1); A(row_first, R); A(pos_of_row, R); A(row_at_pos, R);
     A(ind_len, R); A(dep_len, R); A(pos_ind, R + 1); A(pos_dep, R + 1); A(row_ind_off, R); A(row_dep_off, R);
-    A(ops, C); A(jobs, V); A(scratch, s->cap_scratch + 16); A(state, 1);
+    A(ops, C); A(jobs, V); A(scratch, s->cap_scratch + 16);
+    {
+        // scans: [0] heap pages, [1] TOAST pages, [2] rows, [3] chunks, [4],[5] positions, [6] values
+        const uint64_t lens[7] = {max_heap_pages, max_toast_pages, R, C, R, R, V};
+        uint64_t tiles[7], total_tiles = 0;
+        for (int i = 0; i < 7; i++) { tiles[i] = lens[i] / kScanTile + 2; total_tiles += tiles[i]; }
+        const uint64_t state_bytes = 256, ws_bytes = ((8 + total_tiles) * 4 + 255) & ~255ull;
+        s->zero_bytes = state_bytes + ws_bytes + hsize * 8;
+        if (e == cudaSuccess) e = dalloc(&s->zero_region, s->zero_bytes);
+        if (e == cudaSuccess) e = dalloc(&s->scan_vals, 2 * total_tiles);
+        if (e == cudaSuccess) {
+            s->state = reinterpret_cast<DevState *>(s->zero_region);
+            uint32_t *w = reinterpret_cast<uint32_t *>(s->zero_region + state_bytes);
+            s->htab = reinterpret_cast<unsigned long long *>(s->zero_region + state_bytes + ws_bytes);
+            uint64_t t0 = 0;
+            for (int i = 0; i < 7; i++) {
+                s->ws[i].ticket = w + i;
+                s->ws[i].status = w + 8 + t0;
+                s->ws[i].agg = s->scan_vals + 2 * t0;
+                s->ws[i].incl = s->scan_vals + 2 * t0 + tiles[i];
+                t0 += tiles[i];
+            }
+        }
+    }
     if (stage_pages) { A(stage_heap, max_heap_pages * (uint64_t)kPage); A(stage_toast, max_toast_pages * (uint64_t)kPage); }
 #undef A
     if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&s->h_state), sizeof(DevState), cudaHostAllocPortable);
@@ -189,25 +217,17 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
 // ---- steps -------------------------------------------------------------------------------------
 
 static inline uint32_t small_grid(const cds_segment *s) { return (uint32_t)s->num_sms * 4u; }
-
-static int reset_state(cds_segment *s, cudaStream_t st)
+static inline uint32_t scan_grid(const cds_segment *s, uint64_t n)
 {
-    DevState init;
-    memset(&init, 0, sizeof(init));
-    init.err_key = kNoErr;
-    *s->h_state = init;
-    CU(cudaMemcpyAsync(s->state, s->h_state, sizeof(DevState), cudaMemcpyHostToDevice, st));
-    s->have_rows = s->have_chunks = s->have_plan = false;
-    return CDS_OK;
+    uint64_t tiles = n / kScanTile + 1, cap = (uint64_t)s->num_sms * 4u;
+    return (uint32_t)(tiles < cap ? tiles : cap);
 }
 
-static int index_values(cds_segment *s, cudaStream_t st)
+// A decode starts from zeros: state, scan tickets/status and the hash table, one memset.
+static int reset_state(cds_segment *s, cudaStream_t st)
 {
-    CU(cudaMemsetAsync(s->htab, 0xFF, sizeof(unsigned long long) * ((uint64_t)s->hmask + 1), st));
-    k_index_values<<<small_grid(s), 256, 0, st>>>(s->rows, s->state, s->htab, s->hmask, s->vfirst, s->vcount, s->vbytes, s->vseq0);
-    CU(cudaGetLastError());
-    LAUNCHED(1);
-    s->have_rows = true;
+    CU(cudaMemsetAsync(s->zero_region, 0, s->zero_bytes, st));
+    s->have_rows = s->have_chunks = s->have_plan = false;
     return CDS_OK;
 }
 
@@ -222,16 +242,19 @@ extern "C" int cds_heap_scan(cds_segment *s, const void *d_heap_pages, uint64_t 
     if (rc) return rc;
     s->d_heap = static_cast<const uint8_t *>(d_heap_pages);
     s->n_heap_pages = n_pages;
-    k_page_index<<<1, 1024, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->state, 0, (uint32_t)s->cap_rows);
+    k_page_index<<<scan_grid(s, n_pages), kScanThreads, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->state, 0,
+                                                                  (uint32_t)s->cap_rows, s->ws[0]);
     CU(cudaGetLastError());
     LAUNCHED(1);
     if (n_pages) {
         uint32_t grid = (uint32_t)(n_pages < small_grid(s) ? n_pages : small_grid(s));
-        k_heap_rows<<<grid, 128, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->rows, s->state);
+        k_heap_rows<<<grid, 128, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->rows, s->state, s->htab, s->hmask,
+                                          s->vfirst, s->vcount, s->vbytes, s->vseq0);
         CU(cudaGetLastError());
         LAUNCHED(1);
     }
-    return index_values(s, st);
+    s->have_rows = true;
+    return CDS_OK;
 }
 
 extern "C" int cds_set_rows(cds_segment *s, const uint32_t *h_rows, uint64_t n_rows, const void *d_inline_blob, void *stream)
@@ -242,25 +265,30 @@ extern "C" int cds_set_rows(cds_segment *s, const uint32_t *h_rows, uint64_t n_r
     CU(cudaSetDevice(s->device));
     int rc = reset_state(s, st);
     if (rc) return rc;
-    s->h_state->n_rows = (uint32_t)n_rows;
-    CU(cudaMemcpyAsync(s->state, s->h_state, sizeof(DevState), cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(s->rows, h_rows, n_rows * kRowWords * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    k_set_n_rows<<<1, 1, 0, st>>>(s->state, (uint32_t)n_rows);
+    if (n_rows) CU(cudaMemcpyAsync(s->rows, h_rows, n_rows * kRowWords * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
     CU(cudaStreamSynchronize(st));   // h_rows is the caller's (pageable) memory
     s->d_heap = static_cast<const uint8_t *>(d_inline_blob);
     s->n_heap_pages = 0;
-    return index_values(s, st);
+    k_index_values<<<small_grid(s), 256, 0, st>>>(s->rows, s->state, s->htab, s->hmask, s->vfirst, s->vcount, s->vbytes, s->vseq0);
+    CU(cudaGetLastError());
+    LAUNCHED(2);
+    s->have_rows = true;
+    return CDS_OK;
 }
 
 extern "C" int cds_toast_scan(cds_segment *s, const void *d_toast_pages, uint64_t n_pages, void *stream)
 {
     if (!s || (!d_toast_pages && n_pages) || !s->have_rows) return CDS_ERR_ARG;
+    if (s->have_chunks) return CDS_ERR_ARG;   // one TOAST scan per heap scan: the scan workspaces are single-use
     if (n_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
     if (reinterpret_cast<uintptr_t>(d_toast_pages) & 15u) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(s->device));
     s->d_toast = static_cast<const uint8_t *>(d_toast_pages);
     s->n_toast_pages = n_pages;
-    k_page_index<<<1, 1024, 0, st>>>(s->d_toast, (uint32_t)n_pages, s->toast_base, s->state, 1, (uint32_t)s->cap_chunks);
+    k_page_index<<<scan_grid(s, n_pages), kScanThreads, 0, st>>>(s->d_toast, (uint32_t)n_pages, s->toast_base, s->state, 1,
+                                                                  (uint32_t)s->cap_chunks, s->ws[1]);
     CU(cudaGetLastError());
     LAUNCHED(1);
     if (n_pages) {
@@ -274,28 +302,23 @@ extern "C" int cds_toast_scan(cds_segment *s, const void *d_toast_pages, uint64_
     return CDS_OK;
 }
 
-__global__ void k_set_sample_bytes(DevState *st, uint32_t isb, uint32_t dsb)
-{
-    st->ind_sample_bytes = isb;
-    st->dep_sample_bytes = dsb;
-}
-
 extern "C" int cds_plan(cds_segment *s, uint32_t ind_sample_bytes, uint32_t dep_sample_bytes, void *stream)
 {
-    if (!s || !s->have_rows || !s->have_chunks) return CDS_ERR_ARG;
+    if (!s || !s->have_rows || !s->have_chunks || s->have_plan) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(s->device));
     const uint32_t g = small_grid(s);
-    k_set_sample_bytes<<<1, 1, 0, st>>>(s->state, ind_sample_bytes, dep_sample_bytes);
     k_plan_rows<<<g, 256, 0, st>>>(s->rows, s->d_toast, s->dir_loc, s->vfirst, s->vcount, s->vseq0, s->inline_flag,
                                    s->chunk_flag, s->row_first, s->ind_len, s->dep_len, s->vscr, s->state);
-    k_plan_scan1<<<2, 1024, 0, st>>>(s->inline_flag, s->chunk_flag, s->state);
+    k_plan_scan1<<<dim3(scan_grid(s, s->cap_chunks), 2), kScanThreads, 0, st>>>(s->inline_flag, s->chunk_flag, s->state,
+                                                                              s->ws[2], s->ws[3]);
     k_assign_pos<<<g, 256, 0, st>>>(s->rows, s->inline_flag, s->chunk_flag, s->row_first, s->ind_len, s->dep_len,
-                                    s->pos_of_row, s->row_at_pos, s->pos_ind, s->pos_dep, s->state);
-    k_plan_scan2<<<3, 1024, 0, st>>>(s->pos_ind, s->pos_dep, s->vscr, s->state);
-    k_row_offsets<<<g, 256, 0, st>>>(s->pos_of_row, s->pos_ind, s->pos_dep, s->row_ind_off, s->row_dep_off, s->state);
+                                    s->pos_of_row, s->row_at_pos, s->pos_ind, s->pos_dep, s->state, ind_sample_bytes,
+                                    dep_sample_bytes);
+    k_plan_scan2<<<dim3(scan_grid(s, 2 * s->cap_rows), 3), kScanThreads, 0, st>>>(s->pos_ind, s->pos_dep, s->vscr, s->state,
+                                                                                s->ws[4], s->ws[5], s->ws[6]);
     CU(cudaGetLastError());
-    LAUNCHED(6);
+    LAUNCHED(4);
     s->have_plan = true;
     return CDS_OK;
 }
@@ -308,7 +331,7 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
     CU(cudaSetDevice(s->device));
     k_resolve<<<small_grid(s), 256, 0, st>>>(
         s->rows, s->d_heap, s->dir_id, s->dir_loc, s->dir_ref, s->vfirst, s->vcount, s->vbytes, s->vscr, s->pos_of_row,
-        s->row_ind_off, s->row_dep_off, s->ind_len, s->dep_len, static_cast<uint8_t *>(d_out_ind), ind_cap,
+        s->pos_ind, s->pos_dep, s->row_ind_off, s->row_dep_off, s->ind_len, s->dep_len, static_cast<uint8_t *>(d_out_ind), ind_cap,
         static_cast<uint8_t *>(d_out_dep), dep_cap, s->scratch, s->cap_scratch, s->ops, s->jobs, s->state);
     CU(cudaGetLastError());
     if (s->n_toast_pages) {
@@ -316,7 +339,7 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
         const bool timed = s->ev && s->ev_used < s->ev_cap;
         if (timed) CU(cudaEventRecord(s->ev[2 * s->ev_used], st));
         k_toast_gather<<<grid, kGatherThreads, kGatherSmemBytes, st>>>(s->d_toast, (uint32_t)s->n_toast_pages,
-                                                                       s->toast_base, s->ops);
+                                                                       s->toast_base, s->ops, s->state);
         CU(cudaGetLastError());
         LAUNCHED(1);
         if (timed) { CU(cudaEventRecord(s->ev[2 * s->ev_used + 1], st)); s->ev_used++; }
@@ -331,7 +354,7 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
 
 static void decode_key(unsigned long long key, cds_summary *sum)
 {
-    if (key == kNoErr) { sum->status = CDS_OK; sum->err_stage = 0; sum->err_where = 0; return; }
+    if (key == kNoErr) { sum->status = CDS_OK; sum->err_stage = 0; sum->err_where = 0; return; }   // err_inv == 0
     sum->status = (uint32_t)(key & 0xFFu);
     sum->err_stage = (uint32_t)(key >> 61);
     sum->err_where = (key >> 28) & 0x1FFFFFFFFull;
@@ -349,7 +372,7 @@ extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
     const DevState &h = *s->h_state;
     local.n_rows = h.n_rows; local.n_positions = h.n_pos; local.ind_bytes = h.ind_bytes; local.dep_bytes = h.dep_bytes;
     local.n_chunks = h.n_chunks; local.n_inline = h.n_inline; local.scratch_bytes = h.scratch_bytes;
-    decode_key(h.err_key, &local);
+    decode_key(~h.err_inv, &local);
     if (sum) *sum = local;
     return (int)local.status;
 }
@@ -609,6 +632,30 @@ extern "C" int cds_f32_to_bf16(const void *d_src, uint64_t n_elems, void *d_dst,
     if (blocks > 148ull * 32) blocks = 148ull * 32;
     k_f32_to_bf16<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const float *>(d_src), n_elems,
                                                                      static_cast<__nv_bfloat16 *>(d_dst));
+    CU(cudaGetLastError());
+    LAUNCHED(1);
+    return CDS_OK;
+}
+
+extern "C" int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint32_t hw, uint32_t ch, const void *d_labels,
+                                  const void *d_indices, uint32_t batch, void *d_out, int out_bf16, void *d_out_labels,
+                                  void *stream)
+{
+    if (batch == 0) return CDS_OK;
+    if (!d_images || !d_indices || !d_out || n_samples == 0 || hw == 0 || ch == 0) return CDS_ERR_ARG;
+    uint64_t total = (uint64_t)batch * hw * ch, blocks = (total + 255) / 256;
+    if (blocks > 148ull * 32) blocks = 148ull * 32;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (out_bf16)
+        k_batch_assemble<__nv_bfloat16><<<(uint32_t)blocks, 256, 0, st>>>(
+            static_cast<const float *>(d_images), n_samples, hw, ch, static_cast<const long long *>(d_labels),
+            static_cast<const long long *>(d_indices), batch, static_cast<__nv_bfloat16 *>(d_out),
+            static_cast<long long *>(d_out_labels));
+    else
+        k_batch_assemble<float><<<(uint32_t)blocks, 256, 0, st>>>(
+            static_cast<const float *>(d_images), n_samples, hw, ch, static_cast<const long long *>(d_labels),
+            static_cast<const long long *>(d_indices), batch, static_cast<float *>(d_out),
+            static_cast<long long *>(d_out_labels));
     CU(cudaGetLastError());
     LAUNCHED(1);
     return CDS_OK;

@@ -15,69 +15,63 @@
 
 namespace cds {
 
-// Shared by the heap and the TOAST relation: item count per page from pd_lower, exclusive scan
-// into base[0..n_pages], validation of the header.  ONE block of 1024 threads.
+// Shared by the heap and the TOAST relation: item count per page from pd_lower, device-wide
+// exclusive scan into base[0..n_pages], validation of the header.
 //   toast != 0 additionally asserts pd_special == BLCKSZ (ppr:388-389).
-__global__ void __launch_bounds__(1024, 1)
+__global__ void __launch_bounds__(kScanThreads)
 k_page_index(const uint8_t *__restrict__ pages, uint32_t n_pages, uint32_t *__restrict__ base,
-             DevState *st, int toast, uint32_t cap_items)
+             DevState *st, int toast, uint32_t cap_items, ScanWs ws)
 {
-    __shared__ uint32_t sh[33];
-    uint32_t carry = 0;
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t stage = toast ? 1u : 0u;
-    for (uint32_t b = 0; b < n_pages; b += 1024) {
-        uint32_t p = b + threadIdx.x;
-        uint32_t cnt = 0;
-        if (p < n_pages) {
-            const uint8_t *pg = pages + (size_t)p * kPage;
-            // pd_lower, pd_upper, pd_special live at bytes 12..17 of the header (ppr:629-638)
-            uint2 w = *reinterpret_cast<const uint2 *>(pg + 8);   // bytes 8..15
-            uint32_t pd_lower = w.y & 0xFFFFu;
-            uint32_t w2 = *reinterpret_cast<const uint32_t *>(pg + 16);
-            uint32_t pd_special = w2 & 0xFFFFu;
-            if (pd_lower < kPageHdr || ((pd_lower - kPageHdr) & 3u)) {
-                report(st, stage, p, 0, 0, CDS_ERR_ITEMID_ALIGN);
-            } else if (pd_lower > kPage) {
-                report(st, stage, p, 0, 1, CDS_ERR_TUPLE);
-            } else if (toast && pd_special != kPage) {
-                report(st, stage, p, 0, 2, CDS_ERR_TOAST_SPECIAL);
-            } else {
-                cnt = (pd_lower - kPageHdr) >> 2;
-            }
-        }
-        uint32_t inc = warp_inclusive_scan(cnt);
-        if (lane == 31) sh[warp] = inc;
-        __syncthreads();
-        if (warp == 0) {
-            uint32_t w = sh[lane];
-            uint32_t winc = warp_inclusive_scan(w);
-            sh[lane] = winc - w;
-            if (lane == 31) sh[32] = winc;
-        }
-        __syncthreads();
-        if (p < n_pages) base[p] = carry + sh[warp] + inc - cnt;
-        carry += sh[32];
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        if (carry > cap_items) {
-            // refuse everything: downstream kernels see zero items
+    auto count_of = [&](uint32_t p) -> uint32_t {
+        const uint8_t *pg = pages + (size_t)p * kPage;
+        // pd_lower, pd_upper, pd_special live at bytes 12..17 of the header (ppr:629-638)
+        const uint4 w = *reinterpret_cast<const uint4 *>(pg + 8);      // bytes 8..23
+        const uint32_t pd_lower = w.y & 0xFFFFu, pd_special = w.z & 0xFFFFu;
+        if (pd_lower < kPageHdr || ((pd_lower - kPageHdr) & 3u)) { report(st, stage, p, 0, 0, CDS_ERR_ITEMID_ALIGN); return 0u; }
+        if (pd_lower > kPage) { report(st, stage, p, 0, 1, CDS_ERR_TUPLE); return 0u; }
+        if (toast && pd_special != kPage) { report(st, stage, p, 0, 2, CDS_ERR_TOAST_SPECIAL); return 0u; }
+        return (pd_lower - kPageHdr) >> 2;
+    };
+    bool last;
+    const uint32_t total = device_exclusive_scan<uint32_t>(count_of, base, n_pages, ws, true, &last);
+    if (last && threadIdx.x == 0) {
+        uint32_t n = total;
+        if (total > cap_items) {
+            // refuse everything: downstream kernels see zero items and skip their pages
             report(st, stage, 0, 0, 0, CDS_ERR_CAPACITY);
-            carry = 0;
-            for (uint32_t p = 0; p < n_pages; p++) base[p] = 0;
+            atomicOr(&st->flags, toast ? kFlagChunkOverflow : kFlagRowOverflow);
+            n = 0;
         }
-        base[n_pages] = carry;
-        if (toast) st->n_chunks = carry; else st->n_rows = carry;
+        if (toast) st->n_chunks = n; else st->n_rows = n;
     }
+}
+
+// Reset the per-value statistics of row r and enter its two va_valueid words into the hash table.
+// value index v = 2*row + (0 independent_var | 1 dependent_var) = the row number in df_toast.
+__device__ inline void index_row_values(const uint32_t *row, uint32_t r, unsigned long long *htab, uint32_t hmask,
+                                        uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0)
+{
+#pragma unroll
+    for (uint32_t a = 0; a < 2; a++) {
+        const uint32_t v = 2 * r + a;
+        vfirst[v] = kNone; vcount[v] = 0; vbytes[v] = 0; vseq0[v] = kNone;
+    }
+    if (row[RW_INLINE_LEN] == kNone) return;
+    htab_insert(htab, hmask, row[RW_IND + 3], 2 * r);                        // always external (ppr:348)
+    // an inline dependent_var still contributes the bytes at its va_valueid position to the
+    // reference's chunk filter (ppr:516); mark it so a hit is reported the way .iloc[0] fails
+    htab_insert(htab, hmask, row[RW_DEP + 3], (row[RW_DEP_EXTERNAL] ? 0u : 0x80000000u) | (2 * r + 1));
 }
 
 // One block per heap page (grid-stride), one thread per ItemId: parse the MADlib packed row and
 // write its 16-word descriptor in table order.
 __global__ void __launch_bounds__(128)
 k_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *__restrict__ base,
-            uint32_t *__restrict__ rows, DevState *st)
+            uint32_t *__restrict__ rows, DevState *st, unsigned long long *htab, uint32_t hmask,
+            uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0)
 {
+    if (st->flags & kFlagRowOverflow) return;
     for (uint32_t p = blockIdx.x; p < n_pages; p += gridDim.x) {
         const uint8_t *pg = heap + (size_t)p * kPage;
         const uint32_t r0 = base[p], n = base[p + 1] - r0;
@@ -95,6 +89,7 @@ k_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *
                 report(st, 0, p, 1, i, CDS_ERR_TUPLE);
                 for (uint32_t k = 0; k < kRowWords; k++) row[k] = 0;
                 row[RW_INLINE_LEN] = kNone;                                  // marks the row unusable
+                index_row_values(row, r0 + i, htab, hmask, vfirst, vcount, vbytes, vseq0);
                 continue;
             }
             const uint8_t *td = pg + lp_off + t_hoff;
@@ -110,32 +105,23 @@ k_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *
             row[RW_INLINE_OFF_LO] = (uint32_t)off;
             row[RW_INLINE_OFF_HI] = (uint32_t)(off >> 32);
             row[RW_INLINE_LEN] = tdlen - 24u;
+            index_row_values(row, r0 + i, htab, hmask, vfirst, vcount, vbytes, vseq0);
         }
     }
 }
 
-// Build the va_valueid -> value hash table from the row descriptors and reset per-value stats.
-// value index v = 2*row + (0 independent_var | 1 dependent_var) = the row number in df_toast.
+// cds_set_rows path: rows arrive from the host; build the hash table from them.
 __global__ void __launch_bounds__(256)
 k_index_values(const uint32_t *__restrict__ rows, const DevState *st, unsigned long long *htab,
                uint32_t hmask, uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes,
                uint32_t *vseq0)
 {
     const uint32_t n_rows = st->n_rows;
-    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
-        const uint32_t *row = rows + (size_t)r * kRowWords;
-#pragma unroll
-        for (uint32_t a = 0; a < 2; a++) {
-            uint32_t v = 2 * r + a;
-            vfirst[v] = kNone; vcount[v] = 0; vbytes[v] = 0; vseq0[v] = kNone;
-        }
-        if (row[RW_INLINE_LEN] == kNone) continue;
-        htab_insert(htab, hmask, row[RW_IND + 3], 2 * r);                    // always external (ppr:348)
-        // an inline dependent_var still contributes the bytes at its va_valueid position to the
-        // reference's chunk filter (ppr:516); mark it so a hit is reported the way .iloc[0] fails
-        htab_insert(htab, hmask, row[RW_DEP + 3], (row[RW_DEP_EXTERNAL] ? 0u : 0x80000000u) | (2 * r + 1));
-    }
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x)
+        index_row_values(rows + (size_t)r * kRowWords, r, htab, hmask, vfirst, vcount, vbytes, vseq0);
 }
+
+__global__ void k_set_n_rows(DevState *st, uint32_t n_rows) { st->n_rows = n_rows; }
 
 // One thread per TOAST page: physical walk upward from pd_upper (ppr:391-414).
 __global__ void __launch_bounds__(128)
@@ -146,7 +132,7 @@ k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t
              uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0, DevState *st)
 {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n_pages) return;
+    if (p >= n_pages || (st->flags & kFlagChunkOverflow)) return;
     const uint8_t *pg = toast + (size_t)p * kPage;
     const uint32_t g0 = base[p], n = base[p + 1] - g0;
     uint32_t lp = ld_u16(pg + 14);                                           // pd_upper
@@ -249,18 +235,18 @@ k_plan_rows(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ toast
     }
 }
 
-// Block 0: rank of inline rows (table order).  Block 1: rank of first-seen chunks.
-__global__ void __launch_bounds__(1024, 1)
-k_plan_scan1(uint32_t *inline_flag, uint32_t *chunk_flag, DevState *st)
+// blockIdx.y == 0: rank of inline rows (table order).  blockIdx.y == 1: rank of first-seen chunks.
+__global__ void __launch_bounds__(kScanThreads)
+k_plan_scan1(uint32_t *inline_flag, uint32_t *chunk_flag, DevState *st, ScanWs ws_rows, ScanWs ws_chunks)
 {
-    __shared__ uint32_t sh[33];
-    if (blockIdx.x == 0) {
-        uint32_t tot = block_exclusive_scan<uint32_t, uint32_t>(inline_flag, inline_flag, st->n_rows, sh);
-        if (threadIdx.x == 0) st->n_inline = tot;
+    bool last;
+    if (blockIdx.y == 0) {
+        const uint32_t tot = device_exclusive_scan<uint32_t>([&](uint32_t i) { return inline_flag[i]; }, inline_flag,
+                                                             st->n_rows, ws_rows, false, &last);
+        if (last && threadIdx.x == 0) st->n_inline = tot;
     } else {
-        uint32_t n = st->n_chunks;
-        uint32_t tot = block_exclusive_scan<uint32_t, uint32_t>(chunk_flag, chunk_flag, n, sh);
-        if (threadIdx.x == 0) chunk_flag[n] = tot;
+        device_exclusive_scan<uint32_t>([&](uint32_t i) { return chunk_flag[i]; }, chunk_flag, st->n_chunks, ws_chunks,
+                                        true, &last);
     }
 }
 
@@ -271,7 +257,8 @@ k_assign_pos(const uint32_t *__restrict__ rows, const uint32_t *__restrict__ inl
              const uint32_t *__restrict__ chunk_rank, const uint32_t *__restrict__ row_first,
              const unsigned long long *__restrict__ ind_len, const unsigned long long *__restrict__ dep_len,
              uint32_t *__restrict__ pos_of_row, uint32_t *__restrict__ row_at_pos,
-             unsigned long long *__restrict__ pos_ind, unsigned long long *__restrict__ pos_dep, DevState *st)
+             unsigned long long *__restrict__ pos_ind, unsigned long long *__restrict__ pos_dep, DevState *st,
+             uint32_t isb, uint32_t dsb)
 {
     const uint32_t n_rows = st->n_rows, n_inline = st->n_inline, n_chunks = st->n_chunks;
     if (blockIdx.x == 0 && threadIdx.x == 0) st->n_pos = n_inline + chunk_rank[n_chunks];
@@ -288,7 +275,6 @@ k_assign_pos(const uint32_t *__restrict__ rows, const uint32_t *__restrict__ inl
         pos_ind[pos] = ind_len[r];
         pos_dep[pos] = dep_len[r];
         if (ind_len[r] == 0 || dep_len[r] == 0) report(st, 4, pos, 0, 0, CDS_ERR_MISSING_VALUE);
-        const uint32_t isb = st->ind_sample_bytes, dsb = st->dep_sample_bytes;
         if (isb && dsb && ind_len[r] && dep_len[r]) {
             if (ind_len[r] % isb || dep_len[r] % dsb || ind_len[r] / isb != dep_len[r] / dsb)
                 report(st, 4, pos, 1, 0, CDS_ERR_SHAPE);
@@ -296,35 +282,25 @@ k_assign_pos(const uint32_t *__restrict__ rows, const uint32_t *__restrict__ inl
     }
 }
 
-// Three independent 64-bit exclusive scans, one block each: output offsets of the two value
-// streams in result order, and staging offsets of compressed external values.
-__global__ void __launch_bounds__(1024, 1)
-k_plan_scan2(unsigned long long *pos_ind, unsigned long long *pos_dep, unsigned long long *vscr, DevState *st)
+// Three independent 64-bit exclusive scans (blockIdx.y): output offsets of the two value streams in
+// result order, and staging offsets of compressed external values.
+__global__ void __launch_bounds__(kScanThreads)
+k_plan_scan2(unsigned long long *pos_ind, unsigned long long *pos_dep, unsigned long long *vscr, DevState *st,
+             ScanWs ws0, ScanWs ws1, ScanWs ws2)
 {
-    __shared__ unsigned long long sh[33];
-    if (blockIdx.x == 0) {
-        unsigned long long t = block_exclusive_scan<unsigned long long, unsigned long long>(pos_ind, pos_ind, st->n_pos, sh);
-        if (threadIdx.x == 0) st->ind_bytes = t;
-    } else if (blockIdx.x == 1) {
-        unsigned long long t = block_exclusive_scan<unsigned long long, unsigned long long>(pos_dep, pos_dep, st->n_pos, sh);
-        if (threadIdx.x == 0) st->dep_bytes = t;
+    bool last;
+    if (blockIdx.y == 0) {
+        const unsigned long long t = device_exclusive_scan<unsigned long long>(
+            [&](uint32_t i) { return pos_ind[i]; }, pos_ind, st->n_pos, ws0, false, &last);
+        if (last && threadIdx.x == 0) st->ind_bytes = t;
+    } else if (blockIdx.y == 1) {
+        const unsigned long long t = device_exclusive_scan<unsigned long long>(
+            [&](uint32_t i) { return pos_dep[i]; }, pos_dep, st->n_pos, ws1, false, &last);
+        if (last && threadIdx.x == 0) st->dep_bytes = t;
     } else {
-        unsigned long long t = block_exclusive_scan<unsigned long long, unsigned long long>(vscr, vscr, 2u * st->n_rows, sh);
-        if (threadIdx.x == 0) st->scratch_bytes = t;
-    }
-}
-
-// Per-row output offsets (exported to the host mirror and used by the decode kernels).
-__global__ void __launch_bounds__(256)
-k_row_offsets(const uint32_t *__restrict__ pos_of_row, const unsigned long long *__restrict__ pos_ind,
-              const unsigned long long *__restrict__ pos_dep, unsigned long long *__restrict__ row_ind_off,
-              unsigned long long *__restrict__ row_dep_off, const DevState *st)
-{
-    const uint32_t n_rows = st->n_rows;
-    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
-        uint32_t pos = pos_of_row[r];
-        row_ind_off[r] = pos == kNone ? ~0ull : pos_ind[pos];
-        row_dep_off[r] = pos == kNone ? ~0ull : pos_dep[pos];
+        const unsigned long long t = device_exclusive_scan<unsigned long long>(
+            [&](uint32_t i) { return vscr[i]; }, vscr, 2u * st->n_rows, ws2, false, &last);
+        if (last && threadIdx.x == 0) st->scratch_bytes = t;
     }
 }
 
@@ -336,7 +312,8 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
           const uint32_t *__restrict__ vfirst, const uint32_t *__restrict__ vcount,
           const unsigned long long *__restrict__ vbytes, const unsigned long long *__restrict__ vscr,
           const uint32_t *__restrict__ pos_of_row,
-          const unsigned long long *__restrict__ row_ind_off, const unsigned long long *__restrict__ row_dep_off,
+          const unsigned long long *__restrict__ pos_ind, const unsigned long long *__restrict__ pos_dep,
+          unsigned long long *__restrict__ row_ind_off, unsigned long long *__restrict__ row_dep_off,
           const unsigned long long *__restrict__ ind_len, const unsigned long long *__restrict__ dep_len,
           uint8_t *out_ind, unsigned long long cap_ind, uint8_t *out_dep, unsigned long long cap_dep,
           uint8_t *scratch, unsigned long long cap_scratch,
@@ -373,8 +350,9 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
             if (ok && vbytes[v] == va_extsize && fits && pos_of_row[r] != kNone) {
                 const bool compressed = va_extsize != va_rawsize - 4u;
                 unsigned long long dst;
+                const uint32_t pos = pos_of_row[r];
                 if (compressed) dst = (unsigned long long)(scratch + vscr[v]);
-                else dst = a ? (unsigned long long)(out_dep + row_dep_off[r]) : (unsigned long long)(out_ind + row_ind_off[r]);
+                else dst = a ? (unsigned long long)(out_dep + pos_dep[pos]) : (unsigned long long)(out_ind + pos_ind[pos]);
                 op.dst = dst + (unsigned long long)idx * kChunkMax;
                 op.src_off = loc.y & 0xFFFFu;
                 op.len = size;
@@ -389,6 +367,9 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
         const uint32_t r = v >> 1, a = v & 1u;
         const uint32_t *row = rows + (size_t)r * kRowWords;
         const uint32_t pos = pos_of_row[r];
+        const unsigned long long my_ind_off = pos == kNone ? ~0ull : pos_ind[pos];
+        const unsigned long long my_dep_off = pos == kNone ? ~0ull : pos_dep[pos];
+        if (a == 0) { row_ind_off[r] = my_ind_off; row_dep_off[r] = my_dep_off; }   // exported to the host mirror
         if (fits && pos != kNone && row[RW_INLINE_LEN] != kNone) {
             if (a == 1 && row[RW_DEP_EXTERNAL] == 0) {
                 // inline datum: tupdata[24:] starts with the 8-byte PGLZ header (ppr:344, 537-543)
@@ -397,12 +378,12 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
                 const uint32_t varsize = ld_u32be(src) & 0x3FFFFFFFu;
                 job.err_key = make_err_key(2, r, 0, 0, CDS_ERR_PGLZ_CORRUPT);
                 if (avail < 8u || varsize < 8u || varsize > avail) {
-                    atomicMin(&st->err_key, job.err_key);
+                    report_key(st, job.err_key);
                 } else {
                     job.src = (unsigned long long)(src + 8);
                     job.slen = varsize - 8u;
                     job.rawsize = (uint32_t)dep_len[r];
-                    job.dst = (unsigned long long)(out_dep + row_dep_off[r]);
+                    job.dst = (unsigned long long)(out_dep + my_dep_off);
                 }
             } else if (vcount[v] != 0) {
                 const uint32_t *ptr = row + (a ? RW_DEP : RW_IND);
@@ -411,13 +392,13 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
                     const unsigned long long len = a ? dep_len[r] : ind_len[r];
                     job.err_key = make_err_key(3, vfirst[v], 3, 0, CDS_ERR_PGLZ_CORRUPT);
                     if (va_extsize < 4u) {
-                        atomicMin(&st->err_key, job.err_key);
+                        report_key(st, job.err_key);
                     } else {
                         // staged payload = LE rawsize + stream (ppr:574-594 builds header + payload)
                         job.src = (unsigned long long)(scratch + vscr[v] + 4);
                         job.slen = va_extsize - 4u;
                         job.rawsize = (uint32_t)len;
-                        job.dst = a ? (unsigned long long)(out_dep + row_dep_off[r]) : (unsigned long long)(out_ind + row_ind_off[r]);
+                        job.dst = a ? (unsigned long long)(out_dep + my_dep_off) : (unsigned long long)(out_ind + my_ind_off);
                     }
                 }
             }

@@ -173,7 +173,7 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const uint32_t *n_jobs_dev, uint
                                          reinterpret_cast<uint8_t *>(job.dst), job.rawsize, ring);
         if (lane == 0) {
             if (status) status[j] = ok ? CDS_OK : CDS_ERR_PGLZ_CORRUPT;
-            if (!ok && st && job.err_key) atomicMin(&st->err_key, job.err_key);
+            if (!ok && st && job.err_key) report_key(st, job.err_key);
         }
         __syncwarp();
     }

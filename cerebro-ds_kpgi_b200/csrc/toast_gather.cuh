@@ -105,7 +105,7 @@ __device__ __forceinline__ void copy_payload(const uint8_t *src, uint8_t *dst, u
 
 __global__ void __launch_bounds__(kGatherThreads, 1)
 k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32_t *__restrict__ base,
-               const CopyOp *__restrict__ ops)
+               const CopyOp *__restrict__ ops, const DevState *__restrict__ st)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *stage_buf = smem;
@@ -124,7 +124,7 @@ k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (blockIdx.x >= n_pages) return;
+    if (blockIdx.x >= n_pages || (st->flags & kFlagChunkOverflow)) return;   // no directory: nothing to copy
     const uint32_t my_pages = (n_pages - blockIdx.x + gridDim.x - 1) / gridDim.x;
 
     if (warp == 0) {

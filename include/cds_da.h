@@ -185,6 +185,14 @@ int cds_nhwc_to_nchw_f32(const void *d_src, uint64_t n, uint32_t hw, uint32_t ch
 /* Optional training-buffer dtype (not in the reference; round-to-nearest-even). */
 int cds_f32_to_bf16(const void *d_src, uint64_t n_elems, void *d_dst, void *stream);
 
+/* DADataset.__getitem__ + DataLoader collate (run_pytorchddp_da.py:51-62, run_pytorchddp.py:397-425)
+ * as one launch: sample i = indices[b] mod n_samples (the train-mode epoch padding of
+ * run_pytorchddp_da.py:52-53), out[b] = NCHW view of images[i] (f32, or bf16 when out_bf16 != 0),
+ * out_labels[b] = labels[i].  d_labels / d_out_labels may be NULL.  indices: int64 on the device. */
+int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint32_t hw, uint32_t channels,
+                       const void *d_labels, const void *d_indices, uint32_t batch, void *d_out, int out_bf16,
+                       void *d_out_labels, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
