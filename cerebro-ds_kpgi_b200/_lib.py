@@ -64,6 +64,7 @@ PROTOTYPES = {
     "cds_export_layout": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "cds_export_chunks": (_int, [_vp, _vp, _vp, _vp, _vp, _u64, _pu64, _vp]),
     "cds_pglz_decompress_batch": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp]),
+    "cds_pglz_decompress_batch_static": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "pglz_decompress": (None, [ctypes.c_char_p, ctypes.c_char_p]),
     "cds_onehot_argmax_i16": (_int, [_vp, _u64, _u32, _vp, _vp]),
     "cds_nhwc_to_nchw_f32": (_int, [_vp, _u64, _u32, _u32, _vp, _vp]),

@@ -565,6 +565,121 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
     return CDS_OK;
 }
 
+// ---- pglz batch for callers that must not allocate ---------------------------------------------
+//
+// Some hosts of this library cannot call cudaMalloc on the decode path: a data-loader thread that
+// runs while a training framework owns the whole device memory pool, a latency-sensitive ingest
+// loop, or a process under a fixed memory budget where an allocation may fail (or synchronise the
+// device) at an arbitrary moment.
+// cds_pglz_decompress_batch needs two work arrays (job descriptors, status words) and gets them
+// from cudaMalloc on every call.  The variant below keeps its work area in a fixed array that is
+// part of the loaded module instead, so it never asks the CUDA allocator for anything.
+struct StaticScratch {
+    DevState state;                          // first-error word; must be zero when a call starts
+    PglzJob jobs[CDS_STATIC_MAX_DATUMS];     // rewritten for [0, n) by every call
+};
+// One copy of this array exists on every GPU that loads the library, from load until exit
+// (about 128 KB).  On the host side the NAME below is only a handle for the runtime: it is not a
+// device address and must never be handed to a kernel.  static_scratch_for() asks the runtime for
+// the real address, per device.
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+static std::mutex g_static_mu;
+static void *g_static_addr[64] = {nullptr};
+
+// Device address of g_static_scratch on `device` (which must be the current device).  The first call
+// for a device performs the look-up; later calls return the cached address.
+static int static_scratch_for(int device, StaticScratch **out)
+{
+    if (device < 0 || device >= 64) return CDS_ERR_ARG;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_addr[device]) {
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_scratch)");
+        if (!ptr) return CDS_ERR_CUDA;
+        g_static_addr[device] = ptr;
+    }
+    *out = static_cast<StaticScratch *>(g_static_addr[device]);
+    return CDS_OK;
+}
+
+// One thread per datum: read the 8-byte header on the device and fill the job slot.
+__global__ void __launch_bounds__(256)
+k_build_pglz_jobs(const uint8_t *__restrict__ src, const unsigned long long *__restrict__ src_off, uint8_t *dst,
+                  const unsigned long long *__restrict__ dst_off, uint32_t n, PglzJob *__restrict__ jobs,
+                  int32_t *__restrict__ status, DevState *st)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        PglzJob j;
+        j.src = 0; j.dst = 0; j.slen = kNone; j.rawsize = 0;
+        j.err_key = make_err_key(2, i, 0, 0, CDS_ERR_PGLZ_CORRUPT);
+        const unsigned long long avail = src_off[i + 1] - src_off[i], room = dst_off[i + 1] - dst_off[i];
+        int32_t stat = CDS_ERR_PGLZ_CORRUPT;
+        if (avail >= 8) {
+            const uint8_t *h = src + src_off[i];
+            const uint32_t varsize = ld_u32be(h) & 0x3FFFFFFFu, rawsize = ld_u32(h + 4);
+            if (varsize >= 8 && varsize <= avail && rawsize <= room) {
+                j.src = (unsigned long long)(h + 8);
+                j.dst = (unsigned long long)(dst + dst_off[i]);
+                j.slen = varsize - 8;
+                j.rawsize = rawsize;
+                stat = CDS_OK;
+            }
+        }
+        if (stat != CDS_OK) report_key(st, j.err_key);
+        status[i] = stat;
+        jobs[i] = j;
+    }
+}
+
+__global__ void k_publish_first_corrupt(const DevState *st, long long *first_corrupt)
+{
+    const unsigned long long key = ~st->err_inv;
+    *first_corrupt = st->err_inv == 0 ? -1ll : (long long)((key >> 28) & 0x1FFFFFFFFull);
+}
+
+extern "C" int cds_pglz_decompress_batch_static(int device, const void *d_src, const uint64_t *d_src_off, void *d_dst,
+                                                const uint64_t *d_dst_off, uint64_t n, int32_t *d_status,
+                                                int64_t *d_first_corrupt, void *stream)
+{
+    if (!d_src || !d_src_off || !d_dst || !d_dst_off || !d_status) return CDS_ERR_ARG;
+    if (n > CDS_STATIC_MAX_DATUMS) {
+        snprintf(g_last_error, sizeof(g_last_error),
+                 "cds_pglz_decompress_batch_static: %llu datums requested, the built-in work area holds at most %u "
+                 "(CDS_STATIC_MAX_DATUMS); split the batch or use cds_pglz_decompress_batch",
+                 (unsigned long long)n, (unsigned)CDS_STATIC_MAX_DATUMS);
+        return CDS_ERR_CAPACITY;
+    }
+    if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(device));
+    StaticScratch *sc = nullptr;
+    int rc = static_scratch_for(device, &sc);
+    if (rc != CDS_OK) return rc;
+    // The work area still holds whatever the previous call left: the error word is the only part that is
+    // accumulated into (atomicMax), so it is the only part that has to be cleared.
+    CU(cudaMemsetAsync(&sc->state, 0, sizeof(DevState), st));
+    if (n) {
+        k_build_pglz_jobs<<<(uint32_t)((n + 255) / 256), 256, 0, st>>>(
+            static_cast<const uint8_t *>(d_src), reinterpret_cast<const unsigned long long *>(d_src_off),
+            static_cast<uint8_t *>(d_dst), reinterpret_cast<const unsigned long long *>(d_dst_off), (uint32_t)n, sc->jobs,
+            d_status, &sc->state);
+        CU(cudaGetLastError());
+        uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
+        if (grid > 148u * 7u) grid = 148u * 7u;
+        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(sc->jobs, nullptr, 0u, (uint32_t)n, d_status, &sc->state);
+        CU(cudaGetLastError());
+        LAUNCHED(2);
+    }
+    if (d_first_corrupt) {
+        k_publish_first_corrupt<<<1, 1, 0, st>>>(&sc->state, reinterpret_cast<long long *>(d_first_corrupt));
+        CU(cudaGetLastError());
+        LAUNCHED(1);
+    }
+    return CDS_OK;
+}
+
 extern "C" void pglz_decompress(const void *source, char *dest)
 {
     // Same contract as pg_lzcompress.c:49-50: the caller sized `dest` from the rawsize field.

@@ -168,6 +168,26 @@ int cds_export_chunks(cds_segment *seg, uint32_t *h_chunk_id, uint32_t *h_chunk_
 int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_src_off, void *d_dst,
                               const uint64_t *h_dst_off, uint64_t n, int32_t *h_status, void *stream);
 
+/* No counterpart in the reference.  cds_pglz_decompress_batch for callers that are not allowed to
+ * allocate device memory while they decode — a loader thread beside a framework that has claimed the
+ * whole GPU memory pool, a latency-sensitive ingest loop in which an allocation could stall the device,
+ * a process with a hard memory budget.  Same decoding, same per-datum status, but every pointer is a DEVICE pointer the
+ * caller already owns (offsets are uint64[n+1] on the device; d_status int32[n]; d_first_corrupt, if
+ * not NULL, receives the index of the first corrupt datum or -1) and the work area is an array built
+ * into the library (one copy, ~128 KB, on every GPU that loads it, held until the process exits).
+ * Limits and rules:
+ *   - at most CDS_STATIC_MAX_DATUMS datums per call; more is refused with CDS_ERR_CAPACITY and a
+ *     message in cds_last_error();
+ *   - the call only enqueues work on `stream` (memset + kernels) and never calls cudaMalloc/cudaFree;
+ *   - the first call on a device looks up the work area's address (cudaGetSymbolAddress, with that
+ *     device current): make that first call outside any stream capture;
+ *   - all calls on a device share the one work area: two calls whose kernels can overlap on the GPU
+ *     (different streams, no dependency) race with each other — serialise them. */
+#define CDS_STATIC_MAX_DATUMS 4096u
+int cds_pglz_decompress_batch_static(int device, const void *d_src, const uint64_t *d_src_off, void *d_dst,
+                                     const uint64_t *d_dst_off, uint64_t n, int32_t *d_status,
+                                     int64_t *d_first_corrupt, void *stream);
+
 /* The reference's own symbol and call shape (pg_lzcompress.c:49-50; ctypes binding at ppr:47-49,
  * destination from ctypes.create_string_buffer(rawsize), ppr:247-248): HOST pointers, no status
  * (the C reference printf()s on corruption; this prints the same text to stdout).  Runs on the
