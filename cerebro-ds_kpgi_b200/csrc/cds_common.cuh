@@ -36,7 +36,8 @@ struct DevState {
     uint32_t n_inline;
     uint32_t n_pos;
     uint32_t flags;               // kFlagRowOverflow | kFlagChunkOverflow
-    uint32_t pad0, pad1, pad2;
+    uint32_t pglz_ticket;         // work counter of k_pglz_decode
+    uint32_t pad0, pad1;
 };
 
 // One TOAST chunk -> one copy.  dst == 0: chunk not referenced (or refused); nothing is copied.

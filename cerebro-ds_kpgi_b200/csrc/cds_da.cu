@@ -345,8 +345,8 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
         if (timed) { CU(cudaEventRecord(s->ev[2 * s->ev_used + 1], st)); s->ev_used++; }
     }
     // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
-    k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(s->jobs, &s->state->n_rows, 2u, 0u,
-                                                                                     nullptr, s->state);
+    k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
+        s->jobs, &s->state->n_rows, 2u, 0u, nullptr, s->state, &s->state->pglz_ticket, 1);
     CU(cudaGetLastError());
     LAUNCHED(2);
     return CDS_OK;
@@ -545,14 +545,16 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
     PglzJob *d_jobs = nullptr;
     int32_t *d_stat = nullptr;
     if (e == cudaSuccess) e = dalloc(&d_jobs, n);
-    if (e == cudaSuccess) e = dalloc(&d_stat, n);
+    if (e == cudaSuccess) e = dalloc(&d_stat, n + 1);                       // + the work counter
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_stat + n, 0, sizeof(int32_t), st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_jobs, h_jobs, sizeof(PglzJob) * n, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_stat, h_stat, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
     if (e == cudaSuccess) {
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > 148u * 7u) grid = 148u * 7u;
-        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, 0u, (uint32_t)n, d_stat, nullptr);
+        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, 0u, (uint32_t)n, d_stat, nullptr,
+                                                                     reinterpret_cast<uint32_t *>(d_stat + n), 0);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaMemcpyAsync(h_stat, d_stat, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
@@ -668,7 +670,8 @@ extern "C" int cds_pglz_decompress_batch_static(int device, const void *d_src, c
         CU(cudaGetLastError());
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > 148u * 7u) grid = 148u * 7u;
-        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(sc->jobs, nullptr, 0u, (uint32_t)n, d_status, &sc->state);
+        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(sc->jobs, nullptr, 0u, (uint32_t)n, d_status, &sc->state,
+                                                                     &sc->state.pglz_ticket, 0);
         CU(cudaGetLastError());
         LAUNCHED(2);
     }

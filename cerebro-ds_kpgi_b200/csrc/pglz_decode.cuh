@@ -7,14 +7,18 @@
 // bytes), so parallelism comes from many datums: one warp owns one datum.
 //   * The warp keeps the last 8 KB of output in a shared-memory ring; matches are served from it
 //     (never from global memory), and finished bytes leave for HBM as aligned 16-byte stores.
-//   * A control group (1 control byte + up to 8 items, <= 25 source bytes) is fetched with one
-//     coalesced 32-byte read: lane l holds source byte sp+l.  `__ballot_sync` of
-//     "(byte & 0x0F) == 0x0F" tells every lane where 3-byte tags are, so the item walk of the
-//     group is register-only and identical in all lanes.
+//   * The source stream is read through a register window: every lane holds one aligned 32-bit
+//     word of the current and of the next 128 bytes (coalesced 128-byte loads, the next window is
+//     requested a whole window ahead of its use), so fetching a control group is two shuffles, not
+//     a dependent global load.  Lane l then holds source byte sp+l (a group is <= 25 bytes);
+//     `__ballot_sync` of "(byte & 0x0F) == 0x0F" tells every lane where 3-byte tags are, so the
+//     item walk of the group is register-only and identical in all lanes.
 //   * Literal runs are written by the lanes that already hold those bytes; a match of length L
 //     is expanded by min(L,32) lanes at a time (overlapping matches read modulo the offset).
 //   * Streaks of all-literal groups (control byte 0: incompressible data) are found with one
-//     ballot over the next 32 candidate control bytes and copied 256 bytes at a time.
+//     ballot over the next 32 candidate control bytes and copied 256 bytes at a time, with the
+//     loads of the following 288 source bytes already in flight.
+//   * Datums are handed to warps through a ticket counter, large values first.
 //
 // Corruption semantics follow the reference: the datum is corrupt unless decoding ends with
 // dp == destend and sp == srcend (ppr:229-230).  Additionally reported as corrupt (the reference
@@ -44,10 +48,58 @@ __device__ __forceinline__ void pglz_flush(const uint8_t *ring, uint8_t *dst, ui
     for (uint32_t j = lane; j < nvec; j += 32) {
         const uint32_t pos = b0 + (j << 4);
         const uint4 v = *reinterpret_cast<const uint4 *>(ring + ((pos + shift) & (kRing - 1)));
-        *reinterpret_cast<uint4 *>(dst + pos) = v;
+        __stcs(reinterpret_cast<uint4 *>(dst + pos), v);
     }
     const uint32_t t0 = b0 + (nvec << 4);
     if (lane < to - t0) dst[t0 + lane] = ring[(t0 + lane + shift) & (kRing - 1)];
+}
+
+// Register window over the source stream.  The stream is addressed in the word-aligned frame
+// y = offset + (src & 3); window k covers y in [128k, 128k + 128); lane l holds word 32k + l.
+struct SrcWindow {
+    const uint32_t *wp;   // src rounded down to 4 bytes
+    uint32_t mis;         // src & 3
+    uint32_t nwords;      // words holding at least one stream byte
+    uint32_t k;           // window held in `cur`
+    uint32_t cur, nxt;
+};
+
+__device__ __forceinline__ uint32_t win_word(const SrcWindow &w, uint32_t idx)
+{
+    return idx < w.nwords ? __ldg(w.wp + idx) : 0u;
+}
+__device__ __forceinline__ void win_seek(SrcWindow &w, uint32_t sp, uint32_t lane)
+{
+    w.k = (sp + w.mis) >> 7;
+    w.cur = win_word(w, 32u * w.k + lane);
+    w.nxt = win_word(w, 32u * (w.k + 1u) + lane);
+}
+// Source byte sp + lane (garbage past the end of the stream: callers mask with slen).
+__device__ __forceinline__ uint32_t win_fetch(SrcWindow &w, uint32_t sp, uint32_t lane)
+{
+    const uint32_t y = sp + w.mis, kk = y >> 7;
+    if (kk != w.k) {
+        if (kk == w.k + 1u) {
+            w.cur = w.nxt;
+            w.k = kk;
+            w.nxt = win_word(w, 32u * (kk + 1u) + lane);      // needed 128 source bytes from now
+        } else {
+            win_seek(w, sp, lane);
+        }
+    }
+    const uint32_t rel = (y & 127u) + lane;                      // < 160
+    const uint32_t a = __shfl_sync(0xffffffffu, w.cur, (rel >> 2) & 31u);
+    const uint32_t b = __shfl_sync(0xffffffffu, w.nxt, (rel >> 2) & 31u);
+    return ((rel < 128u ? a : b) >> ((rel & 3u) * 8u)) & 0xFFu;
+}
+
+// The three aligned words that cover the 9 source bytes of the group at sp + 9*lane.
+__device__ __forceinline__ void lit_load(const SrcWindow &w, uint32_t sp, uint32_t lane, uint32_t &w0, uint32_t &w1, uint32_t &w2)
+{
+    const uint32_t i0 = (sp + w.mis + 9u * lane) >> 2;
+    w0 = win_word(w, i0);
+    w1 = win_word(w, i0 + 1u);
+    w2 = win_word(w, i0 + 2u);
 }
 
 // Decode one datum with the calling warp.  Returns true when the stream is well-formed.
@@ -59,21 +111,47 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
     uint32_t sp = 0, dp = 0, flushed = 0;
     bool corrupt = false;
 
+    SrcWindow win;
+    win.mis = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
+    win.wp = reinterpret_cast<const uint32_t *>(src - win.mis);
+    win.nwords = (slen + win.mis + 3u) >> 2;
+    win_seek(win, 0, lane);
+
     while (sp < slen && dp < rawsize && !corrupt) {
-        // ---- streak of all-literal groups: candidate control bytes at sp + 9*lane -------------
-        {
-            const uint32_t cpos = sp + 9u * lane;
-            const bool zero_full = (cpos + 9u <= slen) && (src[cpos] == 0);
-            const uint32_t m = __ballot_sync(0xffffffffu, zero_full);
-            uint32_t streak = (m == 0xffffffffu) ? 32u : (uint32_t)(__ffs(~m) - 1);
-            const uint32_t room = (rawsize - dp) >> 3;                       // whole groups that still fit
-            if (streak > room) streak = room;
-            if (streak >= 2) {
+        // ---- one control group: lane l holds source byte sp + l ----------------------------
+        const uint32_t fetched = win_fetch(win, sp, lane);
+        const bool inb = sp + lane < slen;
+        const uint32_t byte = inb ? fetched : 0u;
+        const uint32_t ctrl = __shfl_sync(0xffffffffu, byte, 0);
+        const uint32_t zmask = __ballot_sync(0xffffffffu, inb && byte == 0u);
+
+        // ---- streak of all-literal groups (control byte 0, 8 literals, 9 source bytes each) ----
+        if ((zmask & 0x00040201u) == 0x00040201u && sp + 27u <= slen && rawsize - dp >= 24u) {
+            uint32_t w0, w1, w2;
+            lit_load(win, sp, lane, w0, w1, w2);
+            for (;;) {
+                uint32_t n0, n1, n2;
+                lit_load(win, sp + 288u, lane, n0, n1, n2);                 // speculative: the streak goes on
+                const uint32_t y0 = sp + win.mis + 9u * lane, sh = (y0 & 3u) * 8u;
+                const bool full = sp + 9u * lane + 9u <= slen;
+                const uint32_t m = __ballot_sync(0xffffffffu, full && ((w0 >> sh) & 0xFFu) == 0u);
+                uint32_t streak = (m == 0xffffffffu) ? 32u : (uint32_t)(__ffs((int)~m) - 1);
+                const uint32_t room = (rawsize - dp) >> 3;                   // whole groups that still fit
+                if (streak > room) streak = room;
                 if (lane < streak) {
-                    const uint8_t *s = src + cpos + 1;
+                    const uint32_t lo = (uint32_t)(((((unsigned long long)w1) << 32) | w0) >> (sh + 8u));
+                    const uint32_t hi = (uint32_t)(((((unsigned long long)w2) << 32) | w1) >> (sh + 8u));
                     const uint32_t o = dp + 8u * lane + shift;
+                    if ((o & 3u) == 0u) {
+                        *reinterpret_cast<uint32_t *>(ring + (o & (kRing - 1))) = lo;
+                        *reinterpret_cast<uint32_t *>(ring + ((o + 4u) & (kRing - 1))) = hi;
+                    } else {
 #pragma unroll
-                    for (int k = 0; k < 8; k++) ring[(o + k) & (kRing - 1)] = s[k];
+                        for (int k = 0; k < 4; k++) {
+                            ring[(o + k) & (kRing - 1)] = (uint8_t)(lo >> (8 * k));
+                            ring[(o + 4 + k) & (kRing - 1)] = (uint8_t)(hi >> (8 * k));
+                        }
+                    }
                 }
                 sp += 9u * streak;
                 dp += 8u * streak;
@@ -84,65 +162,109 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
                     flushed = to;
                     __syncwarp();
                 }
-                continue;
+                if (streak < 32u) break;
+                w0 = n0; w1 = n1; w2 = n2;
             }
+            win_seek(win, sp, lane);
+            continue;
         }
-        // ---- one control group -------------------------------------------------------------
-        const uint32_t byte = (sp + lane < slen) ? src[sp + lane] : 0u;
-        const uint32_t ctrl = __shfl_sync(0xffffffffu, byte, 0);
+
+        // ---- item walk of the group: register-only and identical in all lanes.  Item k starts at
+        //      source offset p_k inside the group; lane k keeps p_k (ppr:203-228 restated).
         const uint32_t extmask = __ballot_sync(0xffffffffu, (byte & 0x0Fu) == 0x0Fu);
-        uint32_t off = 1;                                                    // source offset inside the group
-        uint32_t nout = 0;                                                   // bytes produced by this group
-        bool dirty = false;                                                  // ring written since last sync
-        bool stop = false;                                                   // inner `break` of the reference
-        for (uint32_t k = 0; k < 8 && !stop && !corrupt; ) {
-            if (sp + off >= slen) break;                                     // `sp < srcend` of the inner loop
-            if ((ctrl >> k) & 1u) {
-                if (sp + off + 2u > slen) { corrupt = true; break; }
-                const uint32_t b0 = __shfl_sync(0xffffffffu, byte, off);
-                const uint32_t b1 = __shfl_sync(0xffffffffu, byte, off + 1u);
-                uint32_t len = (b0 & 0x0Fu) + 3u;                            // ppr:205
-                const uint32_t moff = ((b0 & 0xF0u) << 4) | b1;              // ppr:206-208
-                const bool ext = (extmask >> off) & 1u;
-                off += 2u;
-                if (ext) {                                                   // len == 18 (ppr:210-212)
-                    if (sp + off >= slen) { corrupt = true; break; }
-                    len += __shfl_sync(0xffffffffu, byte, off);
-                    off += 1u;
-                }
-                const uint32_t at = dp + nout;
-                if (at + len > rawsize) { corrupt = true; break; }           // ppr:213-215 always ends corrupt
-                if (moff == 0 || moff > at) { corrupt = true; break; }
-                if (dirty) { __syncwarp(); dirty = false; }
-                for (uint32_t i = lane; i < len; i += 32) {
-                    const uint32_t back = (moff >= len) ? i : (i % moff);    // overlapping copy (ppr:216-219)
-                    ring[(at + i + shift) & (kRing - 1)] = ring[(at - moff + back + shift) & (kRing - 1)];
-                }
-                dirty = true;
-                nout += len;
-                k++;
-            } else {
-                // run of literals: consecutive zero control bits, bounded by source and room
-                uint32_t run = (uint32_t)__ffs((int)((ctrl >> k) | 0x100u >> k)) - 1u;   // zeros before next set bit
-                if (run > 8u - k) run = 8u - k;
-                if (run > slen - (sp + off)) run = slen - (sp + off);
-                const uint32_t at = dp + nout;
-                if (at >= rawsize) { stop = true; break; }                   // ppr:221-222 -> corrupt at the end
-                const uint32_t roomb = rawsize - at;
-                bool hit_end = false;
-                if (run > roomb) { run = roomb; hit_end = true; }
-                if (lane >= off && lane < off + run) ring[(at + (lane - off) + shift) & (kRing - 1)] = (uint8_t)byte;
-                dirty = true;
-                nout += run;
-                off += run;
-                k += run;
-                if (hit_end) { stop = true; }                                // next literal would break with sp < srcend
+        const uint32_t n_avail = min(32u, slen - sp);                        // a group is at most 25 bytes
+        uint32_t pnext = 1, my_p = 0, nitems = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < 8; k++) {
+            if (pnext < n_avail) {                                           // `sp < srcend` of the inner loop
+                const uint32_t sz = ((ctrl >> k) & 1u) ? 2u + ((extmask >> pnext) & 1u) : 1u;
+                if (lane == k) my_p = pnext;
+                pnext += sz;
+                nitems = k + 1;
             }
         }
-        if (stop && sp + off < slen) corrupt = true;                         // literal refused: sp != srcend
-        sp += off;
-        dp += nout;
-        __syncwarp();
+        if (pnext > n_avail) { corrupt = true; break; }                      // a tag runs past the source
+
+        // ---- lane k decodes item k
+        const uint32_t b0 = __shfl_sync(0xffffffffu, byte, my_p);
+        const uint32_t b1 = __shfl_sync(0xffffffffu, byte, (my_p + 1u) & 31u);
+        const uint32_t b2 = __shfl_sync(0xffffffffu, byte, (my_p + 2u) & 31u);
+        const bool is_item = lane < nitems;
+        const bool is_match = is_item && ((ctrl >> lane) & 1u);
+        uint32_t len = 1, moff = 0;
+        if (is_match) {
+            len = (b0 & 0x0Fu) + 3u;                                         // ppr:205
+            moff = ((b0 & 0xF0u) << 4) | b1;                                 // ppr:206-208
+            if ((b0 & 0x0Fu) == 0x0Fu) len += b2;                            // ppr:210-212
+        }
+        const uint32_t olen = is_item ? len : 0u;
+        uint32_t incl = olen;                                                // inclusive scan over the 8 item lanes
+#pragma unroll
+        for (int d = 1; d < 8; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= (uint32_t)d) incl += o;
+        }
+        const uint32_t my_o = incl - olen;                                   // output offset of my item in the group
+        const uint32_t total = __shfl_sync(0xffffffffu, incl, 7);
+        // Any item the reference would refuse ends in "corrupt" (ppr:213-215, 221-222 then 229-230):
+        // a literal or a match that does not fit the output, offset 0, offset before the output start.
+        const bool bad = is_item && ((dp + my_o + olen > rawsize) || (is_match && (moff == 0u || moff > dp + my_o)));
+        if (__ballot_sync(0xffffffffu, bad)) { corrupt = true; break; }
+
+        if (total <= 64u) {
+            // ---- short items: one lane per output byte, 32 bytes per step
+            const uint32_t pack = moff | (len << 12) | (my_p << 21) | ((is_match ? 1u : 0u) << 26);
+            for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+                const uint32_t c0 = __popc(__ballot_sync(0xffffffffu, is_item && my_o <= t0));
+                const uint32_t starts = __reduce_or_sync(0xffffffffu, (is_item && my_o > t0 && my_o < t0 + 32u) ? (1u << (my_o - t0)) : 0u);
+                const uint32_t k = c0 - 1u + __popc(starts & ((2u << lane) - 1u));
+                const uint32_t kp = __shfl_sync(0xffffffffu, pack, k & 31u);
+                const uint32_t ko = __shfl_sync(0xffffffffu, my_o, k & 31u);
+                const uint32_t lit = __shfl_sync(0xffffffffu, byte, (kp >> 21) & 31u);
+                const uint32_t t = t0 + lane;
+                const bool live = t < total;
+                const bool m = (kp >> 26) & 1u;
+                bool resolved = true;
+                uint32_t val = lit, srcl = 0;
+                if (live && m) {
+                    const uint32_t kmoff = kp & 0xFFFu, klen = (kp >> 12) & 0x1FFu;
+                    uint32_t j = t - ko;
+                    if (kmoff < klen) j %= kmoff;                            // overlapping copy (ppr:216-219)
+                    const uint32_t spos = dp + ko - kmoff + j;               // absolute output position of the source byte
+                    if (spos >= dp + t0) { resolved = false; srcl = spos - (dp + t0); }   // produced in this very step
+                    else val = ring[(spos + shift) & (kRing - 1)];
+                }
+                for (;;) {                                                   // chase sources inside the step
+                    const uint32_t r = __ballot_sync(0xffffffffu, resolved);
+                    if (r == 0xffffffffu) break;
+                    const uint32_t v = __shfl_sync(0xffffffffu, val, srcl);
+                    if (!resolved && ((r >> srcl) & 1u)) { val = v; resolved = true; }
+                }
+                if (live) ring[(dp + t + shift) & (kRing - 1)] = (uint8_t)val;
+                __syncwarp();
+            }
+        } else {
+            // ---- long matches: item after item, 32 bytes per step and item
+            for (uint32_t k = 0; k < nitems; k++) {
+                const uint32_t klen = __shfl_sync(0xffffffffu, len, k), kmoff = __shfl_sync(0xffffffffu, moff, k);
+                const uint32_t ko = __shfl_sync(0xffffffffu, my_o, k), kpp = __shfl_sync(0xffffffffu, my_p, k);
+                const uint32_t at = dp + ko;
+                if ((ctrl >> k) & 1u) {
+                    if (kmoff >= klen) {
+                        for (uint32_t i = lane; i < klen; i += 32)
+                            ring[(at + i + shift) & (kRing - 1)] = ring[(at - kmoff + i + shift) & (kRing - 1)];
+                    } else {
+                        for (uint32_t i = lane; i < klen; i += 32)
+                            ring[(at + i + shift) & (kRing - 1)] = ring[(at - kmoff + (i % kmoff) + shift) & (kRing - 1)];
+                    }
+                } else if (lane == kpp) {
+                    ring[(at + shift) & (kRing - 1)] = (uint8_t)byte;
+                }
+                __syncwarp();
+            }
+        }
+        sp += pnext;
+        dp += total;
         if (dp - flushed >= kFlushAt) {
             const uint32_t to = dp - ((dp + shift) & 15u);
             pglz_flush(ring, dst, shift, flushed, to, lane);
@@ -157,16 +279,24 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
     return !corrupt && dp == rawsize && sp == slen;                          // ppr:229-230
 }
 
+// Jobs are taken through *ticket (zero at launch).  split != 0: job slots interleave the two values of
+// a row (slot 2r = independent_var, 2r+1 = dependent_var); tickets then visit all even slots first so
+// that the large values start first and the small ones fill the tail.
 __global__ void __launch_bounds__(32 * kPglzWarps)
 k_pglz_decode(const PglzJob *__restrict__ jobs, const uint32_t *n_jobs_dev, uint32_t n_jobs_mul, uint32_t n_jobs_host,
-              int32_t *status, DevState *st)
+              int32_t *status, DevState *st, uint32_t *ticket, int split)
 {
     extern __shared__ __align__(16) uint8_t smem_ring[];
     uint8_t *ring = smem_ring + (size_t)(threadIdx.x >> 5) * kRing;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t n_jobs = n_jobs_dev ? (*n_jobs_dev) * n_jobs_mul : n_jobs_host;
-    const uint32_t wid = blockIdx.x * kPglzWarps + (threadIdx.x >> 5), nw = gridDim.x * kPglzWarps;
-    for (uint32_t j = wid; j < n_jobs; j += nw) {
+    const uint32_t half = n_jobs >> 1;
+    for (;;) {
+        uint32_t t = 0;
+        if (lane == 0) t = atomicAdd(ticket, 1u);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= n_jobs) break;
+        const uint32_t j = split ? (t < half ? 2u * t : 2u * (t - half) + 1u) : t;
         const PglzJob job = jobs[j];
         if (job.slen == kNone) continue;
         const bool ok = pglz_warp_decode(reinterpret_cast<const uint8_t *>(job.src), job.slen,
