@@ -147,8 +147,18 @@ class ClockSampler:
 # CPU arm: the oracle's C restatement on the host cores
 # ------------------------------------------------------------------------------------------------
 
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:  # noqa
+        return os.cpu_count() or 1
+
+
 def cpu_decode_rate(seg, meta, reps, threads=0):
-    """rows/s of oracle/da_oracle.c (OpenMP over values) on the whole segment; best of `reps`."""
+    """rows/s of oracle/da_oracle.c (OpenMP over values) on the whole segment; best of `reps`.
+    threads=0: every core this process may run on (torchrun exports OMP_NUM_THREADS=1, so the count is
+    passed explicitly)."""
+    threads = threads or host_threads()
     sys.path.insert(0, os.path.join(REPO, "oracle"))
     import da_oracle
     from cerebro_ds_kpgi_b200 import build
@@ -165,7 +175,7 @@ def cpu_decode_rate(seg, meta, reps, threads=0):
                    out_ind=out_ind, out_dep=out_dep)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
-    return meta["rows"] / best, best, orc.num_threads() if threads == 0 else threads
+    return meta["rows"] / best, best, threads
 
 
 def python_port_rate(n_rows=2, storage="ext_pglz"):
@@ -186,26 +196,30 @@ def run_reference_arm(args):
     if rank != 0:
         return
     seg, meta = make_workload(args.workload, 2018, args.toast_mib)
-    threads = os.cpu_count() or 1
+    threads = host_threads()
+    n_seg = max(1, args.gpus)          # the whole job: one segment per GPU of our arm, decoded on this host's cores
     times = []
     for i in range(args.warmup + args.steps):
-        rate, dt, used = cpu_decode_rate(seg, meta, 1, threads=0)
+        dt = 0.0
+        for _ in range(n_seg):
+            rate, t, used = cpu_decode_rate(seg, meta, 1, threads=0)
+            dt += t
         if i >= args.warmup:
             times.append(dt)
     ms = 1000.0 * float(np.mean(times))
-    value = meta["rows"] / (ms / 1000.0)
+    value = n_seg * meta["rows"] / (ms / 1000.0)
     alg_bytes = seg.heap.size + seg.toast.size + meta["ind_bytes"] + meta["dep_bytes"] + 8 * meta["rows"]
     line = {
         "impl": "reference", "metric": "decoded_rows_per_s", "value": value, "unit": "rows/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "gb_per_s": alg_bytes / (ms / 1000.0) / 1e9,
+        "gb_per_s": n_seg * alg_bytes / (ms / 1000.0) / 1e9,
         "config": {"workload": args.workload, "description": meta["desc"], "rows_per_segment": meta["rows"],
-                   "toast_mib": seg.toast.size >> 20, "segments": 1},
+                   "toast_mib": seg.toast.size >> 20, "segments": n_seg},
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": used, "kind": "port",
-                         "sample": "whole %d MiB segment per step, oracle/da_oracle.c (C restatement of "
+                         "sample": "%d x whole %d MiB segment per step, oracle/da_oracle.c (C restatement of "
                                    "pg_page_reader.py + pg_lzcompress.c), OpenMP over values; the shipped reference is a "
-                                   "pure-Python loop and cannot read uncompressed external values" % (seg.toast.size >> 20)},
+                                   "pure-Python loop and cannot read uncompressed external values" % (n_seg, seg.toast.size >> 20)},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "host_cores": threads,
         "python_port": {"pglz_rows_per_s": python_port_rate(2, "ext_pglz"), "uncompressed_rows_per_s": python_port_rate(64, "ext_raw"),
