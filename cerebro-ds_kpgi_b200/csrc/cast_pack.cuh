@@ -12,7 +12,8 @@
 
 namespace cds {
 
-// One warp per row; first maximum wins, as np.argmax.
+// One warp per row; first maximum wins, as np.argmax.  Rows whose bytes are 16-byte aligned are read
+// eight classes per lane and load.
 __global__ void __launch_bounds__(256)
 k_onehot_argmax_i16(const int16_t *__restrict__ onehot, unsigned long long n_rows, uint32_t classes,
                     long long *__restrict__ labels)
@@ -20,13 +21,27 @@ k_onehot_argmax_i16(const int16_t *__restrict__ onehot, unsigned long long n_row
     const uint32_t lane = threadIdx.x & 31;
     const unsigned long long w0 = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const unsigned long long nw = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+    const bool vec = ((classes & 7u) == 0u) && ((reinterpret_cast<uintptr_t>(onehot) & 15u) == 0u);
     for (unsigned long long r = w0; r < n_rows; r += nw) {
         const int16_t *row = onehot + r * classes;
         int best = -32769;
         uint32_t best_i = 0xFFFFFFFFu;
-        for (uint32_t c = lane; c < classes; c += 32) {
-            const int v = row[c];
-            if (v > best) { best = v; best_i = c; }
+        if (vec) {
+            const uint4 *row4 = reinterpret_cast<const uint4 *>(row);
+            for (uint32_t c8 = lane; c8 < (classes >> 3); c8 += 32) {
+                const uint4 q = __ldcs(row4 + c8);
+                const uint32_t wds[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const int v = (int)(int16_t)(wds[k >> 1] >> ((k & 1) * 16));
+                    if (v > best) { best = v; best_i = c8 * 8u + k; }
+                }
+            }
+        } else {
+            for (uint32_t c = lane; c < classes; c += 32) {
+                const int v = row[c];
+                if (v > best) { best = v; best_i = c; }
+            }
         }
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {

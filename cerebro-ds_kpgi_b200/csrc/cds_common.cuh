@@ -37,7 +37,8 @@ struct DevState {
     uint32_t n_pos;
     uint32_t flags;               // kFlagRowOverflow | kFlagChunkOverflow
     uint32_t pglz_ticket;         // work counter of k_pglz_decode
-    uint32_t pad0, pad1;
+    uint32_t n_jobs_front;        // compacted pglz jobs: large values from slot 0 up ...
+    uint32_t n_jobs_back;         // ... small values from the last slot down
 };
 
 // One TOAST chunk -> one copy.  dst == 0: chunk not referenced (or refused); nothing is copied.
@@ -123,8 +124,7 @@ __device__ inline uint32_t htab_find(const unsigned long long *tab, uint32_t mas
 // its predecessors' aggregates / inclusive prefixes, 32 at a time.  The workspace (ticket + status
 // words) must be zero when the kernel starts; one cudaMemsetAsync per decode clears all of them.
 constexpr int kScanThreads = 256;
-constexpr int kScanItems = 16;
-constexpr uint32_t kScanTile = kScanThreads * kScanItems;
+constexpr uint32_t kScanMinTile = kScanThreads * 4;   // smallest tile any scan uses (sizes the workspaces)
 
 struct ScanWs {
     uint32_t *ticket;             // 1 word, zeroed
@@ -153,9 +153,10 @@ __device__ inline unsigned long long ld_volatile_u64(const unsigned long long *p
 // out[i] = sum_{j<i} load(j) for i in [0, n); out[n] = total when write_total_at_n.  Every block of
 // the launch must call this (blockDim.x == kScanThreads).  Returns the grand total to the block that
 // processed the last tile (others get 0) through *is_last.
-template <typename T, typename LoadFn>
+template <typename T, int kScanItems, typename LoadFn>
 __device__ inline T device_exclusive_scan(LoadFn load, T *out, uint32_t n, ScanWs ws, bool write_total_at_n, bool *is_last)
 {
+    constexpr uint32_t kScanTile = kScanThreads * kScanItems;
     __shared__ unsigned long long sh_warp[kScanThreads / 32];
     __shared__ unsigned long long sh_prefix;
     __shared__ uint32_t sh_tile;

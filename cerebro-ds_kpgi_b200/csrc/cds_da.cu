@@ -181,7 +181,7 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
         // scans: [0] heap pages, [1] TOAST pages, [2] rows, [3] chunks, [4],[5] positions, [6] values
         const uint64_t lens[7] = {max_heap_pages, max_toast_pages, R, C, R, R, V};
         uint64_t tiles[7], total_tiles = 0;
-        for (int i = 0; i < 7; i++) { tiles[i] = lens[i] / kScanTile + 2; total_tiles += tiles[i]; }
+        for (int i = 0; i < 7; i++) { tiles[i] = lens[i] / kScanMinTile + 2; total_tiles += tiles[i]; }
         const uint64_t state_bytes = 256, ws_bytes = ((8 + total_tiles) * 4 + 255) & ~255ull;
         s->zero_bytes = state_bytes + ws_bytes + hsize * 8;
         if (e == cudaSuccess) e = dalloc(&s->zero_region, s->zero_bytes);
@@ -217,9 +217,9 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
 // ---- steps -------------------------------------------------------------------------------------
 
 static inline uint32_t small_grid(const cds_segment *s) { return (uint32_t)s->num_sms * 4u; }
-static inline uint32_t scan_grid(const cds_segment *s, uint64_t n)
+static inline uint32_t scan_grid(const cds_segment *s, uint64_t n, uint32_t items_per_thread)
 {
-    uint64_t tiles = n / kScanTile + 1, cap = (uint64_t)s->num_sms * 4u;
+    uint64_t tiles = n / ((uint64_t)kScanThreads * items_per_thread) + 1, cap = (uint64_t)s->num_sms * 4u;
     return (uint32_t)(tiles < cap ? tiles : cap);
 }
 
@@ -242,13 +242,14 @@ extern "C" int cds_heap_scan(cds_segment *s, const void *d_heap_pages, uint64_t 
     if (rc) return rc;
     s->d_heap = static_cast<const uint8_t *>(d_heap_pages);
     s->n_heap_pages = n_pages;
-    k_page_index<<<scan_grid(s, n_pages), kScanThreads, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->state, 0,
+    k_page_index<<<scan_grid(s, n_pages, 4), kScanThreads, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->state, 0,
                                                                   (uint32_t)s->cap_rows, s->ws[0]);
     CU(cudaGetLastError());
     LAUNCHED(1);
     if (n_pages) {
-        uint32_t grid = (uint32_t)(n_pages < small_grid(s) ? n_pages : small_grid(s));
-        k_heap_rows<<<grid, 128, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->rows, s->state, s->htab, s->hmask,
+        uint64_t want = n_pages * kHeapSub, cap = (uint64_t)s->num_sms * 16u;
+        uint32_t grid = (uint32_t)(want < cap ? want : cap);
+        k_heap_rows<<<grid, 64, 0, st>>>(s->d_heap, (uint32_t)n_pages, s->heap_base, s->rows, s->state, s->htab, s->hmask,
                                           s->vfirst, s->vcount, s->vbytes, s->vseq0);
         CU(cudaGetLastError());
         LAUNCHED(1);
@@ -287,7 +288,7 @@ extern "C" int cds_toast_scan(cds_segment *s, const void *d_toast_pages, uint64_
     CU(cudaSetDevice(s->device));
     s->d_toast = static_cast<const uint8_t *>(d_toast_pages);
     s->n_toast_pages = n_pages;
-    k_page_index<<<scan_grid(s, n_pages), kScanThreads, 0, st>>>(s->d_toast, (uint32_t)n_pages, s->toast_base, s->state, 1,
+    k_page_index<<<scan_grid(s, n_pages, 4), kScanThreads, 0, st>>>(s->d_toast, (uint32_t)n_pages, s->toast_base, s->state, 1,
                                                                   (uint32_t)s->cap_chunks, s->ws[1]);
     CU(cudaGetLastError());
     LAUNCHED(1);
@@ -310,12 +311,12 @@ extern "C" int cds_plan(cds_segment *s, uint32_t ind_sample_bytes, uint32_t dep_
     const uint32_t g = small_grid(s);
     k_plan_rows<<<g, 256, 0, st>>>(s->rows, s->d_toast, s->dir_loc, s->vfirst, s->vcount, s->vseq0, s->inline_flag,
                                    s->chunk_flag, s->row_first, s->ind_len, s->dep_len, s->vscr, s->state);
-    k_plan_scan1<<<dim3(scan_grid(s, s->cap_chunks), 2), kScanThreads, 0, st>>>(s->inline_flag, s->chunk_flag, s->state,
+    k_plan_scan1<<<dim3(scan_grid(s, s->cap_chunks, 8), 2), kScanThreads, 0, st>>>(s->inline_flag, s->chunk_flag, s->state,
                                                                               s->ws[2], s->ws[3]);
     k_assign_pos<<<g, 256, 0, st>>>(s->rows, s->inline_flag, s->chunk_flag, s->row_first, s->ind_len, s->dep_len,
                                     s->pos_of_row, s->row_at_pos, s->pos_ind, s->pos_dep, s->state, ind_sample_bytes,
                                     dep_sample_bytes);
-    k_plan_scan2<<<dim3(scan_grid(s, 2 * s->cap_rows), 3), kScanThreads, 0, st>>>(s->pos_ind, s->pos_dep, s->vscr, s->state,
+    k_plan_scan2<<<dim3(scan_grid(s, 2 * s->cap_rows, 8), 3), kScanThreads, 0, st>>>(s->pos_ind, s->pos_dep, s->vscr, s->state,
                                                                                 s->ws[4], s->ws[5], s->ws[6]);
     CU(cudaGetLastError());
     LAUNCHED(4);
@@ -346,7 +347,7 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
     }
     // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
     k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
-        s->jobs, &s->state->n_rows, 2u, 0u, nullptr, s->state, &s->state->pglz_ticket, 1);
+        s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket);
     CU(cudaGetLastError());
     LAUNCHED(2);
     return CDS_OK;
@@ -553,8 +554,8 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
     if (e == cudaSuccess) {
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > 148u * 7u) grid = 148u * 7u;
-        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, 0u, (uint32_t)n, d_stat, nullptr,
-                                                                     reinterpret_cast<uint32_t *>(d_stat + n), 0);
+        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, (uint32_t)n, d_stat, nullptr,
+                                                                     reinterpret_cast<uint32_t *>(d_stat + n));
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaMemcpyAsync(h_stat, d_stat, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
@@ -670,8 +671,8 @@ extern "C" int cds_pglz_decompress_batch_static(int device, const void *d_src, c
         CU(cudaGetLastError());
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > 148u * 7u) grid = 148u * 7u;
-        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(sc->jobs, nullptr, 0u, (uint32_t)n, d_status, &sc->state,
-                                                                     &sc->state.pglz_ticket, 0);
+        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(sc->jobs, nullptr, (uint32_t)n, d_status, &sc->state,
+                                                                     &sc->state.pglz_ticket);
         CU(cudaGetLastError());
         LAUNCHED(2);
     }

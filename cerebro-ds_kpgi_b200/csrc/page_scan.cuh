@@ -34,7 +34,7 @@ k_page_index(const uint8_t *__restrict__ pages, uint32_t n_pages, uint32_t *__re
         return (pd_lower - kPageHdr) >> 2;
     };
     bool last;
-    const uint32_t total = device_exclusive_scan<uint32_t>(count_of, base, n_pages, ws, true, &last);
+    const uint32_t total = device_exclusive_scan<uint32_t, 4>(count_of, base, n_pages, ws, true, &last);
     if (last && threadIdx.x == 0) {
         uint32_t n = total;
         if (total > cap_items) {
@@ -64,18 +64,20 @@ __device__ inline void index_row_values(const uint32_t *row, uint32_t r, unsigne
     htab_insert(htab, hmask, row[RW_DEP + 3], (row[RW_DEP_EXTERNAL] ? 0u : 0x80000000u) | (2 * r + 1));
 }
 
-// One block per heap page (grid-stride), one thread per ItemId: parse the MADlib packed row and
-// write its 16-word descriptor in table order.
-__global__ void __launch_bounds__(128)
+// kHeapSub blocks of 64 threads per heap page, one thread per ItemId: parse the MADlib packed row and
+// write its 16-word descriptor in table order.  (A page holds at most 430 such tuples.)
+constexpr uint32_t kHeapSub = 7;
+__global__ void __launch_bounds__(64)
 k_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *__restrict__ base,
             uint32_t *__restrict__ rows, DevState *st, unsigned long long *htab, uint32_t hmask,
             uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0)
 {
     if (st->flags & kFlagRowOverflow) return;
-    for (uint32_t p = blockIdx.x; p < n_pages; p += gridDim.x) {
+    for (uint32_t w = blockIdx.x; w < n_pages * kHeapSub; w += gridDim.x) {
+        const uint32_t p = w / kHeapSub, sub = w - p * kHeapSub;
         const uint8_t *pg = heap + (size_t)p * kPage;
         const uint32_t r0 = base[p], n = base[p + 1] - r0;
-        for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        for (uint32_t i = sub * 64u + threadIdx.x; i < n; i += kHeapSub * 64u) {
             uint32_t *row = rows + (size_t)(r0 + i) * kRowWords;
             uint32_t iid = *reinterpret_cast<const uint32_t *>(pg + kPageHdr + 4u * i);
             uint32_t lp_off = iid & 0x7FFFu, lp_len = iid >> 17;            // ppr:287-300
@@ -136,6 +138,12 @@ k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t
     const uint8_t *pg = toast + (size_t)p * kPage;
     const uint32_t g0 = base[p], n = base[p + 1] - g0;
     uint32_t lp = ld_u16(pg + 14);                                           // pd_upper
+    // The walk itself ignores the ItemIds, as the reference does; they only serve as prefetch hints so that
+    // the dependent tuple-header reads below find their sectors on the way (or already in L2).
+    for (uint32_t i = 0; i < n && i < 8u; i++) {
+        const uint32_t hint = *reinterpret_cast<const uint32_t *>(pg + kPageHdr + 4u * i) & 0x7FFFu;
+        if (hint + 40u <= kPage) asm volatile("prefetch.global.L2 [%0];" ::"l"(pg + hint + 16u));
+    }
     bool dead = false;
     for (uint32_t i = 0; i < n; i++) {
         const uint32_t g = g0 + i;
@@ -145,18 +153,28 @@ k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t
             if (lp + kItemHdr > kPage) dead = true;
         }
         if (!dead) {
-            uint32_t t_hoff = pg[lp + 22];
-            uint32_t hdr = lp + t_hoff + 8u;                                 // ppr:399-403
+            uint32_t t_hoff, hdr, chunkword;
+            bool have = false;
+            if (lp + 40u <= kPage) {
+                // one round trip for the usual t_hoff == 24 tuple: bytes 16..39 hold t_hoff, chunk_id, chunk_seq, length word
+                const uint2 a = *reinterpret_cast<const uint2 *>(pg + lp + 16), b = *reinterpret_cast<const uint2 *>(pg + lp + 24),
+                            c = *reinterpret_cast<const uint2 *>(pg + lp + 32);
+                t_hoff = (a.y >> 16) & 0xFFu;                                // byte 22 (ppr:272-276)
+                if (t_hoff == 24u) { id = b.x; seq = b.y; chunkword = c.x; have = true; }
+            } else {
+                t_hoff = pg[lp + 22];
+            }
+            hdr = lp + t_hoff + 8u;                                          // ppr:399-403
             if (hdr + 4u > kPage) dead = true;
             else {
-                uint32_t chunksize = ld_u32be(pg + hdr) & 0x3FFFFFFFu;       // VARSIZE (ppr:130-131,404)
+                if (!have) chunkword = ld_u32(pg + hdr);
+                const uint32_t chunksize = __byte_perm(chunkword, 0, 0x0123) & 0x3FFFFFFFu;   // VARSIZE (ppr:130-131,404)
                 if (chunksize < 4u || hdr + chunksize > kPage) dead = true;
                 else {
-                    id = ld_u32(pg + lp + t_hoff);
-                    seq = ld_u32(pg + lp + t_hoff + 4);
+                    if (!have) { id = ld_u32(pg + lp + t_hoff); seq = ld_u32(pg + lp + t_hoff + 4); }
                     loc_off = hdr + 4u;
                     loc_len = chunksize - 4u;
-                    hdr0 = pg[hdr];
+                    hdr0 = chunkword & 0xFFu;
                     lp += t_hoff + 8u + chunksize;                           // ppr:405-414
                 }
             }
@@ -241,11 +259,11 @@ k_plan_scan1(uint32_t *inline_flag, uint32_t *chunk_flag, DevState *st, ScanWs w
 {
     bool last;
     if (blockIdx.y == 0) {
-        const uint32_t tot = device_exclusive_scan<uint32_t>([&](uint32_t i) { return inline_flag[i]; }, inline_flag,
+        const uint32_t tot = device_exclusive_scan<uint32_t, 8>([&](uint32_t i) { return inline_flag[i]; }, inline_flag,
                                                              st->n_rows, ws_rows, false, &last);
         if (last && threadIdx.x == 0) st->n_inline = tot;
     } else {
-        device_exclusive_scan<uint32_t>([&](uint32_t i) { return chunk_flag[i]; }, chunk_flag, st->n_chunks, ws_chunks,
+        device_exclusive_scan<uint32_t, 8>([&](uint32_t i) { return chunk_flag[i]; }, chunk_flag, st->n_chunks, ws_chunks,
                                         true, &last);
     }
 }
@@ -290,15 +308,15 @@ k_plan_scan2(unsigned long long *pos_ind, unsigned long long *pos_dep, unsigned 
 {
     bool last;
     if (blockIdx.y == 0) {
-        const unsigned long long t = device_exclusive_scan<unsigned long long>(
+        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>(
             [&](uint32_t i) { return pos_ind[i]; }, pos_ind, st->n_pos, ws0, false, &last);
         if (last && threadIdx.x == 0) st->ind_bytes = t;
     } else if (blockIdx.y == 1) {
-        const unsigned long long t = device_exclusive_scan<unsigned long long>(
+        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>(
             [&](uint32_t i) { return pos_dep[i]; }, pos_dep, st->n_pos, ws1, false, &last);
         if (last && threadIdx.x == 0) st->dep_bytes = t;
     } else {
-        const unsigned long long t = device_exclusive_scan<unsigned long long>(
+        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>(
             [&](uint32_t i) { return vscr[i]; }, vscr, 2u * st->n_rows, ws2, false, &last);
         if (last && threadIdx.x == 0) st->scratch_bytes = t;
     }
@@ -361,6 +379,9 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
         ops[g] = op;
     }
 
+    // pglz jobs are compacted: independent_var jobs (large) grow from slot 0 upward, dependent_var jobs (small)
+    // from the last slot downward; k_pglz_decode hands them out large first.
+    const uint32_t last_slot = 2u * n_rows - 1u;
     for (uint32_t v = tid; v < 2u * n_rows; v += nth) {
         PglzJob job;
         job.src = 0; job.dst = 0; job.slen = kNone; job.rawsize = 0; job.err_key = 0;
@@ -403,7 +424,10 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
                 }
             }
         }
-        jobs[v] = job;
+        if (job.slen != kNone) {
+            if (a == 0) jobs[atomicAdd(&st->n_jobs_front, 1u)] = job;
+            else jobs[last_slot - atomicAdd(&st->n_jobs_back, 1u)] = job;
+        }
     }
 }
 

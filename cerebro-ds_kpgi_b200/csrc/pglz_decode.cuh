@@ -279,24 +279,27 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
     return !corrupt && dp == rawsize && sp == slen;                          // ppr:229-230
 }
 
-// Jobs are taken through *ticket (zero at launch).  split != 0: job slots interleave the two values of
-// a row (slot 2r = independent_var, 2r+1 = dependent_var); tickets then visit all even slots first so
-// that the large values start first and the small ones fill the tail.
+// Jobs are taken through *ticket (zero at launch).  With `st_counts` the job array is the compacted
+// two-ended list k_resolve builds (n_jobs_front slots from the start, n_jobs_back from slot 2*n_rows-1
+// down): front jobs (large values) are handed out first, the small ones fill the tail.
 __global__ void __launch_bounds__(32 * kPglzWarps)
-k_pglz_decode(const PglzJob *__restrict__ jobs, const uint32_t *n_jobs_dev, uint32_t n_jobs_mul, uint32_t n_jobs_host,
-              int32_t *status, DevState *st, uint32_t *ticket, int split)
+k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint32_t n_jobs_host,
+              int32_t *status, DevState *st, uint32_t *ticket)
 {
     extern __shared__ __align__(16) uint8_t smem_ring[];
     uint8_t *ring = smem_ring + (size_t)(threadIdx.x >> 5) * kRing;
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t n_jobs = n_jobs_dev ? (*n_jobs_dev) * n_jobs_mul : n_jobs_host;
-    const uint32_t half = n_jobs >> 1;
+    const uint32_t front = st_counts ? st_counts->n_jobs_front : n_jobs_host;
+    const uint32_t back = st_counts ? st_counts->n_jobs_back : 0u;
+    const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
+    const uint32_t n_jobs = front + back;
+    if (n_jobs == 0) return;
     for (;;) {
         uint32_t t = 0;
         if (lane == 0) t = atomicAdd(ticket, 1u);
         t = __shfl_sync(0xffffffffu, t, 0);
         if (t >= n_jobs) break;
-        const uint32_t j = split ? (t < half ? 2u * t : 2u * (t - half) + 1u) : t;
+        const uint32_t j = t < front ? t : last_slot - (t - front);
         const PglzJob job = jobs[j];
         if (job.slen == kNone) continue;
         const bool ok = pglz_warp_decode(reinterpret_cast<const uint8_t *>(job.src), job.slen,
