@@ -165,8 +165,9 @@ __device__ inline T device_exclusive_scan(LoadFn load, T *out, uint32_t n, ScanW
     *is_last = false;
     T grand = 0;
     if (n == 0) {
-        if (blockIdx.x == 0 && threadIdx.x == 0 && write_total_at_n) out[0] = 0;
-        *is_last = (blockIdx.x == 0);
+        // every participating block reports the (same) empty result: which blocks take part varies by caller
+        if (threadIdx.x == 0 && write_total_at_n) out[0] = 0;
+        *is_last = true;
         return 0;
     }
     for (;;) {

@@ -41,7 +41,8 @@ struct cds_segment {
     // inputs of the current decode
     const uint8_t *d_heap = nullptr, *d_toast = nullptr;
     uint64_t n_heap_pages = 0, n_toast_pages = 0;
-    bool have_rows = false, have_chunks = false, have_plan = false;
+    bool have_rows = false, have_chunks = false, have_plan = false, have_ops = false;
+    int coop_blocks = 0;            // co-resident grid for k_plan_fused (0: cooperative launch unavailable)
     // device buffers
     uint8_t *stage_heap = nullptr, *stage_toast = nullptr;
     uint32_t *heap_base = nullptr, *toast_base = nullptr, *rows = nullptr;
@@ -205,6 +206,13 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
     if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&s->h_state), sizeof(DevState), cudaHostAllocPortable);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_toast_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGatherSmemBytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
+    if (e == cudaSuccess) {
+        int coop = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
+        if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_plan_fused, 256, 0) == cudaSuccess && per_sm > 0)
+            s->coop_blocks = s->num_sms * (per_sm < 2 ? per_sm : 2);
+        cudaGetLastError();
+    }
     if (e != cudaSuccess) {
         int rc = cuda_fail(e, "cds_segment_create");
         cds_segment_destroy(s);
@@ -227,7 +235,7 @@ static inline uint32_t scan_grid(const cds_segment *s, uint64_t n, uint32_t item
 static int reset_state(cds_segment *s, cudaStream_t st)
 {
     CU(cudaMemsetAsync(s->zero_region, 0, s->zero_bytes, st));
-    s->have_rows = s->have_chunks = s->have_plan = false;
+    s->have_rows = s->have_chunks = s->have_plan = s->have_ops = false;
     return CDS_OK;
 }
 
@@ -303,38 +311,62 @@ extern "C" int cds_toast_scan(cds_segment *s, const void *d_toast_pages, uint64_
     return CDS_OK;
 }
 
+static PlanArgs plan_args(cds_segment *s, uint32_t isb, uint32_t dsb, void *out_ind, uint64_t ind_cap, void *out_dep,
+                          uint64_t dep_cap)
+{
+    PlanArgs A;
+    A.rows = s->rows; A.heap = s->d_heap; A.toast = s->d_toast;
+    A.dir_id = s->dir_id; A.dir_loc = s->dir_loc; A.dir_ref = s->dir_ref;
+    A.vfirst = s->vfirst; A.vcount = s->vcount; A.vseq0 = s->vseq0; A.vbytes = s->vbytes; A.vscr = s->vscr;
+    A.inline_flag = s->inline_flag; A.chunk_flag = s->chunk_flag; A.row_first = s->row_first;
+    A.pos_of_row = s->pos_of_row; A.row_at_pos = s->row_at_pos;
+    A.ind_len = s->ind_len; A.dep_len = s->dep_len; A.pos_ind = s->pos_ind; A.pos_dep = s->pos_dep;
+    A.row_ind_off = s->row_ind_off; A.row_dep_off = s->row_dep_off;
+    A.ops = s->ops; A.jobs = s->jobs; A.st = s->state;
+    for (int i = 0; i < 5; i++) A.ws[i] = s->ws[2 + i];
+    A.isb = isb; A.dsb = dsb;
+    A.out_ind = static_cast<uint8_t *>(out_ind); A.out_dep = static_cast<uint8_t *>(out_dep); A.scratch = s->scratch;
+    A.cap_ind = ind_cap; A.cap_dep = dep_cap; A.cap_scratch = s->cap_scratch;
+    return A;
+}
+
+// Plan (and, when the output buffers are already known, the copy descriptors) in one cooperative launch;
+// separate kernels when cooperative launch is not available.
+static int launch_plan(cds_segment *s, PlanArgs &A, bool with_resolve, cudaStream_t st)
+{
+    if (s->coop_blocks > 0) {
+        int do_resolve = with_resolve ? 1 : 0;
+        void *args[] = {&A, &do_resolve};
+        cudaError_t e = cudaLaunchCooperativeKernel((void *)k_plan_fused, dim3((unsigned)s->coop_blocks), dim3(256), args, 0, st);
+        if (e == cudaSuccess) { LAUNCHED(1); return CDS_OK; }
+        cudaGetLastError();
+        s->coop_blocks = 0;            // fall through to the plain launches from now on
+    }
+    const uint32_t g = small_grid(s);
+    k_plan_rows<<<g, 256, 0, st>>>(A);
+    k_plan_scan1<<<dim3(scan_grid(s, s->cap_chunks, 8), 2), kScanThreads, 0, st>>>(A);
+    k_assign_pos<<<g, 256, 0, st>>>(A);
+    k_plan_scan2<<<dim3(scan_grid(s, 2 * s->cap_rows, 8), 3), kScanThreads, 0, st>>>(A);
+    if (with_resolve) k_resolve<<<g, 256, 0, st>>>(A);
+    CU(cudaGetLastError());
+    LAUNCHED(with_resolve ? 5 : 4);
+    return CDS_OK;
+}
+
 extern "C" int cds_plan(cds_segment *s, uint32_t ind_sample_bytes, uint32_t dep_sample_bytes, void *stream)
 {
     if (!s || !s->have_rows || !s->have_chunks || s->have_plan) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(s->device));
-    const uint32_t g = small_grid(s);
-    k_plan_rows<<<g, 256, 0, st>>>(s->rows, s->d_toast, s->dir_loc, s->vfirst, s->vcount, s->vseq0, s->inline_flag,
-                                   s->chunk_flag, s->row_first, s->ind_len, s->dep_len, s->vscr, s->state);
-    k_plan_scan1<<<dim3(scan_grid(s, s->cap_chunks, 8), 2), kScanThreads, 0, st>>>(s->inline_flag, s->chunk_flag, s->state,
-                                                                              s->ws[2], s->ws[3]);
-    k_assign_pos<<<g, 256, 0, st>>>(s->rows, s->inline_flag, s->chunk_flag, s->row_first, s->ind_len, s->dep_len,
-                                    s->pos_of_row, s->row_at_pos, s->pos_ind, s->pos_dep, s->state, ind_sample_bytes,
-                                    dep_sample_bytes);
-    k_plan_scan2<<<dim3(scan_grid(s, 2 * s->cap_rows, 8), 3), kScanThreads, 0, st>>>(s->pos_ind, s->pos_dep, s->vscr, s->state,
-                                                                                s->ws[4], s->ws[5], s->ws[6]);
-    CU(cudaGetLastError());
-    LAUNCHED(4);
+    PlanArgs A = plan_args(s, ind_sample_bytes, dep_sample_bytes, nullptr, 0, nullptr, 0);
+    int rc = launch_plan(s, A, false, st);
+    if (rc) return rc;
     s->have_plan = true;
     return CDS_OK;
 }
 
-extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap, void *d_out_dep, uint64_t dep_cap,
-                               void *stream)
+static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
 {
-    if (!s || !s->have_plan) return CDS_ERR_ARG;
-    cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
-    k_resolve<<<small_grid(s), 256, 0, st>>>(
-        s->rows, s->d_heap, s->dir_id, s->dir_loc, s->dir_ref, s->vfirst, s->vcount, s->vbytes, s->vscr, s->pos_of_row,
-        s->pos_ind, s->pos_dep, s->row_ind_off, s->row_dep_off, s->ind_len, s->dep_len, static_cast<uint8_t *>(d_out_ind), ind_cap,
-        static_cast<uint8_t *>(d_out_dep), dep_cap, s->scratch, s->cap_scratch, s->ops, s->jobs, s->state);
-    CU(cudaGetLastError());
     if (s->n_toast_pages) {
         uint32_t grid = (uint32_t)(s->n_toast_pages < (uint64_t)s->num_sms ? s->n_toast_pages : (uint64_t)s->num_sms);
         const bool timed = s->ev && s->ev_used < s->ev_cap;
@@ -349,8 +381,22 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
     k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
         s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket);
     CU(cudaGetLastError());
-    LAUNCHED(2);
+    LAUNCHED(1);
     return CDS_OK;
+}
+
+extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap, void *d_out_dep, uint64_t dep_cap,
+                               void *stream)
+{
+    if (!s || !s->have_plan || s->have_ops) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(s->device));
+    PlanArgs A = plan_args(s, 0, 0, d_out_ind, ind_cap, d_out_dep, dep_cap);
+    k_resolve<<<small_grid(s), 256, 0, st>>>(A);
+    CU(cudaGetLastError());
+    LAUNCHED(1);
+    s->have_ops = true;
+    return launch_gather_and_pglz(s, st);
 }
 
 static void decode_key(unsigned long long key, cds_summary *sum)
@@ -382,11 +428,47 @@ extern "C" int cds_decode_device(cds_segment *s, const void *d_heap, uint64_t n_
                                  uint64_t n_toast_pages, uint32_t isb, uint32_t dsb, void *d_out_ind, uint64_t ind_cap,
                                  void *d_out_dep, uint64_t dep_cap, void *stream, cds_summary *sum)
 {
-    int rc = cds_heap_scan(s, d_heap, n_heap_pages, stream);
-    if (rc) return rc;
-    if ((rc = cds_toast_scan(s, d_toast, n_toast_pages, stream))) return rc;
-    if ((rc = cds_plan(s, isb, dsb, stream))) return rc;
-    if ((rc = cds_materialize(s, d_out_ind, ind_cap, d_out_dep, dep_cap, stream))) return rc;
+    if (!s || (!d_heap && n_heap_pages) || (!d_toast && n_toast_pages)) return CDS_ERR_ARG;
+    if (n_heap_pages > s->cap_heap_pages || n_toast_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
+    if ((reinterpret_cast<uintptr_t>(d_heap) | reinterpret_cast<uintptr_t>(d_toast)) & 15u) return CDS_ERR_ARG;
+    int rc;
+    {
+        // same steps as cds_heap_scan + cds_toast_scan, with both page indexes in one launch
+        cudaStream_t st = (cudaStream_t)stream;
+        CU(cudaSetDevice(s->device));
+        if ((rc = reset_state(s, st))) return rc;
+        s->d_heap = static_cast<const uint8_t *>(d_heap); s->n_heap_pages = n_heap_pages;
+        s->d_toast = static_cast<const uint8_t *>(d_toast); s->n_toast_pages = n_toast_pages;
+        const uint32_t gx = scan_grid(s, n_heap_pages > n_toast_pages ? n_heap_pages : n_toast_pages, 4);
+        k_page_index2<<<dim3(gx, 2), kScanThreads, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, (uint32_t)s->cap_rows,
+                                                           s->ws[0], s->d_toast, (uint32_t)n_toast_pages, s->toast_base,
+                                                           (uint32_t)s->cap_chunks, s->ws[1], s->state);
+        CU(cudaGetLastError());
+        LAUNCHED(1);
+        if (n_heap_pages) {
+            uint64_t want = n_heap_pages * kHeapSub, cap = (uint64_t)s->num_sms * 16u;
+            k_heap_rows<<<(uint32_t)(want < cap ? want : cap), 64, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, s->rows,
+                                                                          s->state, s->htab, s->hmask, s->vfirst, s->vcount,
+                                                                          s->vbytes, s->vseq0);
+            CU(cudaGetLastError());
+            LAUNCHED(1);
+        }
+        if (n_toast_pages) {
+            k_toast_walk<<<(uint32_t)((n_toast_pages + 127) / 128), 128, 0, st>>>(
+                s->d_toast, (uint32_t)n_toast_pages, s->toast_base, s->htab, s->hmask, s->dir_id, s->dir_loc, s->dir_ref,
+                s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state);
+            CU(cudaGetLastError());
+            LAUNCHED(1);
+        }
+        s->have_rows = s->have_chunks = true;
+    }
+    {
+        cudaStream_t st = (cudaStream_t)stream;
+        PlanArgs A = plan_args(s, isb, dsb, d_out_ind, ind_cap, d_out_dep, dep_cap);
+        if ((rc = launch_plan(s, A, true, st))) return rc;
+        s->have_plan = s->have_ops = true;
+        if ((rc = launch_gather_and_pglz(s, st))) return rc;
+    }
     return sum ? cds_finish(s, stream, sum) : CDS_OK;
 }
 

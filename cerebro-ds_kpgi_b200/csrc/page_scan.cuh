@@ -11,6 +11,8 @@
 // All of this is metadata work: it touches a few sectors per 32 KB page (< 1 % of the bytes);
 // the bulk traffic is in toast_gather.cuh.
 #pragma once
+#include <cooperative_groups.h>
+
 #include "cds_common.cuh"
 
 namespace cds {
@@ -18,9 +20,8 @@ namespace cds {
 // Shared by the heap and the TOAST relation: item count per page from pd_lower, device-wide
 // exclusive scan into base[0..n_pages], validation of the header.
 //   toast != 0 additionally asserts pd_special == BLCKSZ (ppr:388-389).
-__global__ void __launch_bounds__(kScanThreads)
-k_page_index(const uint8_t *__restrict__ pages, uint32_t n_pages, uint32_t *__restrict__ base,
-             DevState *st, int toast, uint32_t cap_items, ScanWs ws)
+__device__ __forceinline__ void d_page_index(const uint8_t *__restrict__ pages, uint32_t n_pages, uint32_t *__restrict__ base,
+                                             DevState *st, int toast, uint32_t cap_items, ScanWs ws)
 {
     const uint32_t stage = toast ? 1u : 0u;
     auto count_of = [&](uint32_t p) -> uint32_t {
@@ -45,6 +46,23 @@ k_page_index(const uint8_t *__restrict__ pages, uint32_t n_pages, uint32_t *__re
         }
         if (toast) st->n_chunks = n; else st->n_rows = n;
     }
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+k_page_index(const uint8_t *__restrict__ pages, uint32_t n_pages, uint32_t *__restrict__ base,
+             DevState *st, int toast, uint32_t cap_items, ScanWs ws)
+{
+    d_page_index(pages, n_pages, base, st, toast, cap_items, ws);
+}
+
+// Heap (blockIdx.y == 0) and TOAST (blockIdx.y == 1) relation indexed by one launch (one-shot decode).
+__global__ void __launch_bounds__(kScanThreads)
+k_page_index2(const uint8_t *__restrict__ heap, uint32_t n_heap, uint32_t *__restrict__ heap_base, uint32_t cap_rows, ScanWs ws_h,
+              const uint8_t *__restrict__ toast, uint32_t n_toast, uint32_t *__restrict__ toast_base, uint32_t cap_chunks, ScanWs ws_t,
+              DevState *st)
+{
+    if (blockIdx.y == 0) d_page_index(heap, n_heap, heap_base, st, 0, cap_rows, ws_h);
+    else d_page_index(toast, n_toast, toast_base, st, 1, cap_chunks, ws_t);
 }
 
 // Reset the per-value statistics of row r and enter its two va_valueid words into the hash table.
@@ -202,26 +220,42 @@ k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t
     }
 }
 
+// ---- detoast plan ---------------------------------------------------------------------------------
+// Five phases (rows -> ranks -> positions -> offsets -> copy descriptors).  They run either as one
+// cooperative launch with grid-wide barriers in between (k_plan_fused) or as separate kernels.
+struct PlanArgs {
+    const uint32_t *rows;
+    const uint8_t *heap, *toast;
+    const uint2 *dir_id, *dir_loc;
+    const uint32_t *dir_ref;
+    uint32_t *vfirst, *vcount, *vseq0;
+    unsigned long long *vbytes, *vscr;
+    uint32_t *inline_flag, *chunk_flag, *row_first, *pos_of_row, *row_at_pos;
+    unsigned long long *ind_len, *dep_len, *pos_ind, *pos_dep, *row_ind_off, *row_dep_off;
+    CopyOp *ops;
+    PglzJob *jobs;
+    DevState *st;
+    ScanWs ws[5];                 // inline rank, chunk rank, ind offsets, dep offsets, staging offsets
+    uint32_t isb, dsb;            // sample sizes for the shape check (0: none)
+    uint8_t *out_ind, *out_dep, *scratch;
+    unsigned long long cap_ind, cap_dep, cap_scratch;
+};
+
 // Per row: decoded lengths, whether the row enters the result in the inline phase, and the
 // first-seen chunk of its external values.
-__global__ void __launch_bounds__(256)
-k_plan_rows(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ toast,
-            const uint2 *__restrict__ dir_loc, const uint32_t *__restrict__ vfirst,
-            const uint32_t *__restrict__ vcount, const uint32_t *__restrict__ vseq0,
-            uint32_t *__restrict__ inline_flag, uint32_t *__restrict__ chunk_flag,
-            uint32_t *__restrict__ row_first, unsigned long long *__restrict__ ind_len,
-            unsigned long long *__restrict__ dep_len, unsigned long long *__restrict__ vscr, DevState *st)
+__device__ __forceinline__ void d_plan_rows(const PlanArgs &A)
 {
+    DevState *st = A.st;
     const uint32_t n_rows = st->n_rows;
     for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
-        const uint32_t *row = rows + (size_t)r * kRowWords;
+        const uint32_t *row = A.rows + (size_t)r * kRowWords;
         unsigned long long len[2] = {0, 0};
         uint32_t first = kNone;
         const bool usable = row[RW_INLINE_LEN] != kNone;
         const bool is_inline = usable && row[RW_DEP_EXTERNAL] == 0;
         for (uint32_t a = 0; a < 2; a++) {
             const uint32_t v = 2 * r + a;
-            vscr[v] = 0;
+            A.vscr[v] = 0;
             if (!usable) continue;
             const uint32_t *ptr = row + (a ? RW_DEP : RW_IND);
             if (a == 1 && is_inline) {
@@ -229,133 +263,118 @@ k_plan_rows(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ toast
                 len[1] = ptr[1];
                 continue;
             }
-            if (vcount[v] == 0) continue;                                   // value has no chunks
-            first = min(first, vfirst[v]);
+            if (A.vcount[v] == 0) continue;                                 // value has no chunks
+            first = min(first, A.vfirst[v]);
             const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
             if (va_extsize == va_rawsize - 4u) {
                 len[a] = va_extsize;                                         // stored uncompressed
             } else {
                 // compressed: rawsize is the first LE word of the stored payload (ppr:240, 574-594)
-                uint32_t g = vseq0[v];
+                uint32_t g = A.vseq0[v];
                 if (g != kNone) {
-                    uint2 loc = dir_loc[g];
+                    uint2 loc = A.dir_loc[g];
                     if ((loc.y >> 16) >= 4u)
-                        len[a] = ld_u32(toast + (size_t)loc.x * kPage + (loc.y & 0xFFFFu));
+                        len[a] = ld_u32(A.toast + (size_t)loc.x * kPage + (loc.y & 0xFFFFu));
                 }
-                vscr[v] = ((unsigned long long)va_extsize + 15ull) & ~15ull;
+                A.vscr[v] = ((unsigned long long)va_extsize + 15ull) & ~15ull;
             }
         }
-        ind_len[r] = len[0];
-        dep_len[r] = len[1];
-        inline_flag[r] = is_inline ? 1u : 0u;
-        row_first[r] = first;
-        if (!is_inline && first != kNone) chunk_flag[first] = 1u;
+        A.ind_len[r] = len[0];
+        A.dep_len[r] = len[1];
+        A.inline_flag[r] = is_inline ? 1u : 0u;
+        A.row_first[r] = first;
+        if (!is_inline && first != kNone) A.chunk_flag[first] = 1u;
     }
 }
 
-// blockIdx.y == 0: rank of inline rows (table order).  blockIdx.y == 1: rank of first-seen chunks.
-__global__ void __launch_bounds__(kScanThreads)
-k_plan_scan1(uint32_t *inline_flag, uint32_t *chunk_flag, DevState *st, ScanWs ws_rows, ScanWs ws_chunks)
+// which == 0: rank of inline rows (table order).  which == 1: rank of first-seen chunks.
+__device__ __forceinline__ void d_plan_scan1(const PlanArgs &A, int which)
 {
     bool last;
-    if (blockIdx.y == 0) {
-        const uint32_t tot = device_exclusive_scan<uint32_t, 8>([&](uint32_t i) { return inline_flag[i]; }, inline_flag,
-                                                             st->n_rows, ws_rows, false, &last);
-        if (last && threadIdx.x == 0) st->n_inline = tot;
+    if (which == 0) {
+        uint32_t *f = A.inline_flag;
+        const uint32_t tot = device_exclusive_scan<uint32_t, 8>([&](uint32_t i) { return f[i]; }, f, A.st->n_rows, A.ws[0], false, &last);
+        if (last && threadIdx.x == 0) A.st->n_inline = tot;
     } else {
-        device_exclusive_scan<uint32_t, 8>([&](uint32_t i) { return chunk_flag[i]; }, chunk_flag, st->n_chunks, ws_chunks,
-                                        true, &last);
+        uint32_t *f = A.chunk_flag;
+        device_exclusive_scan<uint32_t, 8>([&](uint32_t i) { return f[i]; }, f, A.st->n_chunks, A.ws[1], true, &last);
     }
 }
 
 // Result position of every row: inline rows first in table order (ppr:532-552), then rows in
 // the order their first external chunk is met (ppr:553-611; an existing entry keeps its place).
-__global__ void __launch_bounds__(256)
-k_assign_pos(const uint32_t *__restrict__ rows, const uint32_t *__restrict__ inline_rank,
-             const uint32_t *__restrict__ chunk_rank, const uint32_t *__restrict__ row_first,
-             const unsigned long long *__restrict__ ind_len, const unsigned long long *__restrict__ dep_len,
-             uint32_t *__restrict__ pos_of_row, uint32_t *__restrict__ row_at_pos,
-             unsigned long long *__restrict__ pos_ind, unsigned long long *__restrict__ pos_dep, DevState *st,
-             uint32_t isb, uint32_t dsb)
+__device__ __forceinline__ void d_assign_pos(const PlanArgs &A)
 {
+    DevState *st = A.st;
     const uint32_t n_rows = st->n_rows, n_inline = st->n_inline, n_chunks = st->n_chunks;
-    if (blockIdx.x == 0 && threadIdx.x == 0) st->n_pos = n_inline + chunk_rank[n_chunks];
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->n_pos = n_inline + A.chunk_flag[n_chunks];
     for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
-        const uint32_t *row = rows + (size_t)r * kRowWords;
+        const uint32_t *row = A.rows + (size_t)r * kRowWords;
         const bool usable = row[RW_INLINE_LEN] != kNone;
         const bool is_inline = usable && row[RW_DEP_EXTERNAL] == 0;
         uint32_t pos = kNone;
-        if (is_inline) pos = inline_rank[r];
-        else if (row_first[r] != kNone) pos = n_inline + chunk_rank[row_first[r]];
-        pos_of_row[r] = pos;
+        if (is_inline) pos = A.inline_flag[r];
+        else if (A.row_first[r] != kNone) pos = n_inline + A.chunk_flag[A.row_first[r]];
+        A.pos_of_row[r] = pos;
         if (pos == kNone) continue;     // no chunk of this row exists: the reference never emits it
-        row_at_pos[pos] = r;
-        pos_ind[pos] = ind_len[r];
-        pos_dep[pos] = dep_len[r];
-        if (ind_len[r] == 0 || dep_len[r] == 0) report(st, 4, pos, 0, 0, CDS_ERR_MISSING_VALUE);
-        if (isb && dsb && ind_len[r] && dep_len[r]) {
-            if (ind_len[r] % isb || dep_len[r] % dsb || ind_len[r] / isb != dep_len[r] / dsb)
-                report(st, 4, pos, 1, 0, CDS_ERR_SHAPE);
+        const unsigned long long il = A.ind_len[r], dl = A.dep_len[r];
+        A.row_at_pos[pos] = r;
+        A.pos_ind[pos] = il;
+        A.pos_dep[pos] = dl;
+        if (il == 0 || dl == 0) report(st, 4, pos, 0, 0, CDS_ERR_MISSING_VALUE);
+        if (A.isb && A.dsb && il && dl) {
+            if (il % A.isb || dl % A.dsb || il / A.isb != dl / A.dsb) report(st, 4, pos, 1, 0, CDS_ERR_SHAPE);
         }
     }
 }
 
-// Three independent 64-bit exclusive scans (blockIdx.y): output offsets of the two value streams in
-// result order, and staging offsets of compressed external values.
-__global__ void __launch_bounds__(kScanThreads)
-k_plan_scan2(unsigned long long *pos_ind, unsigned long long *pos_dep, unsigned long long *vscr, DevState *st,
-             ScanWs ws0, ScanWs ws1, ScanWs ws2)
+// Three independent 64-bit exclusive scans: output offsets of the two value streams in result order,
+// and staging offsets of compressed external values.
+__device__ __forceinline__ void d_plan_scan2(const PlanArgs &A, int which)
 {
     bool last;
-    if (blockIdx.y == 0) {
-        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>(
-            [&](uint32_t i) { return pos_ind[i]; }, pos_ind, st->n_pos, ws0, false, &last);
+    DevState *st = A.st;
+    if (which == 0) {
+        unsigned long long *x = A.pos_ind;
+        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>([&](uint32_t i) { return x[i]; }, x, st->n_pos, A.ws[2], false, &last);
         if (last && threadIdx.x == 0) st->ind_bytes = t;
-    } else if (blockIdx.y == 1) {
-        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>(
-            [&](uint32_t i) { return pos_dep[i]; }, pos_dep, st->n_pos, ws1, false, &last);
+    } else if (which == 1) {
+        unsigned long long *x = A.pos_dep;
+        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>([&](uint32_t i) { return x[i]; }, x, st->n_pos, A.ws[3], false, &last);
         if (last && threadIdx.x == 0) st->dep_bytes = t;
     } else {
-        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>(
-            [&](uint32_t i) { return vscr[i]; }, vscr, 2u * st->n_rows, ws2, false, &last);
+        unsigned long long *x = A.vscr;
+        const unsigned long long t = device_exclusive_scan<unsigned long long, 8>([&](uint32_t i) { return x[i]; }, x, 2u * st->n_rows, A.ws[4], false, &last);
         if (last && threadIdx.x == 0) st->scratch_bytes = t;
     }
 }
 
 // One thread per chunk: the reference's per-chunk checks (ppr:570-596) and the copy descriptor.
 // Also one pglz job per value (inline datums and compressed external values).
-__global__ void __launch_bounds__(256)
-k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
-          const uint2 *__restrict__ dir_id, const uint2 *__restrict__ dir_loc, const uint32_t *__restrict__ dir_ref,
-          const uint32_t *__restrict__ vfirst, const uint32_t *__restrict__ vcount,
-          const unsigned long long *__restrict__ vbytes, const unsigned long long *__restrict__ vscr,
-          const uint32_t *__restrict__ pos_of_row,
-          const unsigned long long *__restrict__ pos_ind, const unsigned long long *__restrict__ pos_dep,
-          unsigned long long *__restrict__ row_ind_off, unsigned long long *__restrict__ row_dep_off,
-          const unsigned long long *__restrict__ ind_len, const unsigned long long *__restrict__ dep_len,
-          uint8_t *out_ind, unsigned long long cap_ind, uint8_t *out_dep, unsigned long long cap_dep,
-          uint8_t *scratch, unsigned long long cap_scratch,
-          CopyOp *__restrict__ ops, PglzJob *__restrict__ jobs, DevState *st)
+__device__ __forceinline__ void d_resolve(const PlanArgs &A)
 {
+    DevState *st = A.st;
+    const uint32_t *rows = A.rows;
     const uint32_t n_chunks = st->n_chunks, n_rows = st->n_rows;
-    const bool fits = st->ind_bytes <= cap_ind && st->dep_bytes <= cap_dep && st->scratch_bytes <= cap_scratch;
+    const bool fits = st->ind_bytes <= A.cap_ind && st->dep_bytes <= A.cap_dep && st->scratch_bytes <= A.cap_scratch;
     if (!fits && blockIdx.x == 0 && threadIdx.x == 0) report(st, 4, 0, 2, 0, CDS_ERR_CAPACITY);
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
 
     for (uint32_t g = tid; g < n_chunks; g += nth) {
         CopyOp op;
         op.dst = 0; op.src_off = 0; op.len = 0;
-        const uint32_t ref = dir_ref[g];
+        const uint32_t ref = A.dir_ref[g];
         if (ref != kNone) {
             const uint32_t v = ref & 0x3FFFFFFFu, r = v >> 1, a = v & 1u;
             const uint32_t *ptr = rows + (size_t)r * kRowWords + (a ? RW_DEP : RW_IND);
             const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
             const uint32_t numchunks = va_extsize ? (va_extsize - 1u) / kChunkMax + 1u : 0u;   // ppr:155-156
-            const uint32_t first = vfirst[v];
-            const uint2 id = dir_id[g], loc = dir_loc[g];
+            const uint32_t first = A.vfirst[v];
+            const uint2 id = A.dir_id[g], loc = A.dir_loc[g];
             const uint32_t idx = id.y, size = loc.y >> 16;
+            const unsigned long long vb = A.vbytes[v];
             bool ok = true;
-            if (vcount[v] != numchunks) {                                   // ppr:570-572
+            if (A.vcount[v] != numchunks) {                                 // ppr:570-572
                 if (g == first) report(st, 3, first, 0, 0, CDS_ERR_CHUNK_COUNT);
                 ok = false;
             }
@@ -364,19 +383,19 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
             if (numchunks && idx < numchunks - 1u && size != kChunkMax) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_SIZE); ok = false; }   // ppr:587-588
             if (numchunks && idx == numchunks - 1u && (unsigned long long)idx * kChunkMax + size != va_extsize) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_SIZE); ok = false; }   // ppr:589-591
             if (idx >= numchunks) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_SIZE); ok = false; }   // outside the pointer's extent
-            if (g == first && vbytes[v] != va_extsize) { report(st, 3, first, 2, 0, CDS_ERR_FINAL_SIZE); }  // ppr:595-596
-            if (ok && vbytes[v] == va_extsize && fits && pos_of_row[r] != kNone) {
+            if (g == first && vb != va_extsize) { report(st, 3, first, 2, 0, CDS_ERR_FINAL_SIZE); }  // ppr:595-596
+            const uint32_t pos = A.pos_of_row[r];
+            if (ok && vb == va_extsize && fits && pos != kNone) {
                 const bool compressed = va_extsize != va_rawsize - 4u;
                 unsigned long long dst;
-                const uint32_t pos = pos_of_row[r];
-                if (compressed) dst = (unsigned long long)(scratch + vscr[v]);
-                else dst = a ? (unsigned long long)(out_dep + pos_dep[pos]) : (unsigned long long)(out_ind + pos_ind[pos]);
+                if (compressed) dst = (unsigned long long)(A.scratch + A.vscr[v]);
+                else dst = a ? (unsigned long long)(A.out_dep + A.pos_dep[pos]) : (unsigned long long)(A.out_ind + A.pos_ind[pos]);
                 op.dst = dst + (unsigned long long)idx * kChunkMax;
                 op.src_off = loc.y & 0xFFFFu;
                 op.len = size;
             }
         }
-        ops[g] = op;
+        A.ops[g] = op;
     }
 
     // pglz jobs are compacted: independent_var jobs (large) grow from slot 0 upward, dependent_var jobs (small)
@@ -387,14 +406,14 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
         job.src = 0; job.dst = 0; job.slen = kNone; job.rawsize = 0; job.err_key = 0;
         const uint32_t r = v >> 1, a = v & 1u;
         const uint32_t *row = rows + (size_t)r * kRowWords;
-        const uint32_t pos = pos_of_row[r];
-        const unsigned long long my_ind_off = pos == kNone ? ~0ull : pos_ind[pos];
-        const unsigned long long my_dep_off = pos == kNone ? ~0ull : pos_dep[pos];
-        if (a == 0) { row_ind_off[r] = my_ind_off; row_dep_off[r] = my_dep_off; }   // exported to the host mirror
+        const uint32_t pos = A.pos_of_row[r];
+        const unsigned long long my_ind_off = pos == kNone ? ~0ull : A.pos_ind[pos];
+        const unsigned long long my_dep_off = pos == kNone ? ~0ull : A.pos_dep[pos];
+        if (a == 0) { A.row_ind_off[r] = my_ind_off; A.row_dep_off[r] = my_dep_off; }   // exported to the host mirror
         if (fits && pos != kNone && row[RW_INLINE_LEN] != kNone) {
             if (a == 1 && row[RW_DEP_EXTERNAL] == 0) {
                 // inline datum: tupdata[24:] starts with the 8-byte PGLZ header (ppr:344, 537-543)
-                const uint8_t *src = heap + (((unsigned long long)row[RW_INLINE_OFF_HI] << 32) | row[RW_INLINE_OFF_LO]);
+                const uint8_t *src = A.heap + (((unsigned long long)row[RW_INLINE_OFF_HI] << 32) | row[RW_INLINE_OFF_LO]);
                 const uint32_t avail = row[RW_INLINE_LEN];
                 const uint32_t varsize = ld_u32be(src) & 0x3FFFFFFFu;
                 job.err_key = make_err_key(2, r, 0, 0, CDS_ERR_PGLZ_CORRUPT);
@@ -403,31 +422,54 @@ k_resolve(const uint32_t *__restrict__ rows, const uint8_t *__restrict__ heap,
                 } else {
                     job.src = (unsigned long long)(src + 8);
                     job.slen = varsize - 8u;
-                    job.rawsize = (uint32_t)dep_len[r];
-                    job.dst = (unsigned long long)(out_dep + my_dep_off);
+                    job.rawsize = (uint32_t)A.dep_len[r];
+                    job.dst = (unsigned long long)(A.out_dep + my_dep_off);
                 }
-            } else if (vcount[v] != 0) {
+            } else if (A.vcount[v] != 0) {
                 const uint32_t *ptr = row + (a ? RW_DEP : RW_IND);
                 const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
                 if (va_extsize != va_rawsize - 4u) {
-                    const unsigned long long len = a ? dep_len[r] : ind_len[r];
-                    job.err_key = make_err_key(3, vfirst[v], 3, 0, CDS_ERR_PGLZ_CORRUPT);
+                    const unsigned long long len = a ? A.dep_len[r] : A.ind_len[r];
+                    job.err_key = make_err_key(3, A.vfirst[v], 3, 0, CDS_ERR_PGLZ_CORRUPT);
                     if (va_extsize < 4u) {
                         report_key(st, job.err_key);
                     } else {
                         // staged payload = LE rawsize + stream (ppr:574-594 builds header + payload)
-                        job.src = (unsigned long long)(scratch + vscr[v] + 4);
+                        job.src = (unsigned long long)(A.scratch + A.vscr[v] + 4);
                         job.slen = va_extsize - 4u;
                         job.rawsize = (uint32_t)len;
-                        job.dst = a ? (unsigned long long)(out_dep + my_dep_off) : (unsigned long long)(out_ind + my_ind_off);
+                        job.dst = a ? (unsigned long long)(A.out_dep + my_dep_off) : (unsigned long long)(A.out_ind + my_ind_off);
                     }
                 }
             }
         }
         if (job.slen != kNone) {
-            if (a == 0) jobs[atomicAdd(&st->n_jobs_front, 1u)] = job;
-            else jobs[last_slot - atomicAdd(&st->n_jobs_back, 1u)] = job;
+            if (a == 0) A.jobs[atomicAdd(&st->n_jobs_front, 1u)] = job;
+            else A.jobs[last_slot - atomicAdd(&st->n_jobs_back, 1u)] = job;
         }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_plan_rows(const PlanArgs A) { d_plan_rows(A); }
+__global__ void __launch_bounds__(kScanThreads) k_plan_scan1(const PlanArgs A) { d_plan_scan1(A, (int)blockIdx.y); }
+__global__ void __launch_bounds__(256) k_assign_pos(const PlanArgs A) { d_assign_pos(A); }
+__global__ void __launch_bounds__(kScanThreads) k_plan_scan2(const PlanArgs A) { d_plan_scan2(A, (int)blockIdx.y); }
+__global__ void __launch_bounds__(256) k_resolve(const PlanArgs A) { d_resolve(A); }
+
+// All phases in one cooperative launch (every block resident, grid-wide barriers between phases).
+__global__ void __launch_bounds__(256) k_plan_fused(const PlanArgs A, int do_resolve)
+{
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    d_plan_rows(A);
+    grid.sync();
+    d_plan_scan1(A, (int)(blockIdx.x & 1u));          // the two rank scans side by side
+    grid.sync();
+    d_assign_pos(A);
+    grid.sync();
+    d_plan_scan2(A, (int)(blockIdx.x % 3u));          // the three offset scans side by side
+    if (do_resolve) {
+        grid.sync();
+        d_resolve(A);
     }
 }
 
