@@ -93,6 +93,28 @@ __device__ __forceinline__ uint32_t win_fetch(SrcWindow &w, uint32_t sp, uint32_
     return ((rel < 128u ? a : b) >> ((rel & 3u) * 8u)) & 0xFFu;
 }
 
+// Source bytes sp + lane (returned) and sp + 32 + lane (`second`); same caveat past the end of the stream.
+__device__ __forceinline__ uint32_t win_fetch2(SrcWindow &w, uint32_t sp, uint32_t lane, uint32_t &second)
+{
+    const uint32_t y = sp + w.mis, kk = y >> 7;
+    if (kk != w.k) {
+        if (kk == w.k + 1u) {
+            w.cur = w.nxt;
+            w.k = kk;
+            w.nxt = win_word(w, 32u * (kk + 1u) + lane);      // needed 128 source bytes from now
+        } else {
+            win_seek(w, sp, lane);
+        }
+    }
+    const uint32_t rel = (y & 127u) + lane, rel2 = rel + 32u;   // < 160, < 192: inside cur + nxt
+    const uint32_t a = __shfl_sync(0xffffffffu, w.cur, (rel >> 2) & 31u);
+    const uint32_t b = __shfl_sync(0xffffffffu, w.nxt, (rel >> 2) & 31u);
+    const uint32_t c = __shfl_sync(0xffffffffu, w.cur, (rel2 >> 2) & 31u);
+    const uint32_t d = __shfl_sync(0xffffffffu, w.nxt, (rel2 >> 2) & 31u);
+    second = ((rel2 < 128u ? c : d) >> ((rel2 & 3u) * 8u)) & 0xFFu;
+    return ((rel < 128u ? a : b) >> ((rel & 3u) * 8u)) & 0xFFu;
+}
+
 // The three aligned words that cover the 9 source bytes of the group at sp + 9*lane.
 __device__ __forceinline__ void lit_load(const SrcWindow &w, uint32_t sp, uint32_t lane, uint32_t &w0, uint32_t &w1, uint32_t &w2)
 {
@@ -102,6 +124,97 @@ __device__ __forceinline__ void lit_load(const SrcWindow &w, uint32_t sp, uint32
     w2 = win_word(w, i0 + 2u);
 }
 
+// Expand up to 32 items, one per lane (lane i < nitems holds item i in stream order: a literal with
+// its byte in `litbyte`, or a match (len, moff)).  Checks every item the way the reference would meet
+// it; returns false when the datum is corrupt.  When the items produce more than `max_total` bytes
+// nothing is written and *too_big is set.  Otherwise the bytes land in the ring and dp advances.
+__device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match, uint32_t len, uint32_t moff,
+                                                  uint32_t litbyte, uint32_t &dp, uint32_t rawsize, uint8_t *ring,
+                                                  uint32_t shift, uint32_t lane, uint32_t max_total, bool *too_big)
+{
+    const bool is_item = lane < nitems;
+    is_match = is_match && is_item;
+    const uint32_t olen = is_item ? (is_match ? len : 1u) : 0u;
+    uint32_t incl = olen;                                                    // inclusive scan of output lengths
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= (uint32_t)d) incl += o;
+    }
+    const uint32_t my_o = incl - olen;                                       // output offset of my item in this step
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    *too_big = total > max_total;
+    if (*too_big) return true;
+    // Any item the reference would refuse ends in "corrupt" (ppr:213-215, 221-222 then 229-230):
+    // a literal or a match that does not fit the output, offset 0, offset before the output start.
+    const bool bad = is_item && ((dp + my_o + olen > rawsize) || (is_match && (moff == 0u || moff > dp + my_o)));
+    if (__ballot_sync(0xffffffffu, bad)) return false;
+
+    if (total <= 128u) {
+        // ---- short items: one lane per output byte, 32 bytes per step
+        const uint32_t pack = moff | (len << 12) | ((is_match ? 1u : 0u) << 21);
+        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+            const uint32_t c0 = __popc(__ballot_sync(0xffffffffu, is_item && my_o <= t0));
+            const uint32_t starts = __reduce_or_sync(0xffffffffu, (is_item && my_o > t0 && my_o < t0 + 32u) ? (1u << (my_o - t0)) : 0u);
+            const uint32_t k = (c0 - 1u + __popc(starts & ((2u << lane) - 1u))) & 31u;
+            const uint32_t kp = __shfl_sync(0xffffffffu, pack, k);
+            const uint32_t ko = __shfl_sync(0xffffffffu, my_o, k);
+            const uint32_t lit = __shfl_sync(0xffffffffu, litbyte, k);
+            const uint32_t t = t0 + lane;
+            const bool live = t < total;
+            bool resolved = true;
+            uint32_t val = lit, srcl = 0;
+            if (live && ((kp >> 21) & 1u)) {
+                const uint32_t kmoff = kp & 0xFFFu, klen = (kp >> 12) & 0x1FFu;
+                uint32_t j = t - ko;
+                if (kmoff < klen) j %= kmoff;                                // overlapping copy (ppr:216-219)
+                const uint32_t spos = dp + ko - kmoff + j;                   // absolute output position of the source byte
+                if (spos >= dp + t0) { resolved = false; srcl = spos - (dp + t0); }   // produced in this very step
+                else val = ring[(spos + shift) & (kRing - 1)];
+            }
+            for (;;) {                                                       // chase sources inside the step
+                const uint32_t r = __ballot_sync(0xffffffffu, resolved);
+                if (r == 0xffffffffu) break;
+                const uint32_t v = __shfl_sync(0xffffffffu, val, srcl);
+                if (!resolved && ((r >> srcl) & 1u)) { val = v; resolved = true; }
+            }
+            if (live) ring[(dp + t + shift) & (kRing - 1)] = (uint8_t)val;
+            __syncwarp();
+        }
+    } else {
+        // ---- long matches: item after item, 32 bytes per step and item
+        const uint32_t mbits = __ballot_sync(0xffffffffu, is_match);
+        for (uint32_t k = 0; k < nitems; k++) {
+            const uint32_t at = dp + __shfl_sync(0xffffffffu, my_o, k);
+            if ((mbits >> k) & 1u) {
+                const uint32_t klen = __shfl_sync(0xffffffffu, len, k), kmoff = __shfl_sync(0xffffffffu, moff, k);
+                if (kmoff >= klen) {
+                    for (uint32_t i = lane; i < klen; i += 32)
+                        ring[(at + i + shift) & (kRing - 1)] = ring[(at - kmoff + i + shift) & (kRing - 1)];
+                } else if (kmoff == 1u) {
+                    // run of one byte value (zero runs of sparse features): fill with aligned 32-bit stores
+                    const uint32_t v = ring[(at - 1u + shift) & (kRing - 1)] * 0x01010101u;
+                    const uint32_t a0 = at + shift, head = min(klen, (4u - (a0 & 3u)) & 3u);
+                    if (lane < head) ring[(a0 + lane) & (kRing - 1)] = (uint8_t)v;
+                    const uint32_t nw = (klen - head) >> 2, w0 = a0 + head;
+                    for (uint32_t i = lane; i < nw; i += 32)
+                        *reinterpret_cast<uint32_t *>(ring + ((w0 + 4u * i) & (kRing - 1))) = v;
+                    const uint32_t t0 = head + 4u * nw;
+                    if (lane < klen - t0) ring[(a0 + t0 + lane) & (kRing - 1)] = (uint8_t)v;
+                } else {
+                    for (uint32_t i = lane; i < klen; i += 32)
+                        ring[(at + i + shift) & (kRing - 1)] = ring[(at - kmoff + (i % kmoff) + shift) & (kRing - 1)];
+                }
+            } else if (lane == k) {
+                ring[(at + shift) & (kRing - 1)] = (uint8_t)litbyte;
+            }
+            __syncwarp();
+        }
+    }
+    dp += total;
+    return true;
+}
+
 // Decode one datum with the calling warp.  Returns true when the stream is well-formed.
 __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen, uint8_t *dst, uint32_t rawsize,
                                  uint8_t *ring)
@@ -109,6 +222,7 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t shift = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
     uint32_t sp = 0, dp = 0, flushed = 0;
+    uint32_t wide_pause = 0, wide_backoff = 4;                               // steps to stay on the one-group path
     bool corrupt = false;
 
     SrcWindow win;
@@ -118,8 +232,9 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
     win_seek(win, 0, lane);
 
     while (sp < slen && dp < rawsize && !corrupt) {
-        // ---- one control group: lane l holds source byte sp + l ----------------------------
-        const uint32_t fetched = win_fetch(win, sp, lane);
+        // ---- lane l holds source bytes sp + l (and sp + 32 + l for the wide step) ---------------
+        uint32_t byte1;
+        const uint32_t fetched = win_fetch2(win, sp, lane, byte1);
         const bool inb = sp + lane < slen;
         const uint32_t byte = inb ? fetched : 0u;
         const uint32_t ctrl = __shfl_sync(0xffffffffu, byte, 0);
@@ -169,102 +284,92 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
             continue;
         }
 
-        // ---- item walk of the group: register-only and identical in all lanes.  Item k starts at
-        //      source offset p_k inside the group; lane k keeps p_k (ppr:203-228 restated).
-        const uint32_t extmask = __ballot_sync(0xffffffffu, (byte & 0x0Fu) == 0x0Fu);
-        const uint32_t n_avail = min(32u, slen - sp);                        // a group is at most 25 bytes
-        uint32_t pnext = 1, my_p = 0, nitems = 0;
+        bool stepped = false;
+        if (slen - sp >= 64u && wide_pause == 0) {
+            // ---- wide step: up to four whole groups (32 items) at once.  Lane 8g+k owns item k of group g.
+            // Item positions depend on which earlier tags carry a length-extension byte; start from
+            // "none do" and iterate to the fixed point (exact once the ext mask reproduces itself).
+            const uint32_t W = byte | (byte1 << 8);                          // source bytes sp+lane, sp+32+lane
+            const uint32_t e_lo = __ballot_sync(0xffffffffu, (byte & 0x0Fu) == 0x0Fu);
+            const uint32_t e_hi = __ballot_sync(0xffffffffu, (byte1 & 0x0Fu) == 0x0Fu);
+            const uint32_t g = lane >> 3, k = lane & 7u, below = (1u << k) - 1u;
+            uint32_t M = 0, my_p = 0, my_bit = 0, ng = 0, consumed = 0;
+            bool conv = false;
+            for (int it = 0; it < 4 && !conv; it++) {
+                uint32_t S = 0, myS = 0, myC = 0;
+                ng = 0;
 #pragma unroll
-        for (uint32_t k = 0; k < 8; k++) {
-            if (pnext < n_avail) {                                           // `sp < srcend` of the inner loop
-                const uint32_t sz = ((ctrl >> k) & 1u) ? 2u + ((extmask >> pnext) & 1u) : 1u;
-                if (lane == k) my_p = pnext;
-                pnext += sz;
-                nitems = k + 1;
-            }
-        }
-        if (pnext > n_avail) { corrupt = true; break; }                      // a tag runs past the source
-
-        // ---- lane k decodes item k
-        const uint32_t b0 = __shfl_sync(0xffffffffu, byte, my_p);
-        const uint32_t b1 = __shfl_sync(0xffffffffu, byte, (my_p + 1u) & 31u);
-        const uint32_t b2 = __shfl_sync(0xffffffffu, byte, (my_p + 2u) & 31u);
-        const bool is_item = lane < nitems;
-        const bool is_match = is_item && ((ctrl >> lane) & 1u);
-        uint32_t len = 1, moff = 0;
-        if (is_match) {
-            len = (b0 & 0x0Fu) + 3u;                                         // ppr:205
-            moff = ((b0 & 0xF0u) << 4) | b1;                                 // ppr:206-208
-            if ((b0 & 0x0Fu) == 0x0Fu) len += b2;                            // ppr:210-212
-        }
-        const uint32_t olen = is_item ? len : 0u;
-        uint32_t incl = olen;                                                // inclusive scan over the 8 item lanes
-#pragma unroll
-        for (int d = 1; d < 8; d <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= (uint32_t)d) incl += o;
-        }
-        const uint32_t my_o = incl - olen;                                   // output offset of my item in the group
-        const uint32_t total = __shfl_sync(0xffffffffu, incl, 7);
-        // Any item the reference would refuse ends in "corrupt" (ppr:213-215, 221-222 then 229-230):
-        // a literal or a match that does not fit the output, offset 0, offset before the output start.
-        const bool bad = is_item && ((dp + my_o + olen > rawsize) || (is_match && (moff == 0u || moff > dp + my_o)));
-        if (__ballot_sync(0xffffffffu, bad)) { corrupt = true; break; }
-
-        if (total <= 64u) {
-            // ---- short items: one lane per output byte, 32 bytes per step
-            const uint32_t pack = moff | (len << 12) | (my_p << 21) | ((is_match ? 1u : 0u) << 26);
-            for (uint32_t t0 = 0; t0 < total; t0 += 32) {
-                const uint32_t c0 = __popc(__ballot_sync(0xffffffffu, is_item && my_o <= t0));
-                const uint32_t starts = __reduce_or_sync(0xffffffffu, (is_item && my_o > t0 && my_o < t0 + 32u) ? (1u << (my_o - t0)) : 0u);
-                const uint32_t k = c0 - 1u + __popc(starts & ((2u << lane) - 1u));
-                const uint32_t kp = __shfl_sync(0xffffffffu, pack, k & 31u);
-                const uint32_t ko = __shfl_sync(0xffffffffu, my_o, k & 31u);
-                const uint32_t lit = __shfl_sync(0xffffffffu, byte, (kp >> 21) & 31u);
-                const uint32_t t = t0 + lane;
-                const bool live = t < total;
-                const bool m = (kp >> 26) & 1u;
-                bool resolved = true;
-                uint32_t val = lit, srcl = 0;
-                if (live && m) {
-                    const uint32_t kmoff = kp & 0xFFFu, klen = (kp >> 12) & 0x1FFu;
-                    uint32_t j = t - ko;
-                    if (kmoff < klen) j %= kmoff;                            // overlapping copy (ppr:216-219)
-                    const uint32_t spos = dp + ko - kmoff + j;               // absolute output position of the source byte
-                    if (spos >= dp + t0) { resolved = false; srcl = spos - (dp + t0); }   // produced in this very step
-                    else val = ring[(spos + shift) & (kRing - 1)];
-                }
-                for (;;) {                                                   // chase sources inside the step
-                    const uint32_t r = __ballot_sync(0xffffffffu, resolved);
-                    if (r == 0xffffffffu) break;
-                    const uint32_t v = __shfl_sync(0xffffffffu, val, srcl);
-                    if (!resolved && ((r >> srcl) & 1u)) { val = v; resolved = true; }
-                }
-                if (live) ring[(dp + t + shift) & (kRing - 1)] = (uint8_t)val;
-                __syncwarp();
-            }
-        } else {
-            // ---- long matches: item after item, 32 bytes per step and item
-            for (uint32_t k = 0; k < nitems; k++) {
-                const uint32_t klen = __shfl_sync(0xffffffffu, len, k), kmoff = __shfl_sync(0xffffffffu, moff, k);
-                const uint32_t ko = __shfl_sync(0xffffffffu, my_o, k), kpp = __shfl_sync(0xffffffffu, my_p, k);
-                const uint32_t at = dp + ko;
-                if ((ctrl >> k) & 1u) {
-                    if (kmoff >= klen) {
-                        for (uint32_t i = lane; i < klen; i += 32)
-                            ring[(at + i + shift) & (kRing - 1)] = ring[(at - kmoff + i + shift) & (kRing - 1)];
-                    } else {
-                        for (uint32_t i = lane; i < klen; i += 32)
-                            ring[(at + i + shift) & (kRing - 1)] = ring[(at - kmoff + (i % kmoff) + shift) & (kRing - 1)];
+                for (uint32_t gg = 0; gg < 4; gg++) {
+                    if (ng == gg && S <= 39u) {                              // the whole group lies inside the 64 bytes
+                        const uint32_t c = (__shfl_sync(0xffffffffu, W, S & 31u) >> ((S >> 5) * 8u)) & 0xFFu;
+                        if (g == gg) { myS = S; myC = c; }
+                        S += 9u + __popc(c) + __popc((M >> (8u * gg)) & 0xFFu);
+                        ng = gg + 1u;
                     }
-                } else if (lane == kpp) {
-                    ring[(at + shift) & (kRing - 1)] = (uint8_t)byte;
                 }
-                __syncwarp();
+                consumed = S;
+                my_bit = (myC >> k) & 1u;
+                my_p = myS + 1u + k + __popc(myC & below) + __popc((M >> (8u * g)) & below);
+                const uint32_t ebit = ((my_p < 32u ? e_lo : e_hi) >> (my_p & 31u)) & 1u;
+                const uint32_t M2 = __ballot_sync(0xffffffffu, g < ng && my_bit && ebit);
+                conv = (M2 == M);
+                M = M2;
             }
+            if (conv) {
+                const uint32_t w0 = __shfl_sync(0xffffffffu, W, my_p & 31u);
+                const uint32_t w1 = __shfl_sync(0xffffffffu, W, (my_p + 1u) & 31u);
+                const uint32_t w2 = __shfl_sync(0xffffffffu, W, (my_p + 2u) & 31u);
+                const uint32_t b0 = (w0 >> ((my_p >> 5) * 8u)) & 0xFFu;
+                const uint32_t b1 = (w1 >> (((my_p + 1u) >> 5) * 8u)) & 0xFFu;
+                const uint32_t b2 = (w2 >> (((my_p + 2u) >> 5) * 8u)) & 0xFFu;
+                uint32_t len = (b0 & 0x0Fu) + 3u;                            // ppr:205
+                const uint32_t moff = ((b0 & 0xF0u) << 4) | b1;              // ppr:206-208
+                if ((b0 & 0x0Fu) == 0x0Fu) len += b2;                        // ppr:210-212
+                bool too_big;
+                if (!pglz_expand_items(8u * ng, my_bit != 0u, len, moff, b0, dp, rawsize, ring, shift, lane, 2048u, &too_big)) {
+                    corrupt = true;
+                    break;
+                }
+                if (!too_big) { sp += consumed; stepped = true; wide_backoff = 4; }
+            }
+            if (!stepped) {                                                  // long matches / many extension bytes here:
+                wide_pause = wide_backoff;                                   // stay narrow for a while, longer each time
+                wide_backoff = min(wide_backoff * 2u, 1024u);
+            }
+        } else if (wide_pause) {
+            wide_pause--;
         }
-        sp += pnext;
-        dp += total;
+
+        if (!stepped) {
+            // ---- one group.  Item walk: register-only and identical in all lanes; item k starts at source
+            //      offset p_k inside the group and lane k keeps p_k (ppr:203-228 restated).
+            const uint32_t extmask = __ballot_sync(0xffffffffu, (byte & 0x0Fu) == 0x0Fu);
+            const uint32_t n_avail = min(32u, slen - sp);                    // a group is at most 25 bytes
+            uint32_t pnext = 1, my_p = 0, nitems = 0;
+#pragma unroll
+            for (uint32_t k = 0; k < 8; k++) {
+                if (pnext < n_avail) {                                       // `sp < srcend` of the inner loop
+                    const uint32_t sz = ((ctrl >> k) & 1u) ? 2u + ((extmask >> pnext) & 1u) : 1u;
+                    if (lane == k) my_p = pnext;
+                    pnext += sz;
+                    nitems = k + 1;
+                }
+            }
+            if (pnext > n_avail) { corrupt = true; break; }                  // a tag runs past the source
+            const uint32_t b0 = __shfl_sync(0xffffffffu, byte, my_p);
+            const uint32_t b1 = __shfl_sync(0xffffffffu, byte, (my_p + 1u) & 31u);
+            const uint32_t b2 = __shfl_sync(0xffffffffu, byte, (my_p + 2u) & 31u);
+            uint32_t len = (b0 & 0x0Fu) + 3u;                                // ppr:205
+            const uint32_t moff = ((b0 & 0xF0u) << 4) | b1;                  // ppr:206-208
+            if ((b0 & 0x0Fu) == 0x0Fu) len += b2;                            // ppr:210-212
+            bool too_big;
+            if (!pglz_expand_items(nitems, ((ctrl >> lane) & 1u) != 0u, len, moff, b0, dp, rawsize, ring, shift, lane,
+                                   0xFFFFFFFFu, &too_big)) {
+                corrupt = true;
+                break;
+            }
+            sp += pnext;
+        }
         if (dp - flushed >= kFlushAt) {
             const uint32_t to = dp - ((dp + shift) & 15u);
             pglz_flush(ring, dst, shift, flushed, to, lane);
