@@ -271,9 +271,11 @@ def run_ours(args):
         rank, meta["rows"], heap_pages, toast_pages, seg.toast.size / 2 ** 20, time.time() - t_gen))
 
     ds = segment.DeviceSegment(heap_pages, toast_pages, device=local, stage=True)
+    bf16 = args.out_dtype == "bf16"
+    ds.set_output_format(bf16)
     d_heap = torch.from_numpy(seg.heap).cuda()
     d_toast = torch.from_numpy(seg.toast).cuda()
-    out_ind = torch.empty(meta["ind_bytes"], dtype=torch.uint8, device="cuda")
+    out_ind = torch.empty(meta["ind_bytes"] // (2 if bf16 else 1), dtype=torch.uint8, device="cuda")
     out_dep = torch.empty(meta["dep_bytes"], dtype=torch.uint8, device="cuda")
     onehot = out_dep.view(torch.int16).view(-1, meta["classes"])
     labels = torch.empty(meta["samples"], dtype=torch.int64, device="cuda")
@@ -381,9 +383,10 @@ def run_ours(args):
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s (B200_PROFILING.md)"
         # algorithmic bytes, SURVEY.md §8(d): every input page once + every output byte once
-        step_bytes = seg.heap.size + seg.toast.size + meta["ind_bytes"] + meta["dep_bytes"] + 8 * meta["rows"]
+        ind_out = meta["ind_bytes"] // (2 if bf16 else 1)
+        step_bytes = seg.heap.size + seg.toast.size + ind_out + meta["dep_bytes"] + 8 * meta["rows"]
         # the gather kernel: reads the TOAST file once, writes every byte that is stored externally
-        gather_out = meta["ind_bytes"] + (meta["dep_bytes"] if args.workload == "imagenet_raw" else 0)
+        gather_out = ind_out + (meta["dep_bytes"] if args.workload == "imagenet_raw" else 0)
         if args.workload != "imagenet_raw":
             gather_out = int(seg.stored_bytes)          # compressed payloads go to the staging area
         gather_bytes = seg.toast.size + gather_out
@@ -402,7 +405,7 @@ def run_ours(args):
         line = {
             "metric": "decoded_rows_per_s", "value": rows_total / (dev_ms_max / 1000.0), "unit": "rows/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms_max,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8" if not bf16 else "u8->bf16", "data": "synthetic",
             "gb_per_s": world * step_bytes / (dev_ms_max / 1000.0) / 1e9,
             "hbm_frac_whole_step": step_bytes / (dev_ms_max / 1000.0) / 1e9 / peak,
             "config": {"workload": args.workload, "description": meta["desc"], "rows_per_segment": meta["rows"],
@@ -439,6 +442,8 @@ def main():
     ap.add_argument("--workload", default="imagenet_raw", choices=["imagenet_raw", "imagenet_pglz", "criteo"])
     ap.add_argument("--toast-mib", type=int, default=1024, help="TOAST file size per segment (config: 1 GiB)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--out-dtype", default="f32", choices=["f32", "bf16"],
+                    help="independent_var output: f32 = the reference's bits (default); bf16 = fused conversion (extra, not the metric)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -42,17 +42,19 @@ struct DevState {
 };
 
 // One TOAST chunk -> one copy.  dst == 0: chunk not referenced (or refused); nothing is copied.
+constexpr uint32_t kJobToBf16 = 0x80000000u;  // PglzJob.slen flag, same meaning
+constexpr uint32_t kOpToBf16 = 0x80000000u;   // CopyOp.len flag: payload is float32, destination is bfloat16
 struct __align__(16) CopyOp {
     unsigned long long dst;   // absolute device address
     uint32_t src_off;         // payload offset inside its page
-    uint32_t len;             // payload bytes
+    uint32_t len;             // payload bytes (| kOpToBf16)
 };
 
 // One pglz datum.  slen == kNone: empty slot.
 struct __align__(16) PglzJob {
     unsigned long long src;       // first stream byte (after the 8-byte header / 4-byte rawsize)
     unsigned long long dst;
-    uint32_t slen;                // stream bytes
+    uint32_t slen;                // stream bytes (| kJobToBf16: decoded float32 leaves as bfloat16)
     uint32_t rawsize;             // bytes to produce
     unsigned long long err_key;   // key to publish when the stream is corrupt (0: none)
 };

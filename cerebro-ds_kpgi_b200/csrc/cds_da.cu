@@ -43,6 +43,7 @@ struct cds_segment {
     uint64_t n_heap_pages = 0, n_toast_pages = 0;
     bool have_rows = false, have_chunks = false, have_plan = false, have_ops = false;
     int coop_blocks = 0;            // co-resident grid for k_plan_fused (0: cooperative launch unavailable)
+    int ind_bf16 = 0;               // cds_set_output_format: independent_var leaves as bfloat16
     // device buffers
     uint8_t *stage_heap = nullptr, *stage_toast = nullptr;
     uint32_t *heap_base = nullptr, *toast_base = nullptr, *rows = nullptr;
@@ -222,6 +223,13 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
     return CDS_OK;
 }
 
+extern "C" int cds_set_output_format(cds_segment *s, int independent_var_format)
+{
+    if (!s || (independent_var_format != 0 && independent_var_format != 1)) return CDS_ERR_ARG;
+    s->ind_bf16 = independent_var_format;
+    return CDS_OK;
+}
+
 // ---- steps -------------------------------------------------------------------------------------
 
 static inline uint32_t small_grid(const cds_segment *s) { return (uint32_t)s->num_sms * 4u; }
@@ -324,7 +332,7 @@ static PlanArgs plan_args(cds_segment *s, uint32_t isb, uint32_t dsb, void *out_
     A.row_ind_off = s->row_ind_off; A.row_dep_off = s->row_dep_off;
     A.ops = s->ops; A.jobs = s->jobs; A.st = s->state;
     for (int i = 0; i < 5; i++) A.ws[i] = s->ws[2 + i];
-    A.isb = isb; A.dsb = dsb;
+    A.isb = isb; A.dsb = dsb; A.ind_bf16 = (uint32_t)s->ind_bf16;
     A.out_ind = static_cast<uint8_t *>(out_ind); A.out_dep = static_cast<uint8_t *>(out_dep); A.scratch = s->scratch;
     A.cap_ind = ind_cap; A.cap_dep = dep_cap; A.cap_scratch = s->cap_scratch;
     return A;

@@ -237,6 +237,7 @@ struct PlanArgs {
     DevState *st;
     ScanWs ws[5];                 // inline rank, chunk rank, ind offsets, dep offsets, staging offsets
     uint32_t isb, dsb;            // sample sizes for the shape check (0: none)
+    uint32_t ind_bf16;            // independent_var leaves as bfloat16 (stored float32): output offsets are halved
     uint8_t *out_ind, *out_dep, *scratch;
     unsigned long long cap_ind, cap_dep, cap_scratch;
 };
@@ -356,7 +357,8 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
     DevState *st = A.st;
     const uint32_t *rows = A.rows;
     const uint32_t n_chunks = st->n_chunks, n_rows = st->n_rows;
-    const bool fits = st->ind_bytes <= A.cap_ind && st->dep_bytes <= A.cap_dep && st->scratch_bytes <= A.cap_scratch;
+    const uint32_t half = A.ind_bf16 ? 1u : 0u;                             // bf16 output: byte offsets / 2
+    const bool fits = (st->ind_bytes >> half) <= A.cap_ind && st->dep_bytes <= A.cap_dep && st->scratch_bytes <= A.cap_scratch;
     if (!fits && blockIdx.x == 0 && threadIdx.x == 0) report(st, 4, 0, 2, 0, CDS_ERR_CAPACITY);
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
 
@@ -388,11 +390,21 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
             if (ok && vb == va_extsize && fits && pos != kNone) {
                 const bool compressed = va_extsize != va_rawsize - 4u;
                 unsigned long long dst;
-                if (compressed) dst = (unsigned long long)(A.scratch + A.vscr[v]);
-                else dst = a ? (unsigned long long)(A.out_dep + A.pos_dep[pos]) : (unsigned long long)(A.out_ind + A.pos_ind[pos]);
-                op.dst = dst + (unsigned long long)idx * kChunkMax;
                 op.src_off = loc.y & 0xFFFFu;
                 op.len = size;
+                if (compressed) {
+                    op.dst = (unsigned long long)(A.scratch + A.vscr[v]) + (unsigned long long)idx * kChunkMax;
+                } else if (a) {
+                    op.dst = (unsigned long long)(A.out_dep + A.pos_dep[pos]) + (unsigned long long)idx * kChunkMax;
+                } else if (!half) {
+                    op.dst = (unsigned long long)(A.out_ind + A.pos_ind[pos]) + (unsigned long long)idx * kChunkMax;
+                } else if (((size | va_extsize) & 3u) == 0u && (A.pos_ind[pos] & 3ull) == 0ull) {
+                    op.dst = (unsigned long long)(A.out_ind + ((A.pos_ind[pos] + (unsigned long long)idx * kChunkMax) >> 1));
+                    op.len = size | kOpToBf16;
+                } else {
+                    report(st, 4, pos, 1, 1, CDS_ERR_SHAPE);                // not a whole number of float32 elements
+                    op.dst = 0;
+                }
             }
         }
         A.ops[g] = op;
@@ -438,7 +450,15 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
                         job.src = (unsigned long long)(A.scratch + A.vscr[v] + 4);
                         job.slen = va_extsize - 4u;
                         job.rawsize = (uint32_t)len;
-                        job.dst = a ? (unsigned long long)(A.out_dep + my_dep_off) : (unsigned long long)(A.out_ind + my_ind_off);
+                        if (a) job.dst = (unsigned long long)(A.out_dep + my_dep_off);
+                        else if (!half) job.dst = (unsigned long long)(A.out_ind + my_ind_off);
+                        else if ((len & 3ull) == 0ull && (my_ind_off & 3ull) == 0ull) {
+                            job.dst = (unsigned long long)(A.out_ind + (my_ind_off >> 1));
+                            job.slen |= kJobToBf16;
+                        } else {
+                            report(st, 4, pos, 1, 1, CDS_ERR_SHAPE);
+                            job.slen = kNone;
+                        }
                     }
                 }
             }

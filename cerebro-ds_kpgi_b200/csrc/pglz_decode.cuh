@@ -25,6 +25,8 @@
 // reads stale memory instead): tags that run past the source, offset 0, offsets before the
 // start of the output.
 #pragma once
+#include <cuda_bf16.h>
+
 #include "cds_common.cuh"
 
 namespace cds {
@@ -52,6 +54,33 @@ __device__ __forceinline__ void pglz_flush(const uint8_t *ring, uint8_t *dst, ui
     }
     const uint32_t t0 = b0 + (nvec << 4);
     if (lane < to - t0) dst[t0 + lane] = ring[(t0 + lane + shift) & (kRing - 1)];
+}
+
+// bfloat16 variant: the ring holds float32 data, `dst` holds bfloat16; positions are float32 byte offsets
+// (multiples of 4) and `shift` = (2 * dst) & 15, so that a 16-byte ring vector maps onto an aligned
+// 8-byte store.
+__device__ __forceinline__ void pglz_flush_bf16(const uint8_t *ring, uint8_t *dst, uint32_t shift, uint32_t from,
+                                                uint32_t to, uint32_t lane)
+{
+    __nv_bfloat16 *dh = reinterpret_cast<__nv_bfloat16 *>(dst);
+    uint32_t head = ((16u - ((from + shift) & 15u)) & 15u) >> 2;             // floats up to the next ring vector
+    if (head > ((to - from) >> 2)) head = (to - from) >> 2;
+    if (lane < head)
+        dh[(from >> 2) + lane] = __float2bfloat16_rn(*reinterpret_cast<const float *>(ring + ((from + 4u * lane + shift) & (kRing - 1))));
+    const uint32_t b0 = from + 4u * head;
+    const uint32_t nvec = (to - b0) >> 4;
+    for (uint32_t j = lane; j < nvec; j += 32) {
+        const uint32_t pos = b0 + (j << 4);
+        const float4 v = *reinterpret_cast<const float4 *>(ring + ((pos + shift) & (kRing - 1)));
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 q;
+        q.x = *reinterpret_cast<const uint32_t *>(&lo);
+        q.y = *reinterpret_cast<const uint32_t *>(&hi);
+        __stcs(reinterpret_cast<uint2 *>(dst + (pos >> 1)), q);
+    }
+    const uint32_t t0 = b0 + (nvec << 4);
+    if (lane < ((to - t0) >> 2))
+        dh[(t0 >> 2) + lane] = __float2bfloat16_rn(*reinterpret_cast<const float *>(ring + ((t0 + 4u * lane + shift) & (kRing - 1))));
 }
 
 // Register window over the source stream.  The stream is addressed in the word-aligned frame
@@ -216,11 +245,18 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
 }
 
 // Decode one datum with the calling warp.  Returns true when the stream is well-formed.
+template <bool kBf16>
 __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen, uint8_t *dst, uint32_t rawsize,
                                  uint8_t *ring)
 {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t shift = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+    // ring index = output position + shift, chosen so that ring vectors line up with aligned global stores
+    const uint32_t shift = kBf16 ? (uint32_t)((2u * reinterpret_cast<uintptr_t>(dst)) & 15u)
+                                 : (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+    auto flush = [&](uint32_t from, uint32_t to) {
+        if (kBf16) pglz_flush_bf16(ring, dst, shift, from, to, lane);
+        else pglz_flush(ring, dst, shift, from, to, lane);
+    };
     uint32_t sp = 0, dp = 0, flushed = 0;
     uint32_t wide_pause = 0, wide_backoff = 4;                               // steps to stay on the one-group path
     bool corrupt = false;
@@ -273,7 +309,7 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
                 __syncwarp();
                 if (dp - flushed >= kFlushAt) {
                     const uint32_t to = dp - ((dp + shift) & 15u);
-                    pglz_flush(ring, dst, shift, flushed, to, lane);
+                    flush(flushed, to);
                     flushed = to;
                     __syncwarp();
                 }
@@ -372,14 +408,14 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
         }
         if (dp - flushed >= kFlushAt) {
             const uint32_t to = dp - ((dp + shift) & 15u);
-            pglz_flush(ring, dst, shift, flushed, to, lane);
+            flush(flushed, to);
             flushed = to;
             __syncwarp();
         }
     }
     if (!corrupt) {
         __syncwarp();
-        pglz_flush(ring, dst, shift, flushed, dp, lane);
+        flush(flushed, dp);
     }
     return !corrupt && dp == rawsize && sp == slen;                          // ppr:229-230
 }
@@ -407,8 +443,11 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
         const uint32_t j = t < front ? t : last_slot - (t - front);
         const PglzJob job = jobs[j];
         if (job.slen == kNone) continue;
-        const bool ok = pglz_warp_decode(reinterpret_cast<const uint8_t *>(job.src), job.slen,
-                                         reinterpret_cast<uint8_t *>(job.dst), job.rawsize, ring);
+        const bool ok = (job.slen & kJobToBf16)
+            ? pglz_warp_decode<true>(reinterpret_cast<const uint8_t *>(job.src), job.slen & ~kJobToBf16,
+                                     reinterpret_cast<uint8_t *>(job.dst), job.rawsize, ring)
+            : pglz_warp_decode<false>(reinterpret_cast<const uint8_t *>(job.src), job.slen,
+                                      reinterpret_cast<uint8_t *>(job.dst), job.rawsize, ring);
         if (lane == 0) {
             if (status) status[j] = ok ? CDS_OK : CDS_ERR_PGLZ_CORRUPT;
             if (!ok && st && job.err_key) report_key(st, job.err_key);

@@ -14,6 +14,8 @@
 //   * consumer warps realign in shared memory (two aligned LDS.128 + word select) and emit
 //     aligned, coalesced, streaming 16-byte global stores.
 #pragma once
+#include <cuda_bf16.h>
+
 #include "cds_common.cuh"
 
 namespace cds {
@@ -103,6 +105,46 @@ __device__ __forceinline__ void copy_payload(const uint8_t *src, uint8_t *dst, u
     if (tid < len - rem) dst[rem + tid] = src[rem + tid];
 }
 
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b)
+{
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);                    // round to nearest even
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+
+// Same job as copy_payload, but the payload is float32 data and the destination holds bfloat16: `len`
+// source bytes (a multiple of 4, 4-byte aligned in shared memory) become len/2 bytes at `dst`.
+__device__ __forceinline__ void copy_payload_bf16(const uint8_t *src, uint8_t *dst, uint32_t len, uint32_t tid, uint32_t nth)
+{
+    const uint32_t n = len >> 2;                                             // floats
+    const uintptr_t da = reinterpret_cast<uintptr_t>(dst);
+    uint32_t head = ((8u - (uint32_t)(da & 7u)) & 7u) >> 1;                   // floats until dst is 8-byte aligned
+    if (head > n) head = n;
+    const float *sf = reinterpret_cast<const float *>(src);
+    __nv_bfloat16 *dh = reinterpret_cast<__nv_bfloat16 *>(dst);
+    if (tid < head) dh[tid] = __float2bfloat16_rn(sf[tid]);
+    const uint32_t body = (n - head) >> 2;                                   // groups of 4 floats -> one 8-byte store
+    const uint8_t *sb = src + 4u * head;
+    const uint32_t r = smem_u32(sb) & 15u;                                   // 0, 4, 8 or 12
+    const uint4 *s16 = reinterpret_cast<const uint4 *>(sb - r);
+    uint2 *d8 = reinterpret_cast<uint2 *>(dst + 2u * head);
+    for (uint32_t j = tid; j < body; j += nth) {
+        const uint4 a = s16[j];
+        uint4 o = a;
+        if (r != 0) {
+            const uint4 b = s16[j + 1];
+            if (r == 4)       o = make_uint4(a.y, a.z, a.w, b.x);
+            else if (r == 8)  o = make_uint4(a.z, a.w, b.x, b.y);
+            else              o = make_uint4(a.w, b.x, b.y, b.z);
+        }
+        uint2 q;
+        q.x = pack_bf16x2(__uint_as_float(o.x), __uint_as_float(o.y));
+        q.y = pack_bf16x2(__uint_as_float(o.z), __uint_as_float(o.w));
+        asm volatile("st.global.cs.v2.u32 [%0], {%1, %2};" ::"l"(d8 + j), "r"(q.x), "r"(q.y) : "memory");
+    }
+    const uint32_t done = head + (body << 2);
+    if (tid < n - done) dh[done + tid] = __float2bfloat16_rn(sf[done + tid]);
+}
+
 __global__ void __launch_bounds__(kGatherThreads, 1)
 k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32_t *__restrict__ base,
                const CopyOp *__restrict__ ops, const DevState *__restrict__ st)
@@ -155,7 +197,8 @@ k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32
             for (uint32_t j = 0; j < n; j++) {
                 const CopyOp op = j < (uint32_t)kGatherMaxStageOps ? stage_ops[s * kGatherMaxStageOps + j] : ops[g0 + j];
                 if (op.dst == 0 || op.len == 0) continue;
-                copy_payload(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len, ctid, cnth);
+                if (op.len & kOpToBf16) copy_payload_bf16(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len & ~kOpToBf16, ctid, cnth);
+                else copy_payload(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len, ctid, cnth);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[s]);

@@ -41,7 +41,7 @@ def _load_catalog(file_path):
     return df_shape, sys_cat['relname'], table_page_path, toast_page_path
 
 
-def _decode_files(table_page_path, toast_page_path, ind_sample_bytes=0, dep_sample_bytes=0):
+def _decode_files(table_page_path, toast_page_path, ind_sample_bytes=0, dep_sample_bytes=0, ind_bf16=False):
     """Both relations -> pinned host memory -> HBM -> one fused decode.  Returns (part, partial flags)."""
     import torch
     _lib.require_device()
@@ -55,7 +55,7 @@ def _decode_files(table_page_path, toast_page_path, ind_sample_bytes=0, dep_samp
     d_heap = pg_page_reader._to_device(heap_host)
     d_toast = pg_page_reader._to_device(toast_host)
     status, part = _segment.decode_pages(d_heap, d_toast, ind_sample_bytes=ind_sample_bytes,
-                                         dep_sample_bytes=dep_sample_bytes)
+                                         dep_sample_bytes=dep_sample_bytes, ind_bf16=ind_bf16)
     torch.cuda.synchronize()
     # reference order of failures: heap scan, short heap page, TOAST walk, short TOAST page, detoast
     stage = part.summary.err_stage if status else 99
@@ -118,9 +118,10 @@ class DevicePartition:
         return out
 
 
-def input_fn_device(file_path, overwrite_table_page_path=None, overwrite_toast_page_path=None):
+def input_fn_device(file_path, overwrite_table_page_path=None, overwrite_toast_page_path=None, dtype=None):
     """Same call as input_fn, result left on the GPU.  Sample shapes come from the catalog's shape
-    frame (every buffer of a table shares its trailing dimensions)."""
+    frame (every buffer of a table shares its trailing dimensions).  dtype=torch.bfloat16 makes the decode
+    kernels emit bfloat16 images directly (round to nearest even); default: the stored float32 bits."""
     import torch
     df_shape, table_name, table_page_path, toast_page_path = _load_catalog(file_path)
     if overwrite_table_page_path:
@@ -133,8 +134,9 @@ def input_fn_device(file_path, overwrite_table_page_path=None, overwrite_toast_p
     ishape = tuple(int(x) for x in sub['independent_var_shape'].iloc[0][1:])
     dshape = tuple(int(x) for x in sub['dependent_var_shape'].iloc[0][1:])
     isb, dsb = 4 * int(np.prod(ishape)), 2 * int(np.prod(dshape))
-    part = _decode_files(table_page_path, toast_page_path, isb, dsb)
-    images = part.ind.view(torch.float32).view((-1,) + ishape)
+    bf16 = dtype is not None and dtype == torch.bfloat16
+    part = _decode_files(table_page_path, toast_page_path, isb, dsb, ind_bf16=bf16)
+    images = part.ind.view(torch.bfloat16 if bf16 else torch.float32).view((-1,) + ishape)
     onehot = part.dep.view(torch.int16).view((-1,) + dshape)
     labels = _segment.onehot_argmax(onehot.reshape(onehot.shape[0], -1))
     lay = part.layout

@@ -85,6 +85,10 @@ class DeviceSegment:
         except Exception:  # noqa
             pass
 
+    def set_output_format(self, ind_bf16=False):
+        """independent_var as stored (float32 bytes, default) or converted to bfloat16 on the fly."""
+        _lib.check(self.L.cds_set_output_format(self._h, 1 if ind_bf16 else 0))
+
     # ---- step API -------------------------------------------------------------------------
     def heap_scan(self, heap, stream=None):
         _lib.check(self.L.cds_heap_scan(self._h, _ptr(heap), heap.numel() // BLCKSZ, _stream_ptr(stream)))
@@ -271,7 +275,7 @@ class DecodedPartition:
 
 
 def decode_pages(heap, toast, device=None, ind_sample_bytes=0, dep_sample_bytes=0, rows=None, inline_blob=None,
-                 segment=None):
+                 segment=None, ind_bf16=False):
     """Two-phase decode of page buffers already on the GPU (uint8 CUDA tensors): scan + plan, one
     host sync to size the outputs, then materialize.  With `rows` (exported-row layout) the heap scan
     is replaced by an upload of those rows (`toast_page_read` path).  Returns (status, DecodedPartition)."""
@@ -281,6 +285,7 @@ def decode_pages(heap, toast, device=None, ind_sample_bytes=0, dep_sample_bytes=
         seg = segment or DeviceSegment(max(1, (heap.numel() // BLCKSZ) if heap is not None else (len(rows) // 400 + 1)),
                                        toast.numel() // BLCKSZ, device=dev.index)
         try:
+            seg.set_output_format(ind_bf16)
             if rows is None:
                 seg.heap_scan(heap)
             else:
@@ -290,13 +295,14 @@ def decode_pages(heap, toast, device=None, ind_sample_bytes=0, dep_sample_bytes=
             s1 = seg.finish()
             if s1.status != 0:
                 return int(s1.status), DecodedPartition(s1, None, None, None, None)
-            ind = torch.empty(int(s1.ind_bytes) + 16, dtype=torch.uint8, device=dev)
+            ind_out_bytes = int(s1.ind_bytes) // 2 if ind_bf16 else int(s1.ind_bytes)
+            ind = torch.empty(ind_out_bytes + 16, dtype=torch.uint8, device=dev)
             dep = torch.empty(int(s1.dep_bytes) + 16, dtype=torch.uint8, device=dev)
             seg.materialize(ind, dep)
             s2 = seg.finish()
             out_rows = seg.rows()
             lay = seg.layout(int(s2.n_rows), int(s2.n_positions))
-            return int(s2.status), DecodedPartition(s2, out_rows, lay, ind[:int(s1.ind_bytes)], dep[:int(s1.dep_bytes)])
+            return int(s2.status), DecodedPartition(s2, out_rows, lay, ind[:ind_out_bytes], dep[:int(s1.dep_bytes)])
         finally:
             if segment is None:
                 seg.close()

@@ -81,6 +81,13 @@ int cds_segment_create(cds_segment **out, int device, uint64_t max_heap_pages, u
                        uint64_t max_chunks, uint64_t scratch_bytes, int stage_pages);
 int cds_segment_destroy(cds_segment *seg);
 
+/* Output format of independent_var for the following cds_materialize / cds_decode_* calls on this handle:
+ * 0 (default) = the stored bytes (float32 for these tables; a bit copy, as ppr:165-182),
+ * 1 = bfloat16, converted from the stored float32 with round-to-nearest-even inside the gather and the
+ *     pglz decoder (no float32 copy is written); capacities and cds_summary.ind_bytes stay in float32
+ *     bytes, the buffer needs ind_bytes / 2.  Not in the reference: an optional training-buffer dtype. */
+int cds_set_output_format(cds_segment *seg, int independent_var_format);
+
 /* ---- the path, step by step (each enqueues on `stream` and returns; no host sync) ---------- */
 
 /* table_page_read (ppr:451-494): page header (ppr:253-269), ItemId (ppr:285-305), tuple header

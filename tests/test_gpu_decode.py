@@ -200,3 +200,34 @@ def test_one_shot_decode_device_and_host(torch_cuda, coracle):
     assert ei.value.code == 102
     assert int(small.sum()) == 0
     ds.close()
+
+
+def test_fused_bf16_output_matches_rne_of_oracle(torch_cuda, coracle):
+    """Optional output dtype (not in the reference): the gather and the pglz decoder emit bfloat16 directly.
+    Must equal round-to-nearest-even of the oracle's float32 output, for every storage form and for
+    odd result offsets; dependent_var is untouched."""
+    from cerebro_ds_kpgi_b200 import synth
+    torch = torch_cuda
+    rng = np.random.default_rng(8)
+    ind, dep = [], []
+    for i in range(24):
+        b = 1 + i % 3
+        ind.append((rng.standard_normal((b, 37, 29, 3)) * 10.0 ** int(rng.integers(-3, 4))).astype(np.float32))
+        dep.append(np.eye(7, dtype=np.int16)[rng.integers(0, 7, b)])
+    st = [["ext_raw", "ext_pglz", "ext_literal"][i % 3] for i in range(24)]
+    seg = synth.build_segment(ind, dep, ind_storage=st, dep_storage=["inline_pglz", "ext_raw"] * 12)
+    want = coracle.decode(seg.heap, seg.toast)
+    status, part = gpu_decode(torch, seg.heap, seg.toast, ind_bf16=True)
+    assert status == 0
+    ref = torch.from_numpy(want["out_ind"].view(np.float32).copy()).to(torch.bfloat16)
+    got = part.ind.view(torch.bfloat16).cpu()
+    assert got.shape == ref.shape and torch.equal(got.view(torch.int16), ref.view(torch.int16))
+    assert part.dep.cpu().numpy().tobytes() == want["out_dep"].tobytes()
+    # real shape, uncompressed: 112x112x3 rows
+    ind, dep = synth.imagenet_rows(20, seed=3, kind="normal")
+    seg = synth.build_segment(ind, dep, ind_storage="ext_raw", dep_storage="ext_raw")
+    want = coracle.decode(seg.heap, seg.toast)
+    status, part = gpu_decode(torch, seg.heap, seg.toast, ind_bf16=True, ind_sample_bytes=150528, dep_sample_bytes=2000)
+    assert status == 0
+    ref = torch.from_numpy(want["out_ind"].view(np.float32).copy()).to(torch.bfloat16)
+    assert torch.equal(part.ind.view(torch.bfloat16).cpu().view(torch.int16), ref.view(torch.int16))
