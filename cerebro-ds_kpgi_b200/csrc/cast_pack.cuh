@@ -9,6 +9,7 @@
 #include <cuda_bf16.h>
 
 #include "cds_common.cuh"
+#include "tma_helpers.cuh"
 
 namespace cds {
 
@@ -120,6 +121,86 @@ k_batch_assemble(const float *__restrict__ images, unsigned long long n_samples,
             long long s = indices[b] % (long long)n_samples;
             if (s < 0) s += (long long)n_samples;
             out_labels[b] = labels[s];
+        }
+    }
+}
+
+// Staged version of the two NHWC -> NCHW kernels above for images whose samples are 16-byte multiples:
+// persistent CTAs, a producer warp streams tiles of `tp` whole pixels (tp * ch * 4 bytes, a multiple of 16)
+// into a shared-memory ring with TMA bulk copies, consumer warps read one channel of consecutive pixels
+// (stride `ch` words: conflict-free for odd ch) and write coalesced channel planes.  Every source byte is
+// read once and every destination byte written once.
+//   indices == NULL: sample b of the source goes to slot b (whole-partition transpose);
+//   otherwise sample = indices[b] mod n_samples (batch assembly).
+constexpr int kAsmStages = 4;
+constexpr int kAsmConsumerWarps = 12;
+constexpr int kAsmThreads = 32 * (1 + kAsmConsumerWarps);
+constexpr uint32_t kAsmMaxTileBytes = 48 * 1024;
+
+template <typename TOut>
+__global__ void __launch_bounds__(kAsmThreads, 1)
+k_assemble_tma(const float *__restrict__ images, unsigned long long n_samples, uint32_t hw, uint32_t ch, uint32_t tp,
+               const long long *__restrict__ labels, const long long *__restrict__ indices, uint32_t batch,
+               TOut *__restrict__ out, long long *__restrict__ out_labels)
+{
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const uint32_t tile_bytes = tp * ch * 4u;
+    unsigned long long *full = reinterpret_cast<unsigned long long *>(smem_raw + (size_t)kAsmStages * tile_bytes);
+    unsigned long long *empty = full + kAsmStages;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kAsmStages; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], kAsmConsumerWarps); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const uint32_t tiles_per = hw / tp;
+    const unsigned long long total = (unsigned long long)batch * tiles_per;
+    if (blockIdx.x >= total) return;
+    const uint32_t mine = (uint32_t)((total - blockIdx.x + gridDim.x - 1) / gridDim.x);
+    const unsigned long long per = (unsigned long long)hw * ch;
+
+    auto sample_of = [&](uint32_t b) -> unsigned long long {
+        if (!indices) return b;
+        long long s = indices[b] % (long long)n_samples;
+        return (unsigned long long)(s < 0 ? s + (long long)n_samples : s);
+    };
+
+    if (warp == 0) {
+        for (uint32_t it = 0; it < mine; it++) {
+            const uint32_t s = it % kAsmStages, round = it / kAsmStages;
+            const unsigned long long w = blockIdx.x + (unsigned long long)it * gridDim.x;
+            const uint32_t b = (uint32_t)(w / tiles_per), t = (uint32_t)(w - (unsigned long long)b * tiles_per);
+            if (round > 0) mbar_wait(&empty[s], (round - 1) & 1u);
+            if (lane == 0) {
+                const float *src = images + sample_of(b) * per + (unsigned long long)t * tp * ch;
+                mbar_arrive_expect_tx(&full[s], tile_bytes);
+                tma_load_bulk(smem_raw + (size_t)s * tile_bytes, src, tile_bytes, &full[s]);
+                if (t == 0 && labels && out_labels) out_labels[b] = labels[sample_of(b)];
+            }
+        }
+    } else {
+        const uint32_t ctid = threadIdx.x - 32, cnth = 32 * kAsmConsumerWarps;
+        for (uint32_t it = 0; it < mine; it++) {
+            const uint32_t s = it % kAsmStages, round = it / kAsmStages;
+            const unsigned long long w = blockIdx.x + (unsigned long long)it * gridDim.x;
+            const uint32_t b = (uint32_t)(w / tiles_per), t = (uint32_t)(w - (unsigned long long)b * tiles_per);
+            mbar_wait(&full[s], round & 1u);
+            const float *tile = reinterpret_cast<const float *>(smem_raw + (size_t)s * tile_bytes);
+            TOut *dst = out + (unsigned long long)b * per + (unsigned long long)t * tp;
+            if constexpr (sizeof(TOut) == 4) {
+                for (uint32_t c = 0; c < ch; c++)
+                    for (uint32_t p = ctid; p < tp; p += cnth)
+                        __stcs(reinterpret_cast<float *>(dst) + (unsigned long long)c * hw + p, tile[p * ch + c]);
+            } else {
+                // two pixels per lane -> one 32-bit store of two bfloat16 (tp and hw are even here)
+                for (uint32_t c = 0; c < ch; c++)
+                    for (uint32_t p2 = ctid; p2 < (tp >> 1); p2 += cnth) {
+                        const __nv_bfloat162 h = __floats2bfloat162_rn(tile[(2u * p2) * ch + c], tile[(2u * p2 + 1u) * ch + c]);
+                        __stcs(reinterpret_cast<unsigned int *>(dst + (unsigned long long)c * hw) + p2, *reinterpret_cast<const unsigned int *>(&h));
+                    }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
         }
     }
 }

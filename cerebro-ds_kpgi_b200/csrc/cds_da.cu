@@ -820,10 +820,50 @@ extern "C" int cds_onehot_argmax_i16(const void *d_onehot, uint64_t n_rows, uint
     return CDS_OK;
 }
 
+// Tile of whole pixels for k_assemble_tma: tp divides hw, tp*ch*4 is a multiple of 16 and at most
+// kAsmMaxTileBytes, tp even when two pixels share a bf16 store.  0: the staged kernel does not apply.
+static uint32_t assemble_tile(const void *images, uint32_t hw, uint32_t ch, bool bf16)
+{
+    if ((reinterpret_cast<uintptr_t>(images) & 15u) || (((uint64_t)hw * ch * 4u) & 15u)) return 0;
+    if (bf16 && (hw & 1u)) return 0;
+    uint32_t best = 0;
+    for (uint32_t tp = 1; tp <= hw && (uint64_t)tp * ch * 4u <= kAsmMaxTileBytes; tp++) {
+        if (hw % tp) continue;
+        if (((uint64_t)tp * ch * 4u) & 15u) continue;
+        if (bf16 && (tp & 1u)) continue;
+        best = tp;
+    }
+    return (best && (uint64_t)best * ch * 4u >= 4096u) ? best : 0;
+}
+
+template <typename TOut>
+static int launch_assemble_tma(const void *d_images, uint64_t n_samples, uint32_t hw, uint32_t ch, uint32_t tp,
+                               const void *d_labels, const void *d_indices, uint32_t batch, void *d_out, void *d_out_labels,
+                               cudaStream_t st)
+{
+    const size_t smem = (size_t)kAsmStages * tp * ch * 4u + 2 * kAsmStages * sizeof(unsigned long long) + 16;
+    CU(cudaFuncSetAttribute(k_assemble_tma<TOut>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const uint64_t total = (uint64_t)batch * (hw / tp);
+    const uint32_t grid = (uint32_t)(total < (uint64_t)sms ? total : (uint64_t)sms);
+    k_assemble_tma<TOut><<<grid, kAsmThreads, smem, st>>>(
+        static_cast<const float *>(d_images), n_samples, hw, ch, tp, static_cast<const long long *>(d_labels),
+        static_cast<const long long *>(d_indices), batch, static_cast<TOut *>(d_out), static_cast<long long *>(d_out_labels));
+    CU(cudaGetLastError());
+    LAUNCHED(1);
+    return CDS_OK;
+}
+
 extern "C" int cds_nhwc_to_nchw_f32(const void *d_src, uint64_t n, uint32_t hw, uint32_t ch, void *d_dst, void *stream)
 {
     if (n == 0) return CDS_OK;
     if (!d_src || !d_dst || hw == 0 || ch == 0) return CDS_ERR_ARG;
+    if (n <= 0xFFFFFFFFull && ch > 1) {
+        const uint32_t tp = assemble_tile(d_src, hw, ch, false);
+        if (tp) return launch_assemble_tma<float>(d_src, n, hw, ch, tp, nullptr, nullptr, (uint32_t)n, d_dst, nullptr, (cudaStream_t)stream);
+    }
     uint64_t total = n * hw * ch, blocks = (total + 255) / 256;
     if (blocks > 148ull * 32) blocks = 148ull * 32;
     k_nhwc_to_nchw_f32<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const float *>(d_src), n, hw, ch,
@@ -852,9 +892,17 @@ extern "C" int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint
 {
     if (batch == 0) return CDS_OK;
     if (!d_images || !d_indices || !d_out || n_samples == 0 || hw == 0 || ch == 0) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (ch > 1) {
+        const uint32_t tp = assemble_tile(d_images, hw, ch, out_bf16 != 0);
+        if (tp) {
+            if (out_bf16)
+                return launch_assemble_tma<__nv_bfloat16>(d_images, n_samples, hw, ch, tp, d_labels, d_indices, batch, d_out, d_out_labels, st);
+            return launch_assemble_tma<float>(d_images, n_samples, hw, ch, tp, d_labels, d_indices, batch, d_out, d_out_labels, st);
+        }
+    }
     uint64_t total = (uint64_t)batch * hw * ch, blocks = (total + 255) / 256;
     if (blocks > 148ull * 32) blocks = 148ull * 32;
-    cudaStream_t st = (cudaStream_t)stream;
     if (out_bf16)
         k_batch_assemble<__nv_bfloat16><<<(uint32_t)blocks, 256, 0, st>>>(
             static_cast<const float *>(d_images), n_samples, hw, ch, static_cast<const long long *>(d_labels),

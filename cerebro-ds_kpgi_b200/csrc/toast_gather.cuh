@@ -17,6 +17,7 @@
 #include <cuda_bf16.h>
 
 #include "cds_common.cuh"
+#include "tma_helpers.cuh"
 
 namespace cds {
 
@@ -29,39 +30,6 @@ constexpr size_t kGatherSmemBytes =
     (size_t)kGatherStages * kGatherMaxStageOps * sizeof(CopyOp) +
     (size_t)kGatherStages * 2 * sizeof(uint32_t) + (size_t)kGatherStages * 2 * sizeof(unsigned long long) + 64;
 
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(unsigned long long *bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra WAIT_DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "WAIT_DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
-__device__ __forceinline__ void tma_load_page(void *smem_dst, const void *gsrc, uint32_t bytes, unsigned long long *bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
-                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
 __device__ __forceinline__ void st_stream_v4(void *gdst, uint4 v)
 {
     asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(gdst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
@@ -177,7 +145,7 @@ k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32
             if (round > 0) mbar_wait(&empty[s], (round - 1) & 1u);
             if (lane == 0) {
                 mbar_arrive_expect_tx(&full[s], kPage);
-                tma_load_page(stage_buf + (size_t)s * kPage, pages + (size_t)p * kPage, kPage, &full[s]);
+                tma_load_bulk(stage_buf + (size_t)s * kPage, pages + (size_t)p * kPage, kPage, &full[s]);
             }
             const uint32_t g0 = base[p], n = base[p + 1] - g0;
             for (uint32_t j = lane; j < n && j < (uint32_t)kGatherMaxStageOps; j += 32)

@@ -132,6 +132,15 @@ def test_input_fn_device_and_consumers(tmp_path, torch_cuda, coracle):
     ref_x = np.stack([np.rollaxis(want["out_ind"].view(np.float32).reshape(20, 112, 112, 3)[i % 20], 2, 0) for i in range(37, 45)])
     assert x.shape == (8, 3, 112, 112) and x.cpu().numpy().tobytes() == ref_x.tobytes()
     assert np.array_equal(y.cpu().numpy(), part.labels.cpu().numpy()[np.arange(37, 45) % 20])
+    xb, yb = ds.batch(idx, dtype=torch.bfloat16)          # optional dtype: RNE of the same values
+    assert torch.equal(xb.cpu().view(torch.int16), torch.from_numpy(ref_x).to(torch.bfloat16).view(torch.int16))
+    assert torch.equal(yb, y)
+    # a shape the staged kernel does not take (odd pixel count): generic path, same answer
+    from cerebro_ds_kpgi_b200 import segment
+    odd = torch.randn(7, 5, 3, 3, device="cuda")
+    assert torch.equal(segment.nhwc_to_nchw(odd), odd.permute(0, 3, 1, 2).contiguous())
+    big = torch.randn(33, 112, 112, 3, device="cuda")
+    assert torch.equal(segment.nhwc_to_nchw(big), big.permute(0, 3, 1, 2).contiguous())
     # Keras-style consumer (run_da_cerebro_standalone.py:33-56)
     out = da.input_fn(os.path.join(d, "train"))
     g = consumers.generator_df(out)
