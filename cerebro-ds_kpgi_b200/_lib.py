@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libcds_da.so")
 (CDS_OK, CDS_ERR_PARTIAL_PAGE, CDS_ERR_ITEMID_ALIGN, CDS_ERR_TOAST_SPECIAL, CDS_ERR_TUPLE, CDS_ERR_RAWSIZE,
  CDS_ERR_CHUNK_COUNT, CDS_ERR_CHUNK_EXTENDED, CDS_ERR_MAX_CHUNK, CDS_ERR_CHUNK_SIZE, CDS_ERR_FINAL_SIZE,
  CDS_ERR_PGLZ_CORRUPT, CDS_ERR_SHAPE, CDS_ERR_CATALOG_MISS, CDS_ERR_MISSING_VALUE) = range(15)
+CDS_ERR_TEXT_NUMBER = 15
 CDS_ERR_CUDA, CDS_ERR_ARG, CDS_ERR_CAPACITY, CDS_ERR_NO_DEVICE = 100, 101, 102, 103
 
 ROW_WORDS = 16
@@ -70,6 +71,7 @@ PROTOTYPES = {
     "cds_onehot_argmax_i16": (_int, [_vp, _u64, _u32, _vp, _vp]),
     "cds_nhwc_to_nchw_f32": (_int, [_vp, _u64, _u32, _u32, _vp, _vp]),
     "cds_f32_to_bf16": (_int, [_vp, _u64, _vp, _vp]),
+    "cds_text_etl": (_int, [_int, _vp, _u64, _u32, _u32, _vp, _vp, _vp, _u64, _pu64, _pu64, _vp]),
     "cds_batch_assemble": (_int, [_vp, _u64, _u32, _u32, _vp, _vp, _u32, _vp, _int, _vp, _vp]),
 }
 

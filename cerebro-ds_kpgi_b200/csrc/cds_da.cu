@@ -14,6 +14,7 @@
 #include "cds_common.cuh"
 #include "page_scan.cuh"
 #include "pglz_decode.cuh"
+#include "text_etl.cuh"
 #include "toast_gather.cuh"
 
 using namespace cds;
@@ -92,6 +93,7 @@ extern "C" const char *cds_status_str(int s)
     case CDS_ERR_SHAPE: return "decoded size does not match the sample shape";
     case CDS_ERR_CATALOG_MISS: return "chunk id matches no external pointer";
     case CDS_ERR_MISSING_VALUE: return "a value has no chunks";
+    case CDS_ERR_TEXT_NUMBER: return "numeric literal outside the exactly convertible range";
     case CDS_ERR_CUDA: return "CUDA error";
     case CDS_ERR_ARG: return "bad argument";
     case CDS_ERR_CAPACITY: return "capacity exceeded";
@@ -915,5 +917,65 @@ extern "C" int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint
             static_cast<long long *>(d_out_labels));
     CU(cudaGetLastError());
     LAUNCHED(1);
+    return CDS_OK;
+}
+
+// ---- text ETL -----------------------------------------------------------------
+
+extern "C" int cds_text_etl(int device, const void *d_text, uint64_t n_bytes, uint32_t values_per_row, uint32_t label_digits,
+                            void *d_features, void *d_labels, void *d_ids, uint64_t cap_rows, uint64_t *n_rows,
+                            uint64_t *err_pos, void *stream)
+{
+    if (!n_rows || values_per_row == 0 || (n_bytes && (!d_text || !d_features || !d_labels))) return CDS_ERR_ARG;
+    *n_rows = 0;
+    if (err_pos) *err_pos = 0;
+    if (n_bytes == 0) return CDS_OK;
+    if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaSetDevice(device));
+    const uint64_t n_tiles64 = (n_bytes + kTextTile - 1) / kTextTile;
+    if (n_tiles64 > 0x7FFFFFFFull) return CDS_ERR_CAPACITY;
+    const uint32_t n_tiles = (uint32_t)n_tiles64, scan_tiles = n_tiles / kScanMinTile + 2;
+    const uint32_t per_row = values_per_row + 2u;
+    // one allocation: [TextState | 2 tickets | 2 x status] zeroed, then counts, then scan values
+    const size_t zero_bytes = 256 + 4 * (8 + 2 * (size_t)scan_tiles);
+    uint8_t *zero = nullptr;
+    uint32_t *counts = nullptr;
+    unsigned long long *vals = nullptr;
+    cudaError_t e = dalloc(&zero, zero_bytes);
+    if (e == cudaSuccess) e = dalloc(&counts, 2 * ((size_t)n_tiles + 1));
+    if (e == cudaSuccess) e = dalloc(&vals, 4 * (size_t)scan_tiles);
+    TextState h;
+    memset(&h, 0, sizeof(h));
+    if (e == cudaSuccess) e = cudaMemsetAsync(zero, 0, zero_bytes, st);
+    if (e == cudaSuccess) {
+        TextState *state = reinterpret_cast<TextState *>(zero);
+        uint32_t *w = reinterpret_cast<uint32_t *>(zero + 256);
+        ScanWs ws0{w, w + 8, vals, vals + scan_tiles}, ws1{w + 1, w + 8 + scan_tiles, vals + 2 * scan_tiles, vals + 3 * scan_tiles};
+        uint32_t *tile_tokens = counts, *tile_lines = counts + n_tiles + 1;
+        const uint8_t *text = static_cast<const uint8_t *>(d_text);
+        k_text_count<<<n_tiles, kTextThreads, 0, st>>>(text, n_bytes, tile_tokens, tile_lines);
+        uint32_t sg = n_tiles / (kScanThreads * 4) + 1;
+        if (sg > 592) sg = 592;
+        k_text_scan<<<dim3(sg, 2), kScanThreads, 0, st>>>(tile_tokens, tile_lines, n_tiles, ws0, ws1, state, n_bytes, text);
+        k_text_parse<<<n_tiles, kTextThreads, 0, st>>>(text, n_bytes, tile_tokens, tile_lines, per_row, label_digits,
+                                                       static_cast<float *>(d_features), static_cast<long long *>(d_labels),
+                                                       static_cast<long long *>(d_ids), cap_rows, state);
+        e = cudaGetLastError();
+        LAUNCHED(3);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&h, state, sizeof(h), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    }
+    if (zero) cudaFree(zero);
+    if (counts) cudaFree(counts);
+    if (vals) cudaFree(vals);
+    if (e != cudaSuccess) return cuda_fail(e, "cds_text_etl");
+    *n_rows = h.n_lines;
+    if (h.err_inv) {
+        const unsigned long long key = ~h.err_inv;
+        if (err_pos) *err_pos = (((key >> 28) & 0x1FFFFFFFFull) << 4) | ((key >> 8) & 0xFu);
+        return (int)(key & 0xFFu);
+    }
+    if (h.n_tokens != h.n_lines * per_row) return CDS_ERR_SHAPE;            // the last line has no newline to check it
     return CDS_OK;
 }

@@ -1,0 +1,227 @@
+// text_etl.cuh — gpfdist TEXT unload -> float32 arrays on the GPU.
+//
+// Replaces the parser of the reference's filesystem ETL
+// (/root/reference/cerebro_gpdb/etl_imagenet.py:30-37, etl_criteo.py:28-37) for files written by
+// /root/reference/cerebro_gpdb/unload_imagenet.sql:1-14 (FORMAT 'TEXT', DELIMITER '|'): one row per
+// line, `id|{v,v,...}|label`, the feature column a (possibly nested) brace array of decimal numbers.
+//   reference:  literal_eval(text with braces -> brackets) -> Python numbers -> np.asarray(float32)
+//   here:       every numeric token is parsed by one thread; decimal -> double is exact
+//               (integer mantissa < 2^53 times/divided by an exactly representable power of ten, one
+//               IEEE rounding: Clinger's fast path), then double -> float32 (round to nearest even),
+//               i.e. the same double rounding as float(token) followed by np.float32.
+// Tokens outside that range (more than 15-16 significant digits with a huge exponent, NaN, Infinity)
+// are refused with CDS_ERR_TEXT_NUMBER: there is no slow path on the CPU to fall back to.
+//
+// Rows are uniform: every line holds `per_row` numeric tokens (id, features..., label) in that order,
+// which is checked at every line end.
+#pragma once
+#include "cds_common.cuh"
+
+namespace cds {
+
+constexpr uint32_t kTextTile = 4096;          // characters per CTA tile
+constexpr uint32_t kTextThreads = 256;        // 16 characters per thread
+
+__device__ __forceinline__ bool is_num_char(uint32_t c)
+{
+    return (c >= '0' && c <= '9') || c == '-' || c == '+' || c == '.' || (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z');
+}
+
+struct TextState {
+    unsigned long long err_inv;   // ~(smallest error key): position of the first bad token / line
+    unsigned long long n_tokens;
+    unsigned long long n_lines;
+    unsigned long long pad;
+};
+
+// Pass 1: per tile, how many tokens start and how many lines end inside it.
+__global__ void __launch_bounds__(kTextThreads)
+k_text_count(const uint8_t *__restrict__ text, unsigned long long n, uint32_t *__restrict__ tile_tokens,
+             uint32_t *__restrict__ tile_lines)
+{
+    __shared__ uint32_t sh[2][kTextThreads / 32];
+    const unsigned long long base = (unsigned long long)blockIdx.x * kTextTile + threadIdx.x * 16ull;
+    uint32_t tok = 0, nl = 0;
+    uint32_t prev = (base > 0 && base <= n) ? text[base - 1] : '\n';
+    for (uint32_t k = 0; k < 16; k++) {
+        const unsigned long long i = base + k;
+        if (i >= n) break;
+        const uint32_t c = text[i];
+        tok += (is_num_char(c) && !is_num_char(prev)) ? 1u : 0u;
+        nl += (c == '\n') ? 1u : 0u;
+        prev = c;
+    }
+    for (int d = 16; d > 0; d >>= 1) { tok += __shfl_xor_sync(0xffffffffu, tok, d); nl += __shfl_xor_sync(0xffffffffu, nl, d); }
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = tok; sh[1][threadIdx.x >> 5] = nl; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t a = 0, b = 0;
+        for (uint32_t w = 0; w < kTextThreads / 32; w++) { a += sh[0][w]; b += sh[1][w]; }
+        tile_tokens[blockIdx.x] = a;
+        tile_lines[blockIdx.x] = b;
+    }
+}
+
+// Pass 2: exclusive scans of the two per-tile counts (blockIdx.y selects which).
+__global__ void __launch_bounds__(kScanThreads)
+k_text_scan(uint32_t *tile_tokens, uint32_t *tile_lines, uint32_t n_tiles, ScanWs ws0, ScanWs ws1, TextState *st,
+            unsigned long long n, const uint8_t *__restrict__ text)
+{
+    bool last;
+    if (blockIdx.y == 0) {
+        uint32_t *x = tile_tokens;
+        const uint32_t t = device_exclusive_scan<uint32_t, 4>([&](uint32_t i) { return x[i]; }, x, n_tiles, ws0, true, &last);
+        if (last && threadIdx.x == 0) st->n_tokens = t;
+    } else {
+        uint32_t *x = tile_lines;
+        const uint32_t t = device_exclusive_scan<uint32_t, 4>([&](uint32_t i) { return x[i]; }, x, n_tiles, ws1, true, &last);
+        // a last line without a trailing newline still counts (readlines() returns it)
+        if (last && threadIdx.x == 0) st->n_lines = t + ((n > 0 && text[n - 1] != '\n') ? 1u : 0u);
+    }
+}
+
+__device__ __forceinline__ double pow10_exact(uint32_t k)
+{
+    // 10^0 .. 10^22 are exactly representable in binary64
+    const double t[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15,
+                          1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    return t[k];
+}
+
+// Parse the numeric token starting at text[i].  Returns false when it is not a plain decimal literal or
+// cannot be converted exactly by the fast path.  *out = float(token) rounded to float32; *as_int = the
+// integer value when the token is an integer literal (labels, ids).
+__device__ inline bool parse_number(const uint8_t *__restrict__ text, unsigned long long i, unsigned long long n,
+                                    float *out, long long *as_int, uint32_t *ndigits_int)
+{
+    bool neg = false;
+    if (i < n && (text[i] == '-' || text[i] == '+')) { neg = text[i] == '-'; i++; }
+    unsigned long long m = 0;
+    int e10 = 0, sig = 0, digits = 0;
+    bool any = false, frac = false, is_int = true;
+    for (; i < n; i++) {
+        const uint32_t c = text[i];
+        if (c >= '0' && c <= '9') {
+            any = true;
+            digits++;
+            if (sig < 19) {
+                m = m * 10ull + (c - '0');
+                if (m) sig++;
+                if (frac) e10--;
+            } else {
+                if (c != '0') return false;             // a 20th significant digit: not exactly handled
+                if (!frac) e10++;
+            }
+        } else if (c == '.' && !frac) {
+            frac = true;
+            is_int = false;
+        } else {
+            break;
+        }
+    }
+    if (!any) return false;
+    if (i < n && (text[i] == 'e' || text[i] == 'E')) {
+        is_int = false;
+        i++;
+        bool eneg = false;
+        if (i < n && (text[i] == '-' || text[i] == '+')) { eneg = text[i] == '-'; i++; }
+        int ex = 0, nd = 0;
+        for (; i < n && text[i] >= '0' && text[i] <= '9'; i++, nd++) ex = ex < 100000 ? ex * 10 + (text[i] - '0') : ex;
+        if (nd == 0) return false;
+        e10 += eneg ? -ex : ex;
+    }
+    if (i < n && is_num_char(text[i])) return false;   // trailing letters / second sign: NaN, Infinity, 1.2.3 ...
+    double d;
+    if (m == 0) {
+        d = 0.0;
+    } else if (m < (1ull << 53) && e10 >= 0 && e10 <= 22) {
+        d = (double)m * pow10_exact((uint32_t)e10);
+    } else if (m < (1ull << 53) && e10 < 0 && e10 >= -22) {
+        d = (double)m / pow10_exact((uint32_t)-e10);
+    } else if (m < (1ull << 53) && e10 > 22 && e10 <= 22 + 15) {
+        // Clinger's extension: m * 10^(e10-22) is still an exact integer below 2^53 for small m
+        double mm = (double)m * pow10_exact((uint32_t)(e10 - 22));
+        if (mm >= 9007199254740992.0) return false;
+        d = mm * 1e22;
+    } else {
+        return false;
+    }
+    if (is_int && m == 0) neg = false;                   // "-0" is the Python int 0: np.float32(0) is +0.0 ("-0.0" stays -0.0)
+    *out = (float)(neg ? -d : d);                        // double -> float32, round to nearest even
+    *as_int = is_int ? (neg ? -(long long)m : (long long)m) : 0;
+    *ndigits_int = is_int ? (uint32_t)digits : 0u;
+    return true;
+}
+
+// Pass 3: every token start is parsed by the thread that owns its character.
+//   token t of the file: row = t / per_row, k = t % per_row; k == 0 -> id, k == per_row-1 -> label,
+//   otherwise feature k-1.  label_digits != 0: the label is a string of that many digits, each an int
+//   (etl_criteo.py:35-36).  Every line end must fall on a row boundary of the token stream.
+__global__ void __launch_bounds__(kTextThreads)
+k_text_parse(const uint8_t *__restrict__ text, unsigned long long n, const uint32_t *__restrict__ tile_tokens,
+             const uint32_t *__restrict__ tile_lines, uint32_t per_row, uint32_t label_digits,
+             float *__restrict__ features, long long *__restrict__ labels, long long *__restrict__ ids,
+             unsigned long long cap_rows, TextState *st)
+{
+    __shared__ uint32_t sh_tok[kTextThreads / 32], sh_nl[kTextThreads / 32];
+    const unsigned long long base = (unsigned long long)blockIdx.x * kTextTile + threadIdx.x * 16ull;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t flags = 0, nls = 0;                                             // bit k: token start / newline at base+k
+    uint32_t prev = (base > 0 && base <= n) ? text[base - 1] : '\n';
+    for (uint32_t k = 0; k < 16; k++) {
+        const unsigned long long i = base + k;
+        if (i >= n) break;
+        const uint32_t c = text[i];
+        if (is_num_char(c) && !is_num_char(prev)) flags |= 1u << k;
+        if (c == '\n') nls |= 1u << k;
+        prev = c;
+    }
+    // ranks inside the tile
+    uint32_t tcnt = __popc(flags), ncnt = __popc(nls), tinc = tcnt, ninc = ncnt;
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, tinc, d), b = __shfl_up_sync(0xffffffffu, ninc, d);
+        if (lane >= (uint32_t)d) { tinc += a; ninc += b; }
+    }
+    if (lane == 31) { sh_tok[warp] = tinc; sh_nl[warp] = ninc; }
+    __syncthreads();
+    uint32_t toff = 0, noff = 0;
+    for (uint32_t w = 0; w < warp; w++) { toff += sh_tok[w]; noff += sh_nl[w]; }
+    unsigned long long t = (unsigned long long)tile_tokens[blockIdx.x] + toff + tinc - tcnt;   // index of my first token
+    unsigned long long l = (unsigned long long)tile_lines[blockIdx.x] + noff + ninc - ncnt;    // lines ended before my chars
+    const uint32_t nfeat = per_row - 2u;
+    for (uint32_t k = 0; k < 16; k++) {
+        const unsigned long long i = base + k;
+        if ((flags >> k) & 1u) {
+            const unsigned long long row = t / per_row;
+            const uint32_t col = (uint32_t)(t - row * per_row);
+            float v;
+            long long iv;
+            uint32_t nd;
+            if (!parse_number(text, i, n, &v, &iv, &nd)) {
+                atomicMax(&st->err_inv, ~make_err_key(0, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_TEXT_NUMBER));
+            } else if (row < cap_rows) {
+                if (col == 0) { if (ids) ids[row] = iv; }
+                else if (col <= nfeat) features[row * nfeat + (col - 1u)] = v;
+                else if (!label_digits) labels[row] = iv;
+                else {
+                    if (nd != label_digits) atomicMax(&st->err_inv, ~make_err_key(1, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_SHAPE));
+                    else {
+                        unsigned long long x = (unsigned long long)iv;
+                        for (int q = (int)label_digits - 1; q >= 0; q--) { labels[row * label_digits + q] = (long long)(x % 10ull); x /= 10ull; }
+                    }
+                }
+            } else {
+                atomicMax(&st->err_inv, ~make_err_key(2, 0, 0, 0, CDS_ERR_CAPACITY));
+            }
+            t++;
+        }
+        if ((nls >> k) & 1u) {
+            // tokens seen so far (t) must be exactly (lines ended + 1) rows worth
+            if (t != (l + 1ull) * per_row)
+                atomicMax(&st->err_inv, ~make_err_key(1, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_SHAPE));
+            l++;
+        }
+    }
+}
+
+}  // namespace cds

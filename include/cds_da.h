@@ -41,6 +41,8 @@ enum cds_status {
     CDS_ERR_SHAPE = 12,         /* ValueError (array size vs. catalog shape)        ppr:167,173  */
     CDS_ERR_CATALOG_MISS = 13,  /* IndexError (.iloc[0] on an empty frame)          ppr:563-564  */
     CDS_ERR_MISSING_VALUE = 14, /* a pointer whose value has no chunks (reference: None entry)  */
+    CDS_ERR_TEXT_NUMBER = 15,   /* text ETL: NaN/Infinity/malformed literal (literal_eval raises too) or a
+                                   literal outside the exactly convertible range (see cds_text_etl)  */
     CDS_ERR_CUDA = 100,         /* a CUDA runtime call failed: see cds_last_error()             */
     CDS_ERR_ARG = 101,          /* bad argument                                                  */
     CDS_ERR_CAPACITY = 102,     /* rows / chunks / scratch / output larger than the capacity    */
@@ -219,6 +221,22 @@ int cds_f32_to_bf16(const void *d_src, uint64_t n_elems, void *d_dst, void *stre
 int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint32_t hw, uint32_t channels,
                        const void *d_labels, const void *d_indices, uint32_t batch, void *d_out, int out_bf16,
                        void *d_out_labels, void *stream);
+
+/* ---- text ETL ("next" row f-4) ---------------------------------------------------------------- */
+
+/* The parser of the filesystem ETL (etl_imagenet.py:30-37 `parser`, etl_criteo.py:28-37) for gpfdist
+ * TEXT unloads (unload_imagenet.sql:1-14): lines `id|{v,v,...}|label` in device memory -> features
+ * float32 [rows, values_per_row] (nested braces are flattened in file order, as np.asarray of the nested
+ * list), labels int64 [rows] (label_digits == 0: int(label), etl_imagenet.py:36) or int64 [rows,
+ * label_digits] (label is a digit string, one int per character, etl_criteo.py:35-36), ids int64 [rows]
+ * (may be NULL).  Numbers follow the reference's double rounding: float(token) exactly (decimal ->
+ * binary64, correctly rounded) then binary64 -> float32.  Exactly convertible range: at most 19
+ * significant digits with mantissa < 2^53 and a decimal exponent in [-22, 37]; anything else, NaN and
+ * Infinity return CDS_ERR_TEXT_NUMBER with the byte position in *err_pos.  A line whose token count is
+ * not values_per_row + 2 returns CDS_ERR_SHAPE.  Synchronous; *n_rows = lines parsed. */
+int cds_text_etl(int device, const void *d_text, uint64_t n_bytes, uint32_t values_per_row, uint32_t label_digits,
+                 void *d_features, void *d_labels, void *d_ids, uint64_t cap_rows, uint64_t *n_rows,
+                 uint64_t *err_pos, void *stream);
 
 #ifdef __cplusplus
 }

@@ -135,6 +135,48 @@ def frame_case(ref_reader):
     print("frames_small_mixed: %d df_toast rows, %d chunks -> %d KB" % (len(df_toast), len(chunks), os.path.getsize(path) // 1024))
 
 
+def text_etl_cases():
+    """Outputs of the reference's own text parsers (etl_imagenet.py:30-37, etl_criteo.py:28-37) on synthetic
+    gpfdist TEXT unload lines.  h5py / tqdm are stubbed: the parsers do not use them."""
+    for m in ("h5py", "tqdm"):
+        sys.modules.setdefault(m, types.ModuleType(m))
+    sys.path.insert(0, "/root/reference/cerebro_gpdb")
+    import etl_criteo
+    import etl_imagenet
+    rng = np.random.default_rng(99)
+    fmts = ["%.6g", "%.9g", "%.3f", "%d", "%.6e", "%.15g"]
+    lines = []
+    for r in range(40):                                       # ImageNet style: nested 4x3x3, int label
+        vals = rng.standard_normal(36) * 10.0 ** rng.integers(-5, 9, 36)
+        vals[rng.integers(0, 36, 4)] = 0.0
+        toks = []
+        for v in vals:
+            f = fmts[int(rng.integers(0, len(fmts)))]
+            toks.append(f % (int(v) if f == "%d" else v))
+        rows = ["{" + ",".join("{" + ",".join(toks[(i * 3 + j) * 3:(i * 3 + j) * 3 + 3]) + "}" for j in range(3)) + "}" for i in range(4)]
+        lines.append("%d|{%s}|%d\n" % (1000 + r, ",".join(rows), int(rng.integers(0, 1000))))
+    lines.append("7|{{{-0,+1.5,1e22},{123456789012345,0.000001,9007199254740991}," + "{1e-22,2.5e+10,-3E5}},{{1,2,3},{4,5,6},{7,8,9}},"
+                 "{{1,2,3},{4,5,6},{7,8,9}},{{1,2,3},{4,5,6},{7,8,9}}}|0")      # edge literals, no trailing newline
+    text_a = "".join(lines)
+    parsed = [etl_imagenet.parser(l) for l in text_a.splitlines(True)]
+    feats_a = np.stack([p[1] for p in parsed]).astype(np.float32)
+    assert feats_a.shape == (41, 4, 3, 3)
+    lines = []
+    for r in range(30):                                       # Criteo style: flat 0/1 floats, digit-string label
+        v = (rng.random(64) < 0.1).astype(int)
+        lines.append("%d|{%s}|%s\n" % (r, ",".join(str(x) for x in v), "01" if rng.random() < 0.3 else "10"))
+    text_b = "".join(lines)
+    parsed_b = [etl_criteo.parser(l) for l in text_b.splitlines(True)]
+    path = os.path.join(HERE, "text_etl.npz")
+    np.savez_compressed(path,
+                        text_a=np.frombuffer(text_a.encode(), dtype=np.uint8), ids_a=np.array([int(p[0]) for p in parsed]),
+                        feats_a=feats_a, labels_a=np.array([p[2] for p in parsed], dtype=np.int64),
+                        text_b=np.frombuffer(text_b.encode(), dtype=np.uint8), ids_b=np.array([int(p[0]) for p in parsed_b]),
+                        feats_b=np.array([p[1] for p in parsed_b], dtype=np.float32),
+                        labels_b=np.array([p[2] for p in parsed_b], dtype=np.int64))
+    print("text_etl: %d + %d lines -> %d KB" % (len(parsed), len(parsed_b), os.path.getsize(path) // 1024))
+
+
 def pglz_cases(ref_reader):
     """Known-answer vectors: (varlena incl. 8-byte header) -> bytes, decoded by BOTH reference decoders."""
     import ctypes
@@ -270,3 +312,4 @@ if __name__ == "__main__":
     frame_case(ref_reader)
     pglz_cases(ref_reader)
     error_cases(ref_reader, ref_da)
+    text_etl_cases()
