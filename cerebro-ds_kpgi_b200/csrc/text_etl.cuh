@@ -21,6 +21,7 @@ namespace cds {
 
 constexpr uint32_t kTextTile = 4096;          // characters per CTA tile
 constexpr uint32_t kTextThreads = 256;        // 16 characters per thread
+constexpr uint32_t kTextHalo = 64;            // characters of the next tile staged with this one
 
 __device__ __forceinline__ bool is_num_char(uint32_t c)
 {
@@ -34,6 +35,22 @@ struct TextState {
     unsigned long long pad;
 };
 
+// The 16 characters of this thread (zero past the end) and the character before them.
+__device__ __forceinline__ void load16(const uint8_t *__restrict__ text, unsigned long long base, unsigned long long n,
+                                       uint32_t w[4], uint32_t &prev)
+{
+    if (base + 16 <= n && ((reinterpret_cast<uintptr_t>(text) + base) & 15u) == 0) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(text + base));
+        w[0] = q.x; w[1] = q.y; w[2] = q.z; w[3] = q.w;
+    } else {
+        w[0] = w[1] = w[2] = w[3] = 0;
+        for (uint32_t k = 0; k < 16 && base + k < n; k++) w[k >> 2] |= (uint32_t)text[base + k] << ((k & 3) * 8);
+    }
+    // the previous thread holds my predecessor character; the first lane of a warp reads it
+    const uint32_t up = __shfl_up_sync(0xffffffffu, w[3] >> 24, 1);
+    prev = (threadIdx.x & 31) ? up : ((base > 0 && base <= n) ? (uint32_t)text[base - 1] : (uint32_t)'\n');
+}
+
 // Pass 1: per tile, how many tokens start and how many lines end inside it.
 __global__ void __launch_bounds__(kTextThreads)
 k_text_count(const uint8_t *__restrict__ text, unsigned long long n, uint32_t *__restrict__ tile_tokens,
@@ -41,14 +58,14 @@ k_text_count(const uint8_t *__restrict__ text, unsigned long long n, uint32_t *_
 {
     __shared__ uint32_t sh[2][kTextThreads / 32];
     const unsigned long long base = (unsigned long long)blockIdx.x * kTextTile + threadIdx.x * 16ull;
-    uint32_t tok = 0, nl = 0;
-    uint32_t prev = (base > 0 && base <= n) ? text[base - 1] : '\n';
+    uint32_t tok = 0, nl = 0, w[4], prev;
+    load16(text, base, n, w, prev);
+#pragma unroll
     for (uint32_t k = 0; k < 16; k++) {
-        const unsigned long long i = base + k;
-        if (i >= n) break;
-        const uint32_t c = text[i];
-        tok += (is_num_char(c) && !is_num_char(prev)) ? 1u : 0u;
-        nl += (c == '\n') ? 1u : 0u;
+        const uint32_t c = (w[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
+        const bool in = base + k < n;
+        tok += (in && is_num_char(c) && !is_num_char(prev)) ? 1u : 0u;
+        nl += (in && c == '\n') ? 1u : 0u;
         prev = c;
     }
     for (int d = 16; d > 0; d >>= 1) { tok += __shfl_xor_sync(0xffffffffu, tok, d); nl += __shfl_xor_sync(0xffffffffu, nl, d); }
@@ -80,13 +97,10 @@ k_text_scan(uint32_t *tile_tokens, uint32_t *tile_lines, uint32_t n_tiles, ScanW
     }
 }
 
-__device__ __forceinline__ double pow10_exact(uint32_t k)
-{
-    // 10^0 .. 10^22 are exactly representable in binary64
-    const double t[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15,
-                          1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
-    return t[k];
-}
+// 10^0 .. 10^22 are exactly representable in binary64
+__constant__ double kPow10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15,
+                                  1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+__device__ __forceinline__ double pow10_exact(uint32_t k) { return kPow10[k]; }
 
 // Parse the numeric token starting at text[i].  Returns false when it is not a plain decimal literal or
 // cannot be converted exactly by the fast path.  *out = float(token) rounded to float32; *as_int = the
@@ -164,16 +178,23 @@ k_text_parse(const uint8_t *__restrict__ text, unsigned long long n, const uint3
              unsigned long long cap_rows, TextState *st)
 {
     __shared__ uint32_t sh_tok[kTextThreads / 32], sh_nl[kTextThreads / 32];
-    const unsigned long long base = (unsigned long long)blockIdx.x * kTextTile + threadIdx.x * 16ull;
+    __shared__ __align__(16) uint8_t tile[kTextTile + kTextHalo];           // this tile's characters + the start of the next
+    const unsigned long long tile_base = (unsigned long long)blockIdx.x * kTextTile;
+    const unsigned long long base = tile_base + threadIdx.x * 16ull;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t flags = 0, nls = 0;                                             // bit k: token start / newline at base+k
-    uint32_t prev = (base > 0 && base <= n) ? text[base - 1] : '\n';
+    uint32_t flags = 0, nls = 0, w[4], prev;                                 // bit k: token start / newline at base+k
+    load16(text, base, n, w, prev);
+    *reinterpret_cast<uint4 *>(tile + threadIdx.x * 16u) = make_uint4(w[0], w[1], w[2], w[3]);
+    if (threadIdx.x < kTextHalo) {
+        const unsigned long long h = tile_base + kTextTile + threadIdx.x;
+        tile[kTextTile + threadIdx.x] = h < n ? text[h] : (uint8_t)'\n';
+    }
+#pragma unroll
     for (uint32_t k = 0; k < 16; k++) {
-        const unsigned long long i = base + k;
-        if (i >= n) break;
-        const uint32_t c = text[i];
-        if (is_num_char(c) && !is_num_char(prev)) flags |= 1u << k;
-        if (c == '\n') nls |= 1u << k;
+        const uint32_t c = (w[k >> 2] >> ((k & 3) * 8)) & 0xFFu;
+        const bool in = base + k < n;
+        if (in && is_num_char(c) && !is_num_char(prev)) flags |= 1u << k;
+        if (in && c == '\n') nls |= 1u << k;
         prev = c;
     }
     // ranks inside the tile
@@ -189,38 +210,51 @@ k_text_parse(const uint8_t *__restrict__ text, unsigned long long n, const uint3
     unsigned long long t = (unsigned long long)tile_tokens[blockIdx.x] + toff + tinc - tcnt;   // index of my first token
     unsigned long long l = (unsigned long long)tile_lines[blockIdx.x] + noff + ninc - ncnt;    // lines ended before my chars
     const uint32_t nfeat = per_row - 2u;
-    for (uint32_t k = 0; k < 16; k++) {
+    const unsigned long long staged = min((unsigned long long)(kTextTile + kTextHalo), n - min(n, tile_base));
+    // Every lane walks its own token starts (lowest first), so that the j-th tokens of all lanes are parsed together.
+    uint32_t todo = flags;
+    while (todo) {
+        const uint32_t k = (uint32_t)__ffs((int)todo) - 1u;
+        todo &= todo - 1u;
         const unsigned long long i = base + k;
-        if ((flags >> k) & 1u) {
-            const unsigned long long row = t / per_row;
-            const uint32_t col = (uint32_t)(t - row * per_row);
-            float v;
-            long long iv;
-            uint32_t nd;
-            if (!parse_number(text, i, n, &v, &iv, &nd)) {
-                atomicMax(&st->err_inv, ~make_err_key(0, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_TEXT_NUMBER));
-            } else if (row < cap_rows) {
-                if (col == 0) { if (ids) ids[row] = iv; }
-                else if (col <= nfeat) features[row * nfeat + (col - 1u)] = v;
-                else if (!label_digits) labels[row] = iv;
+        const unsigned long long row = t / per_row;
+        const uint32_t col = (uint32_t)(t - row * per_row);
+        float v;
+        long long iv;
+        uint32_t nd;
+        // tokens are parsed out of shared memory; one that could run past the staged halo goes to global memory
+        const uint32_t li = threadIdx.x * 16u + k;
+        const bool ok = (li + 48u <= staged || staged == n - tile_base) ? parse_number(tile, li, staged, &v, &iv, &nd)
+                                                                       : parse_number(text, i, n, &v, &iv, &nd);
+        if (!ok) {
+            atomicMax(&st->err_inv, ~make_err_key(0, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_TEXT_NUMBER));
+        } else if (row < cap_rows) {
+            if (col == 0) { if (ids) ids[row] = iv; }
+            else if (col <= nfeat) features[row * nfeat + (col - 1u)] = v;
+            else if (!label_digits) labels[row] = iv;
+            else {
+                if (nd != label_digits) atomicMax(&st->err_inv, ~make_err_key(1, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_SHAPE));
                 else {
-                    if (nd != label_digits) atomicMax(&st->err_inv, ~make_err_key(1, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_SHAPE));
-                    else {
-                        unsigned long long x = (unsigned long long)iv;
-                        for (int q = (int)label_digits - 1; q >= 0; q--) { labels[row * label_digits + q] = (long long)(x % 10ull); x /= 10ull; }
-                    }
+                    unsigned long long x = (unsigned long long)iv;
+                    for (int q = (int)label_digits - 1; q >= 0; q--) { labels[row * label_digits + q] = (long long)(x % 10ull); x /= 10ull; }
                 }
-            } else {
-                atomicMax(&st->err_inv, ~make_err_key(2, 0, 0, 0, CDS_ERR_CAPACITY));
             }
-            t++;
+        } else {
+            atomicMax(&st->err_inv, ~make_err_key(2, 0, 0, 0, CDS_ERR_CAPACITY));
         }
-        if ((nls >> k) & 1u) {
-            // tokens seen so far (t) must be exactly (lines ended + 1) rows worth
-            if (t != (l + 1ull) * per_row)
-                atomicMax(&st->err_inv, ~make_err_key(1, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_SHAPE));
-            l++;
-        }
+        t++;
+    }
+    // line ends: the tokens seen before a newline must be exactly (lines ended + 1) rows worth
+    const unsigned long long t0 = t - tcnt;
+    todo = nls;
+    while (todo) {
+        const uint32_t k = (uint32_t)__ffs((int)todo) - 1u;
+        todo &= todo - 1u;
+        const unsigned long long i = base + k;
+        const unsigned long long t_at = t0 + __popc(flags & ((1u << k) - 1u));
+        const unsigned long long l_at = l + __popc(nls & ((1u << k) - 1u));
+        if (t_at != (l_at + 1ull) * per_row)
+            atomicMax(&st->err_inv, ~make_err_key(1, i >> 4, 0, (uint32_t)(i & 15), CDS_ERR_SHAPE));
     }
 }
 
