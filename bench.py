@@ -226,7 +226,7 @@ def run_reference_arm(args):
                         "note": "oracle/da_oracle.py: pure-Python restatement with the shipped reference's loop structure, "
                                 "1 process (as the reference runs), 2 pglz rows / 64 uncompressed rows; context only"},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -255,6 +255,8 @@ def run_ours(args):
         log("note: WORLD_SIZE=%d, --gpus=%d" % (world, args.gpus))
     L = _lib.require_device()
     torch.cuda.set_device(local)
+    from cerebro_ds_kpgi_b200 import hostnuma
+    numa = hostnuma.bind_to_gpu_node(local)          # before any staging buffer is allocated or touched
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -428,15 +430,35 @@ def run_ours(args):
             "h2d": {"gb_per_s": h2d_gbs, "note": "cudaMemcpyAsync from pinned memory alone; PCIe Gen5 x16 ~63 GB/s theoretical"},
             "gpu_launches": launches,
             "clocks": clocks,
+            "host": {"numa_bind_rank0": numa, "cores_visible": host_threads()},
         }
         if cpu:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def protect_stdout():
+    """Libraries (NCCL's version banner, for one) write to fd 1.  The contract is ONE JSON line on stdout, so fd 1 is
+    pointed at stderr for the whole run and the JSON line goes to the saved descriptor at the end."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
+REAL_STDOUT = None
+
+
+def emit(line):
+    REAL_STDOUT.write(json.dumps(line) + "\n")
+    REAL_STDOUT.flush()
+
+
 def main():
+    global REAL_STDOUT
+    REAL_STDOUT = protect_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

@@ -9,4 +9,4 @@ repository root maps the identifier onto it).
 """
 __version__ = "0.1.0"
 
-__all__ = ["pg_page_reader", "da", "segment", "consumers", "synth", "build"]
+__all__ = ["pg_page_reader", "da", "segment", "consumers", "etl", "mop", "hostnuma", "synth", "build"]
