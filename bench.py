@@ -178,53 +178,103 @@ def cpu_decode_rate(seg, meta, reps, threads=0):
     return meta["rows"] / best, best, threads
 
 
-def python_port_rate(n_rows=2, storage="ext_pglz"):
-    """rows/s of the pure-Python restatement (same loop structure as the shipped reference,
-    pg_page_reader.py:191-231,364-448,527-612) on a few ImageNet rows, one core — context only."""
+# The reference arm ("reference-C x N"): the reference's reader is Python; its structure is
+# restated in oracle/da_oracle.py, pglz goes through the reference's own pg_lzcompress.c (oracle/_ref) when that
+# was compiled, and the work is spread over all host cores as disjoint row ranges, one sub-segment per process.
+_REF_PART = None          # (heap, toast, buffers) of THIS worker process
+
+
+def _ref_pglz():
     sys.path.insert(0, os.path.join(REPO, "oracle"))
     import da_oracle
-    from cerebro_ds_kpgi_b200 import synth
-    ind, dep = synth.imagenet_rows(n_rows, seed=2018, kind="norm_u8")
-    seg = synth.build_segment(ind, dep, ind_storage=storage, dep_storage="inline_pglz")
-    t0 = time.perf_counter()
-    da_oracle.input_fn_bytes(seg.heap, seg.toast, None)
-    return n_rows / (time.perf_counter() - t0)
+    try:
+        return da_oracle.RefPglz().pglz_decompress, "oracle/_ref/pg_lzcompress.so (the reference's own C decoder)"
+    except RuntimeError:
+        return da_oracle.COracle().pglz_decompress, "oracle/da_oracle.c pglz (oracle/_ref not built on this machine)"
+
+
+def _ref_init(counter, workload, part_mib):
+    """Worker start-up (spawned, so nothing CUDA-related is inherited): build this worker's sub-segment."""
+    global _REF_PART
+    with counter.get_lock():
+        idx = counter.value
+        counter.value += 1
+    seg, meta = make_workload(workload, 2018 + 100 * idx, part_mib)
+    _REF_PART = (seg.heap, seg.toast, len(seg.rows), _ref_pglz()[0])
+
+
+def _ref_worker(_):
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    import da_oracle
+    heap, toast, buffers, pglz = _REF_PART
+    out = da_oracle.input_fn_bytes(heap, toast, None, pglz=pglz)
+    assert len(out) == buffers
+    return buffers
+
+
+class PythonPortPool:
+    """oracle/da_oracle.py (pure-Python page walk / detoast, the reference's loop structure) over all cores:
+    `procs` spawned workers, each holding one sub-segment of 1/procs of the workload's rows."""
+
+    def __init__(self, workload, toast_mib, procs):
+        import multiprocessing as mp
+        ctx = mp.get_context("spawn")
+        self.procs = procs
+        part_mib = max(1, toast_mib // procs)
+        seg, meta = make_workload(workload, 2018, part_mib)
+        self.rows, self.buffers = procs * meta["rows"], procs * len(seg.rows)
+        self.pool = ctx.Pool(procs, initializer=_ref_init, initargs=(ctx.Value("i", 0), workload, part_mib))
+        self.pglz_note = _ref_pglz()[1]
+        self.step(1)                                              # every worker up and its sub-segment built
+
+    def step(self, repeats=1):
+        t0 = time.perf_counter()
+        for _ in range(repeats):
+            got = sum(self.pool.map(_ref_worker, range(self.procs), chunksize=1))
+            assert got == self.buffers, (got, self.buffers)
+        return time.perf_counter() - t0
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+    def describe(self, repeats):
+        return ("%d x the %d-row workload per step as %d sub-segments, one process each: oracle/da_oracle.py (Python restatement "
+                "of pg_page_reader.py's page walk / detoast) with pglz through %s" % (repeats, self.rows, self.procs, self.pglz_note))
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    seg, meta = make_workload(args.workload, 2018, args.toast_mib)
     threads = host_threads()
     n_seg = max(1, args.gpus)          # the whole job: one segment per GPU of our arm, decoded on this host's cores
+    pool = PythonPortPool(args.workload, args.toast_mib, threads)
     times = []
     for i in range(args.warmup + args.steps):
-        dt = 0.0
-        for _ in range(n_seg):
-            rate, t, used = cpu_decode_rate(seg, meta, 1, threads=0)
-            dt += t
+        dt = pool.step(n_seg)
         if i >= args.warmup:
             times.append(dt)
+    pool.close()
     ms = 1000.0 * float(np.mean(times))
-    value = n_seg * meta["rows"] / (ms / 1000.0)
+    value = n_seg * pool.rows / (ms / 1000.0)
+    # the much faster all-C restatement, for transparency (not what the reference ships)
+    seg, meta = make_workload(args.workload, 2018, args.toast_mib)
+    c_rate, c_dt, c_threads = cpu_decode_rate(seg, meta, 3)
     alg_bytes = seg.heap.size + seg.toast.size + meta["ind_bytes"] + meta["dep_bytes"] + 8 * meta["rows"]
     line = {
         "impl": "reference", "metric": "decoded_rows_per_s", "value": value, "unit": "rows/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "gb_per_s": n_seg * alg_bytes / (ms / 1000.0) / 1e9,
-        "config": {"workload": args.workload, "description": meta["desc"], "rows_per_segment": meta["rows"],
+        "gb_per_s": value * alg_bytes / meta["rows"] / 1e9,
+        "config": {"workload": args.workload, "description": meta["desc"], "rows_per_segment": pool.rows,
                    "toast_mib": seg.toast.size >> 20, "segments": n_seg},
-        "cpu_baseline": {"value": value, "unit": "rows/s", "cores": used, "kind": "port",
-                         "sample": "%d x whole %d MiB segment per step, oracle/da_oracle.c (C restatement of "
-                                   "pg_page_reader.py + pg_lzcompress.c), OpenMP over values; the shipped reference is a "
-                                   "pure-Python loop and cannot read uncompressed external values" % (n_seg, seg.toast.size >> 20)},
+        "cpu_baseline": {"value": value, "unit": "rows/s", "cores": threads, "kind": "port", "sample": pool.describe(n_seg)},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "host_cores": threads,
-        "python_port": {"pglz_rows_per_s": python_port_rate(2, "ext_pglz"), "uncompressed_rows_per_s": python_port_rate(64, "ext_raw"),
-                        "note": "oracle/da_oracle.py: pure-Python restatement with the shipped reference's loop structure, "
-                                "1 process (as the reference runs), 2 pglz rows / 64 uncompressed rows; context only"},
+        "c_port_openmp": {"value": c_rate, "unit": "rows/s", "cores": c_threads, "ms_per_segment": 1000.0 * c_dt,
+                          "note": "oracle/da_oracle.c, the whole path in C with OpenMP over values: far faster than anything the "
+                                  "reference ships (its reader is a Python loop); reported so that nothing is hidden"},
     }
     emit(line)
 
@@ -401,12 +451,17 @@ def run_ours(args):
         # CPU baseline on this host (rank 0 only, N=1 only)
         cpu = None
         if world == 1 and not args.no_cpu:
-            rate, dt, cores = cpu_decode_rate(seg, meta, reps=3)
-            cpu = {"value": rate, "unit": "rows/s", "cores": cores, "kind": "port",
-                   "sample": "whole %d MiB segment, best of 3, oracle/da_oracle.c with OpenMP over values (%.0f ms)" % (
-                       seg.toast.size >> 20, dt * 1000.0),
-                   "python_port_rows_per_s": python_port_rate(2, "ext_pglz"),
-                   "python_port_note": "pure-Python restatement (the shipped reference's loop structure) on 2 pglz rows, 1 core"}
+            threads = host_threads()
+            pool = PythonPortPool(args.workload, args.toast_mib, threads)
+            pool.step(1)                                         # warm the workers up
+            dt = min(pool.step(1), pool.step(1))
+            pool.close()
+            c_rate, c_dt, c_threads = cpu_decode_rate(seg, meta, reps=3)
+            cpu = {"value": pool.rows / dt, "unit": "rows/s", "cores": threads, "kind": "port",
+                   "sample": pool.describe(1) + " (best of 2, %.0f ms)" % (dt * 1000.0),
+                   "c_port_openmp_rows_per_s": c_rate,
+                   "c_port_note": "oracle/da_oracle.c, whole path in C + OpenMP (%d threads, %.0f ms per segment): much faster "
+                                  "than the reference's Python reader; kept beside it for transparency" % (c_threads, c_dt * 1000.0)}
         line = {
             "metric": "decoded_rows_per_s", "value": rows_total / (dev_ms_max / 1000.0), "unit": "rows/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms_max,
