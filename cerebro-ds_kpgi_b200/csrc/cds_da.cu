@@ -603,6 +603,35 @@ extern "C" int cds_export_chunks(cds_segment *s, uint32_t *h_id, uint32_t *h_seq
 
 // ---- pglz on its own ---------------------------------------------------------------------------
 
+// One thread per datum: read the 8-byte header on the device and fill the job slot.
+__global__ void __launch_bounds__(256)
+k_build_pglz_jobs(const uint8_t *__restrict__ src, const unsigned long long *__restrict__ src_off, uint8_t *dst,
+                  const unsigned long long *__restrict__ dst_off, uint32_t n, PglzJob *__restrict__ jobs,
+                  int32_t *__restrict__ status, DevState *st)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        PglzJob j;
+        j.src = 0; j.dst = 0; j.slen = kNone; j.rawsize = 0;
+        j.err_key = make_err_key(2, i, 0, 0, CDS_ERR_PGLZ_CORRUPT);
+        const unsigned long long avail = src_off[i + 1] - src_off[i], room = dst_off[i + 1] - dst_off[i];
+        int32_t stat = CDS_ERR_PGLZ_CORRUPT;
+        if (avail >= 8) {
+            const uint8_t *h = src + src_off[i];
+            const uint32_t varsize = ld_u32be(h) & 0x3FFFFFFFu, rawsize = ld_u32(h + 4);
+            if (varsize >= 8 && varsize <= avail && rawsize <= room) {
+                j.src = (unsigned long long)(h + 8);
+                j.dst = (unsigned long long)(dst + dst_off[i]);
+                j.slen = varsize - 8;
+                j.rawsize = rawsize;
+                stat = CDS_OK;
+            }
+        }
+        if (stat != CDS_OK && st) report_key(st, j.err_key);
+        status[i] = stat;
+        jobs[i] = j;
+    }
+}
+
 extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_src_off, void *d_dst,
                                          const uint64_t *h_dst_off, uint64_t n, int32_t *h_status, void *stream)
 {
@@ -611,51 +640,33 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
     if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(device));
-    // headers are read on the host side of the call: fetch the 8 header bytes of every datum
-    PglzJob *h_jobs = (PglzJob *)malloc(sizeof(PglzJob) * n);
-    int32_t *h_stat = (int32_t *)calloc(n, sizeof(int32_t));
-    if (!h_jobs || !h_stat) { free(h_jobs); free(h_stat); return CDS_ERR_ARG; }
-    const uint8_t *src = static_cast<const uint8_t *>(d_src);
-    uint8_t *dst = static_cast<uint8_t *>(d_dst);
-    cudaError_t e = cudaSuccess;
-    for (uint64_t i = 0; i < n && e == cudaSuccess; i++) {
-        PglzJob &j = h_jobs[i];
-        j.src = 0; j.dst = 0; j.slen = kNone; j.rawsize = 0; j.err_key = 0;
-        const uint64_t avail = h_src_off[i + 1] - h_src_off[i], room = h_dst_off[i + 1] - h_dst_off[i];
-        uint8_t hdr[8];
-        if (avail < 8) { h_stat[i] = CDS_ERR_PGLZ_CORRUPT; continue; }
-        e = cudaMemcpyAsync(hdr, src + h_src_off[i], 8, cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-        if (e != cudaSuccess) break;
-        const uint32_t varsize = (((uint32_t)hdr[0] << 24) | ((uint32_t)hdr[1] << 16) | ((uint32_t)hdr[2] << 8) | hdr[3]) & 0x3FFFFFFFu;
-        const uint32_t rawsize = (uint32_t)hdr[4] | ((uint32_t)hdr[5] << 8) | ((uint32_t)hdr[6] << 16) | ((uint32_t)hdr[7] << 24);
-        if (varsize < 8 || varsize > avail || rawsize > room) { h_stat[i] = CDS_ERR_PGLZ_CORRUPT; continue; }
-        j.src = (unsigned long long)(src + h_src_off[i] + 8);
-        j.dst = (unsigned long long)(dst + h_dst_off[i]);
-        j.slen = varsize - 8;
-        j.rawsize = rawsize;
-    }
+    // work arrays of this call: the two offset tables, one job per datum, status words + the ticket counter
+    unsigned long long *d_off = nullptr;
     PglzJob *d_jobs = nullptr;
     int32_t *d_stat = nullptr;
+    cudaError_t e = dalloc(&d_off, 2 * (n + 1));
     if (e == cudaSuccess) e = dalloc(&d_jobs, n);
-    if (e == cudaSuccess) e = dalloc(&d_stat, n + 1);                       // + the work counter
+    if (e == cudaSuccess) e = dalloc(&d_stat, n + 1);
     if (e == cudaSuccess) e = cudaMemsetAsync(d_stat + n, 0, sizeof(int32_t), st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_jobs, h_jobs, sizeof(PglzJob) * n, cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_stat, h_stat, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, h_src_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off + n + 1, h_dst_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
     if (e == cudaSuccess) {
+        k_build_pglz_jobs<<<(uint32_t)((n + 255) / 256), 256, 0, st>>>(static_cast<const uint8_t *>(d_src), d_off,
+                                                                       static_cast<uint8_t *>(d_dst), d_off + n + 1, (uint32_t)n,
+                                                                       d_jobs, d_stat, nullptr);
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > 148u * 7u) grid = 148u * 7u;
         k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, (uint32_t)n, d_stat, nullptr,
                                                                      reinterpret_cast<uint32_t *>(d_stat + n));
         e = cudaGetLastError();
+        LAUNCHED(2);
     }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(h_stat, d_stat, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && h_status) e = cudaMemcpyAsync(h_status, d_stat, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e == cudaSuccess && h_status) memcpy(h_status, h_stat, sizeof(int32_t) * n);
+    if (d_off) cudaFree(d_off);
     if (d_jobs) cudaFree(d_jobs);
     if (d_stat) cudaFree(d_stat);
-    free(h_jobs); free(h_stat);
     if (e != cudaSuccess) return cuda_fail(e, "cds_pglz_decompress_batch");
     return CDS_OK;
 }
@@ -697,35 +708,6 @@ static int static_scratch_for(int device, StaticScratch **out)
     }
     *out = static_cast<StaticScratch *>(g_static_addr[device]);
     return CDS_OK;
-}
-
-// One thread per datum: read the 8-byte header on the device and fill the job slot.
-__global__ void __launch_bounds__(256)
-k_build_pglz_jobs(const uint8_t *__restrict__ src, const unsigned long long *__restrict__ src_off, uint8_t *dst,
-                  const unsigned long long *__restrict__ dst_off, uint32_t n, PglzJob *__restrict__ jobs,
-                  int32_t *__restrict__ status, DevState *st)
-{
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        PglzJob j;
-        j.src = 0; j.dst = 0; j.slen = kNone; j.rawsize = 0;
-        j.err_key = make_err_key(2, i, 0, 0, CDS_ERR_PGLZ_CORRUPT);
-        const unsigned long long avail = src_off[i + 1] - src_off[i], room = dst_off[i + 1] - dst_off[i];
-        int32_t stat = CDS_ERR_PGLZ_CORRUPT;
-        if (avail >= 8) {
-            const uint8_t *h = src + src_off[i];
-            const uint32_t varsize = ld_u32be(h) & 0x3FFFFFFFu, rawsize = ld_u32(h + 4);
-            if (varsize >= 8 && varsize <= avail && rawsize <= room) {
-                j.src = (unsigned long long)(h + 8);
-                j.dst = (unsigned long long)(dst + dst_off[i]);
-                j.slen = varsize - 8;
-                j.rawsize = rawsize;
-                stat = CDS_OK;
-            }
-        }
-        if (stat != CDS_OK) report_key(st, j.err_key);
-        status[i] = stat;
-        jobs[i] = j;
-    }
 }
 
 __global__ void k_publish_first_corrupt(const DevState *st, long long *first_corrupt)

@@ -19,6 +19,7 @@ import re
 import numpy as np
 
 from . import _lib
+from . import hostio
 from . import pg_page_reader
 from . import segment as _segment
 from .pg_page_reader import logs, table_page_read, toast_page_read  # noqa: F401  (same names as da.py:20-22)
@@ -46,14 +47,12 @@ def _decode_files(table_page_path, toast_page_path, ind_sample_bytes=0, dep_samp
     import torch
     _lib.require_device()
     logs("START READING TABLE: {}".format(table_page_path))
-    h_hold, heap_host, heap_partial = pg_page_reader.read_relation(table_page_path)
+    d_heap, heap_partial = hostio.relation_to_device(table_page_path, pg_page_reader.relation_files)
     logs("END READING TABLE: {}".format(table_page_path))
     logs("START READING TOAST: {}".format(toast_page_path))
-    t_hold, toast_host, toast_partial = pg_page_reader.read_relation(toast_page_path)
+    d_toast, toast_partial = hostio.relation_to_device(toast_page_path, pg_page_reader.relation_files)
     logs("END READING TOAST: {}".format(toast_page_path))
     logs("START DETOASTING")
-    d_heap = pg_page_reader._to_device(heap_host)
-    d_toast = pg_page_reader._to_device(toast_host)
     status, part = _segment.decode_pages(d_heap, d_toast, ind_sample_bytes=ind_sample_bytes,
                                          dep_sample_bytes=dep_sample_bytes, ind_bf16=ind_bf16)
     torch.cuda.synchronize()
@@ -81,12 +80,8 @@ def input_fn(file_path, overwrite_table_page_path=None, overwrite_toast_page_pat
     if overwrite_toast_page_path:
         toast_page_path = overwrite_toast_page_path
     part = _decode_files(table_page_path, toast_page_path)
-    ind_host = np.empty(part.ind.numel(), dtype=np.uint8)
-    dep_host = np.empty(part.dep.numel(), dtype=np.uint8)
-    if ind_host.size:
-        torch.from_numpy(ind_host).copy_(part.ind)
-    if dep_host.size:
-        torch.from_numpy(dep_host).copy_(part.dep)
+    ind_host = hostio.device_to_numpy(part.ind)
+    dep_host = hostio.device_to_numpy(part.dep)
     out = pg_page_reader._assemble(part, ind_host, dep_host, df_shape, table_name)
     logs("END DETOASTING")
     logs("ITEM NUM:{}, BUFFER_IDs:{}".format(len(out.keys()), out.keys()))

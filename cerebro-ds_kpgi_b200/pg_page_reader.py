@@ -276,7 +276,7 @@ def _rows_to_frames(rows, heap_host):
 def _scan_heap(page_dir):
     import torch
     _lib.require_device()
-    holder, heap_host, partial = read_relation(page_dir)
+    holder, heap_host, partial = read_relation(page_dir, pinned=False)     # small; its bytes are needed on the host too
     n_pages = heap_host.size // BLOCK_SIZE
     seg = _segment.DeviceSegment(max(1, n_pages), 0)
     try:
@@ -418,13 +418,8 @@ def _detoast_on_device(d_heap, d_toast, rows, inline_blob, df_shape, table_name,
     if partial:
         raise_for_status(_lib.CDS_ERR_PARTIAL_PAGE)
     raise_for_status(status)
-    ind_host = np.empty(part.ind.numel(), dtype=np.uint8)
-    dep_host = np.empty(part.dep.numel(), dtype=np.uint8)
-    if ind_host.size:
-        torch.from_numpy(ind_host).copy_(part.ind)
-    if dep_host.size:
-        torch.from_numpy(dep_host).copy_(part.dep)
-    return _assemble(part, ind_host, dep_host, df_shape, table_name)
+    from . import hostio
+    return _assemble(part, hostio.device_to_numpy(part.ind), hostio.device_to_numpy(part.dep), df_shape, table_name)
 
 
 def toast_page_read(page_dir, df_toast, df_shape, table_name):
@@ -433,9 +428,9 @@ def toast_page_read(page_dir, df_toast, df_shape, table_name):
     import torch
     _lib.require_device()
     logs("START READING TOAST: {}".format(page_dir))
+    from . import hostio
     rows, blob = _rows_from_df_toast(df_toast)
-    holder, toast_host, partial = read_relation(page_dir)
-    d_toast = _to_device(toast_host)
+    d_toast, partial = hostio.relation_to_device(page_dir, relation_files)
     d_blob = torch.from_numpy(blob.copy()).cuda()
     logs("END READING TOAST: {}".format(page_dir))
     logs("START DETOASTING")
