@@ -230,8 +230,9 @@ int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint32_t hw, ui
  * list), labels int64 [rows] (label_digits == 0: int(label), etl_imagenet.py:36) or int64 [rows,
  * label_digits] (label is a digit string, one int per character, etl_criteo.py:35-36), ids int64 [rows]
  * (may be NULL).  Numbers follow the reference's double rounding: float(token) exactly (decimal ->
- * binary64, correctly rounded) then binary64 -> float32.  Exactly convertible range: at most 19
- * significant digits with mantissa < 2^53 and a decimal exponent in [-22, 37]; anything else, NaN and
+ * binary64, correctly rounded: Eisel-Lemire with Clinger's path as back-up) then binary64 -> float32.
+ * Accepted: at most 19 significant digits and a decimal exponent (after shifting the digits into the
+ * mantissa) in [-80, 60] — every float4/float8 text value of the unloads; anything else, NaN and
  * Infinity return CDS_ERR_TEXT_NUMBER with the byte position in *err_pos.  A line whose token count is
  * not values_per_row + 2 returns CDS_ERR_SHAPE.  Synchronous; *n_rows = lines parsed. */
 int cds_text_etl(int device, const void *d_text, uint64_t n_bytes, uint32_t values_per_row, uint32_t label_digits,

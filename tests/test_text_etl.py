@@ -59,7 +59,15 @@ def test_gpu_text_etl_random_lines_vs_oracle_and_refusals():
     assert np.array_equal(got[0], want[0]) and np.array_equal(got[2], want[2])
     assert got[1].tobytes() == want[1].tobytes()
     # literal_eval raises on these; so does the GPU parser
-    for bad in (b"1|{NaN,1}|0\n", b"1|{Infinity,1}|0\n", b"1|{1.5.2,1}|0\n", b"1|{1e-30,1}|0\n"):
+    # the whole float4 range in PostgreSQL's text form, subnormals and extremes included, plus long mantissas
+    vals = np.concatenate([np.float32(10.0) ** rng.uniform(-44.9, 38.5, 4000).astype(np.float32) * rng.choice([-1, 1], 4000),
+                           np.array([1.17549435e-38, 3.40282347e+38, 1.4e-45, 0.1, 16777217.0], dtype=np.float64)])
+    toks = ["%.9g" % v for v in vals] + ["%.17g" % float(v) for v in vals[:500]] + ["1234567890123456789", "0.000000000000000000012345"]
+    line = ("5|{%s}|3\n" % ",".join(toks)).encode()
+    want = da_oracle.text_parse(line)
+    got = etl.parse_text(line, len(toks))
+    assert got[1].tobytes() == want[1].tobytes()
+    for bad in (b"1|{NaN,1}|0\n", b"1|{Infinity,1}|0\n", b"1|{1.5.2,1}|0\n", b"1|{1e-300,1}|0\n", b"1|{12345678901234567891,1}|0\n"):
         with pytest.raises(ValueError):
             etl.parse_text(bad, 2)
     with pytest.raises(ValueError):
