@@ -74,7 +74,7 @@ def make_workload(name, seed, toast_mib):
         B = 256
         per_buf = B * 7306 * 4
         n = max(1, (target * 20) // per_buf)       # ~20x compression: size the TOAST file, not the output
-        n = min(n, 200)
+        n = min(n, 1024)           # a real partition holds ~6 300 such buffers (1 624 157 rows / 256)
         ind, dep = synth.criteo_buffers(n, seed=seed, rows_per_buffer=B)
         seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="inline_pglz", dist_key=seed - 2018,
                                   keep_expected=False, effort=4)
