@@ -208,7 +208,8 @@ k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t
                 } else {
                     atomicMin(&vfirst[ref], g);
                     atomicAdd(&vcount[ref], 1u);
-                    atomicAdd(&vbytes[ref], (unsigned long long)loc_len);
+                    // low 36 bits: payload bytes of the value; high 28 bits: sum of its chunk_seq (mod 2^28)
+                    atomicAdd(&vbytes[ref], (unsigned long long)loc_len + ((unsigned long long)(seq & 0x0FFFFFFFu) << 36));
                     if (seq == 0) atomicMin(&vseq0[ref], g);
                 }
             }
@@ -374,7 +375,8 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
             const uint32_t first = A.vfirst[v];
             const uint2 id = A.dir_id[g], loc = A.dir_loc[g];
             const uint32_t idx = id.y, size = loc.y >> 16;
-            const unsigned long long vb = A.vbytes[v];
+            const unsigned long long vb = A.vbytes[v] & 0xFFFFFFFFFull;
+            const uint32_t seqsum = (uint32_t)(A.vbytes[v] >> 36);
             bool ok = true;
             if (A.vcount[v] != numchunks) {                                 // ppr:570-572
                 if (g == first) report(st, 3, first, 0, 0, CDS_ERR_CHUNK_COUNT);
@@ -386,6 +388,13 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
             if (numchunks && idx == numchunks - 1u && (unsigned long long)idx * kChunkMax + size != va_extsize) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_SIZE); ok = false; }   // ppr:589-591
             if (idx >= numchunks) { report(st, 3, first, 1, idx, CDS_ERR_CHUNK_SIZE); ok = false; }   // outside the pointer's extent
             if (g == first && vb != va_extsize) { report(st, 3, first, 2, 0, CDS_ERR_FINAL_SIZE); }  // ppr:595-596
+            // every chunk_seq 0..numchunks-1 exactly once?  (The reference sorts and joins whatever it finds; a repeated
+            // sequence number would land two chunks on the same bytes here, so it is refused.)
+            const uint32_t want_sum = (uint32_t)((((unsigned long long)numchunks * (numchunks ? numchunks - 1u : 0u)) >> 1) & 0x0FFFFFFFull);
+            if (A.vcount[v] == numchunks && seqsum != want_sum) {
+                if (g == first) report(st, 3, first, 1, 0x1FFFF, CDS_ERR_CHUNK_SIZE);
+                ok = false;
+            }
             const uint32_t pos = A.pos_of_row[r];
             if (ok && vb == va_extsize && fits && pos != kNone) {
                 const bool compressed = va_extsize != va_rawsize - 4u;

@@ -204,3 +204,21 @@ def test_full_size_pglz_round_trip(torch_cuda):
     src = torch.from_numpy(np.concatenate([x.reshape(-1) for x in ind])).cuda()
     assert torch.equal(part.ind.view(torch.float32), src)
     assert torch.equal(part.dep.view(torch.int16), torch.from_numpy(np.concatenate([d.reshape(-1) for d in dep])).cuda())
+
+
+def test_repeated_chunk_seq_is_refused_not_overlaid(torch_cuda):
+    """Two chunks of one value with the same chunk_seq (and the right count and byte total): the reference would join
+    them in sorted order; the gather would drop both onto the same bytes, so the decode reports "unexpected chunk size"."""
+    import struct
+    from cerebro_ds_kpgi_b200 import synth, _lib
+    ind, dep = synth.imagenet_rows(2, seed=5, shape=(60, 60, 3), classes=4, kind="normal")       # 43 200 B: 6 chunks
+    seg = synth.build_segment(ind, dep, ind_storage="ext_raw", dep_storage="inline_pglz")
+    status, _ = decode(torch_cuda, seg.heap, seg.toast)
+    assert status == 0
+    toast = seg.toast.copy()
+    iid = struct.unpack_from("<I", toast, 24 + 4 * 2)[0]           # third inserted tuple: chunk_seq 2 of the first value
+    off = iid & 0x7FFF
+    assert struct.unpack_from("<I", toast, off + 28)[0] == 2
+    struct.pack_into("<I", toast, off + 28, 1)                     # now chunk_seq 1 appears twice, 2 never
+    status, _ = decode(torch_cuda, seg.heap, toast)
+    assert status == _lib.CDS_ERR_CHUNK_SIZE
