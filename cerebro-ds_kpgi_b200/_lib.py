@@ -49,6 +49,7 @@ PROTOTYPES = {
     "cds_segment_create": (_int, [ctypes.POINTER(_vp), _int, _u64, _u64, _u64, _u64, _int]),
     "cds_segment_destroy": (_int, [_vp]),
     "cds_set_output_format": (_int, [_vp, _int]),
+    "cds_set_normalize_lut": (_int, [_vp, _vp, _u32]),
     "cds_heap_scan": (_int, [_vp, _vp, _u64, _vp]),
     "cds_set_rows": (_int, [_vp, _vp, _u64, _vp, _vp]),
     "cds_toast_scan": (_int, [_vp, _vp, _u64, _vp]),

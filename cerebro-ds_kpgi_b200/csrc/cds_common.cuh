@@ -44,6 +44,10 @@ struct DevState {
 // One TOAST chunk -> one copy.  dst == 0: chunk not referenced (or refused); nothing is copied.
 constexpr uint32_t kJobToBf16 = 0x80000000u;  // PglzJob.slen flag, same meaning
 constexpr uint32_t kOpToBf16 = 0x80000000u;   // CopyOp.len flag: payload is float32, destination is bfloat16
+constexpr uint32_t kOpU8Norm = 0x40000000u;   // CopyOp.len flag: payload is uint8 pixels, destination float32 = lut[channel][x];
+                                              // CopyOp.src_off bits 16.. hold the channel of the chunk's first byte
+constexpr uint32_t kJobU8Norm = 0x40000000u;  // PglzJob.slen flag, same meaning
+constexpr uint32_t kFlagBits = 0xC0000000u;
 struct __align__(16) CopyOp {
     unsigned long long dst;   // absolute device address
     uint32_t src_off;         // payload offset inside its page

@@ -44,7 +44,9 @@ struct cds_segment {
     uint64_t n_heap_pages = 0, n_toast_pages = 0;
     bool have_rows = false, have_chunks = false, have_plan = false, have_ops = false;
     int coop_blocks = 0;            // co-resident grid for k_plan_fused (0: cooperative launch unavailable)
-    int ind_bf16 = 0;               // cds_set_output_format: independent_var leaves as bfloat16
+    int ind_format = 0;             // cds_set_output_format: 0 stored bytes, 1 f32 -> bf16, 2 u8 -> f32 through the table
+    float *d_lut = nullptr;         // cds_set_normalize_lut: [channels][256]
+    uint32_t lut_channels = 0;
     // device buffers
     uint8_t *stage_heap = nullptr, *stage_toast = nullptr;
     uint32_t *heap_base = nullptr, *toast_base = nullptr, *rows = nullptr;
@@ -143,6 +145,7 @@ extern "C" int cds_segment_destroy(cds_segment *s)
                     s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch};
     for (void *b : bufs) if (b) cudaFree(b);
     if (s->h_state) cudaFreeHost(s->h_state);
+    if (s->d_lut) cudaFree(s->d_lut);
     if (s->ev) {
         for (uint32_t i = 0; i < 2 * s->ev_cap; i++) cudaEventDestroy(s->ev[i]);
         free(s->ev);
@@ -227,8 +230,19 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
 
 extern "C" int cds_set_output_format(cds_segment *s, int independent_var_format)
 {
-    if (!s || (independent_var_format != 0 && independent_var_format != 1)) return CDS_ERR_ARG;
-    s->ind_bf16 = independent_var_format;
+    if (!s || independent_var_format < 0 || independent_var_format > 2) return CDS_ERR_ARG;
+    if (independent_var_format == 2 && !s->d_lut) return CDS_ERR_ARG;       // set the table first
+    s->ind_format = independent_var_format;
+    return CDS_OK;
+}
+
+extern "C" int cds_set_normalize_lut(cds_segment *s, const float *h_lut, uint32_t channels)
+{
+    if (!s || !h_lut || channels == 0 || channels > kMaxLutChannels) return CDS_ERR_ARG;
+    CU(cudaSetDevice(s->device));
+    if (!s->d_lut) CU(cudaMalloc(reinterpret_cast<void **>(&s->d_lut), sizeof(float) * 256 * kMaxLutChannels));
+    CU(cudaMemcpy(s->d_lut, h_lut, sizeof(float) * 256 * channels, cudaMemcpyHostToDevice));
+    s->lut_channels = channels;
     return CDS_OK;
 }
 
@@ -334,7 +348,10 @@ static PlanArgs plan_args(cds_segment *s, uint32_t isb, uint32_t dsb, void *out_
     A.row_ind_off = s->row_ind_off; A.row_dep_off = s->row_dep_off;
     A.ops = s->ops; A.jobs = s->jobs; A.st = s->state;
     for (int i = 0; i < 5; i++) A.ws[i] = s->ws[2 + i];
-    A.isb = isb; A.dsb = dsb; A.ind_bf16 = (uint32_t)s->ind_bf16;
+    A.isb = isb; A.dsb = dsb;
+    A.ind_bf16 = s->ind_format == 1 ? 1u : 0u;
+    A.ind_u8norm = s->ind_format == 2 ? 1u : 0u;
+    A.lut_channels = s->lut_channels ? s->lut_channels : 1u;
     A.out_ind = static_cast<uint8_t *>(out_ind); A.out_dep = static_cast<uint8_t *>(out_dep); A.scratch = s->scratch;
     A.cap_ind = ind_cap; A.cap_dep = dep_cap; A.cap_scratch = s->cap_scratch;
     return A;
@@ -382,14 +399,15 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
         const bool timed = s->ev && s->ev_used < s->ev_cap;
         if (timed) CU(cudaEventRecord(s->ev[2 * s->ev_used], st));
         k_toast_gather<<<grid, kGatherThreads, kGatherSmemBytes, st>>>(s->d_toast, (uint32_t)s->n_toast_pages,
-                                                                       s->toast_base, s->ops, s->state);
+                                                                       s->toast_base, s->ops, s->state,
+                                                                       s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels);
         CU(cudaGetLastError());
         LAUNCHED(1);
         if (timed) { CU(cudaEventRecord(s->ev[2 * s->ev_used + 1], st)); s->ev_used++; }
     }
     // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
     k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
-        s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket);
+        s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket, s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels);
     CU(cudaGetLastError());
     LAUNCHED(1);
     return CDS_OK;
@@ -658,7 +676,7 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > 148u * 7u) grid = 148u * 7u;
         k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, (uint32_t)n, d_stat, nullptr,
-                                                                     reinterpret_cast<uint32_t *>(d_stat + n));
+                                                                     reinterpret_cast<uint32_t *>(d_stat + n), nullptr, 0u);
         e = cudaGetLastError();
         LAUNCHED(2);
     }
@@ -746,7 +764,7 @@ extern "C" int cds_pglz_decompress_batch_static(int device, const void *d_src, c
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > 148u * 7u) grid = 148u * 7u;
         k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(sc->jobs, nullptr, (uint32_t)n, d_status, &sc->state,
-                                                                     &sc->state.pglz_ticket);
+                                                                     &sc->state.pglz_ticket, nullptr, 0u);
         CU(cudaGetLastError());
         LAUNCHED(2);
     }

@@ -239,6 +239,8 @@ struct PlanArgs {
     ScanWs ws[5];                 // inline rank, chunk rank, ind offsets, dep offsets, staging offsets
     uint32_t isb, dsb;            // sample sizes for the shape check (0: none)
     uint32_t ind_bf16;            // independent_var leaves as bfloat16 (stored float32): output offsets are halved
+    uint32_t ind_u8norm;          // independent_var is uint8 pixels, leaves as float32 through the table: offsets x 4
+    uint32_t lut_channels;
     uint8_t *out_ind, *out_dep, *scratch;
     unsigned long long cap_ind, cap_dep, cap_scratch;
 };
@@ -359,7 +361,8 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
     const uint32_t *rows = A.rows;
     const uint32_t n_chunks = st->n_chunks, n_rows = st->n_rows;
     const uint32_t half = A.ind_bf16 ? 1u : 0u;                             // bf16 output: byte offsets / 2
-    const bool fits = (st->ind_bytes >> half) <= A.cap_ind && st->dep_bytes <= A.cap_dep && st->scratch_bytes <= A.cap_scratch;
+    const uint32_t quad = A.ind_u8norm ? 2u : 0u;                           // u8 -> f32 output: byte offsets x 4
+    const bool fits = ((st->ind_bytes >> half) << quad) <= A.cap_ind && st->dep_bytes <= A.cap_dep && st->scratch_bytes <= A.cap_scratch;
     if (!fits && blockIdx.x == 0 && threadIdx.x == 0) report(st, 4, 0, 2, 0, CDS_ERR_CAPACITY);
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
 
@@ -405,6 +408,11 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
                     op.dst = (unsigned long long)(A.scratch + A.vscr[v]) + (unsigned long long)idx * kChunkMax;
                 } else if (a) {
                     op.dst = (unsigned long long)(A.out_dep + A.pos_dep[pos]) + (unsigned long long)idx * kChunkMax;
+                } else if (quad) {
+                    const unsigned long long voff = (unsigned long long)idx * kChunkMax;     // byte (= pixel component) inside the value
+                    op.dst = (unsigned long long)(A.out_ind + ((A.pos_ind[pos] + voff) << 2));
+                    op.src_off |= (uint32_t)(voff % A.lut_channels) << 16;
+                    op.len = size | kOpU8Norm;
                 } else if (!half) {
                     op.dst = (unsigned long long)(A.out_ind + A.pos_ind[pos]) + (unsigned long long)idx * kChunkMax;
                 } else if (((size | va_extsize) & 3u) == 0u && (A.pos_ind[pos] & 3ull) == 0ull) {
@@ -460,6 +468,7 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
                         job.slen = va_extsize - 4u;
                         job.rawsize = (uint32_t)len;
                         if (a) job.dst = (unsigned long long)(A.out_dep + my_dep_off);
+                        else if (quad) { job.dst = (unsigned long long)(A.out_ind + (my_ind_off << 2)); job.slen |= kJobU8Norm; }
                         else if (!half) job.dst = (unsigned long long)(A.out_ind + my_ind_off);
                         else if ((len & 3ull) == 0ull && (my_ind_off & 3ull) == 0ull) {
                             job.dst = (unsigned long long)(A.out_ind + (my_ind_off >> 1));

@@ -83,6 +83,31 @@ __device__ __forceinline__ void pglz_flush_bf16(const uint8_t *ring, uint8_t *ds
         dh[(t0 >> 2) + lane] = __float2bfloat16_rn(*reinterpret_cast<const float *>(ring + ((t0 + 4u * lane + shift) & (kRing - 1))));
 }
 
+// uint8 -> float32 variant: the ring holds uint8 pixel components, `dst` holds float32 = lut[channel][x] with
+// channel = position mod channels; `shift` = (dst >> 2) & 3 so that a 4-byte ring word maps onto an aligned 16-byte store.
+__device__ __forceinline__ void pglz_flush_u8norm(const uint8_t *ring, float *dst, uint32_t shift, uint32_t from, uint32_t to,
+                                                  uint32_t lane, const float *__restrict__ lut, uint32_t ch)
+{
+    uint32_t head = (4u - ((from + shift) & 3u)) & 3u;
+    if (head > to - from) head = to - from;
+    if (lane < head) dst[from + lane] = __ldg(lut + ((from + lane) % ch) * 256u + ring[(from + lane + shift) & (kRing - 1)]);
+    const uint32_t b0 = from + head;
+    const uint32_t nq = (to - b0) >> 2;
+    for (uint32_t j = lane; j < nq; j += 32) {
+        const uint32_t pos = b0 + (j << 2);
+        const uint32_t w = *reinterpret_cast<const uint32_t *>(ring + ((pos + shift) & (kRing - 1)));
+        uint32_t c = pos % ch;
+        float4 o;
+        o.x = __ldg(lut + c * 256u + (w & 0xFFu));          c = (c + 1u == ch) ? 0u : c + 1u;
+        o.y = __ldg(lut + c * 256u + ((w >> 8) & 0xFFu));   c = (c + 1u == ch) ? 0u : c + 1u;
+        o.z = __ldg(lut + c * 256u + ((w >> 16) & 0xFFu));  c = (c + 1u == ch) ? 0u : c + 1u;
+        o.w = __ldg(lut + c * 256u + (w >> 24));
+        __stcs(reinterpret_cast<float4 *>(dst + pos), o);
+    }
+    const uint32_t t0 = b0 + (nq << 2);
+    if (lane < to - t0) dst[t0 + lane] = __ldg(lut + ((t0 + lane) % ch) * 256u + ring[(t0 + lane + shift) & (kRing - 1)]);
+}
+
 // Register window over the source stream.  The stream is addressed in the word-aligned frame
 // y = offset + (src & 3); window k covers y in [128k, 128k + 128); lane l holds word 32k + l.
 struct SrcWindow {
@@ -245,16 +270,19 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
 }
 
 // Decode one datum with the calling warp.  Returns true when the stream is well-formed.
-template <bool kBf16>
+// kOut: 0 = the decoded bytes, 1 = float32 -> bfloat16, 2 = uint8 -> float32 through `lut`.
+template <int kOut>
 __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen, uint8_t *dst, uint32_t rawsize,
-                                 uint8_t *ring)
+                                 uint8_t *ring, const float *__restrict__ lut, uint32_t lut_channels)
 {
     const uint32_t lane = threadIdx.x & 31;
     // ring index = output position + shift, chosen so that ring vectors line up with aligned global stores
-    const uint32_t shift = kBf16 ? (uint32_t)((2u * reinterpret_cast<uintptr_t>(dst)) & 15u)
-                                 : (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
+    const uint32_t shift = kOut == 1 ? (uint32_t)((2u * reinterpret_cast<uintptr_t>(dst)) & 15u)
+                         : kOut == 2 ? (uint32_t)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3u)
+                                     : (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
     auto flush = [&](uint32_t from, uint32_t to) {
-        if (kBf16) pglz_flush_bf16(ring, dst, shift, from, to, lane);
+        if (kOut == 1) pglz_flush_bf16(ring, dst, shift, from, to, lane);
+        else if (kOut == 2) pglz_flush_u8norm(ring, reinterpret_cast<float *>(dst), shift, from, to, lane, lut, lut_channels);
         else pglz_flush(ring, dst, shift, from, to, lane);
     };
     uint32_t sp = 0, dp = 0, flushed = 0;
@@ -425,7 +453,7 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
 // down): front jobs (large values) are handed out first, the small ones fill the tail.
 __global__ void __launch_bounds__(32 * kPglzWarps)
 k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint32_t n_jobs_host,
-              int32_t *status, DevState *st, uint32_t *ticket)
+              int32_t *status, DevState *st, uint32_t *ticket, const float *__restrict__ lut, uint32_t lut_channels)
 {
     extern __shared__ __align__(16) uint8_t smem_ring[];
     uint8_t *ring = smem_ring + (size_t)(threadIdx.x >> 5) * kRing;
@@ -443,11 +471,12 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
         const uint32_t j = t < front ? t : last_slot - (t - front);
         const PglzJob job = jobs[j];
         if (job.slen == kNone) continue;
-        const bool ok = (job.slen & kJobToBf16)
-            ? pglz_warp_decode<true>(reinterpret_cast<const uint8_t *>(job.src), job.slen & ~kJobToBf16,
-                                     reinterpret_cast<uint8_t *>(job.dst), job.rawsize, ring)
-            : pglz_warp_decode<false>(reinterpret_cast<const uint8_t *>(job.src), job.slen,
-                                      reinterpret_cast<uint8_t *>(job.dst), job.rawsize, ring);
+        const uint8_t *jsrc = reinterpret_cast<const uint8_t *>(job.src);
+        uint8_t *jdst = reinterpret_cast<uint8_t *>(job.dst);
+        const uint32_t jlen = job.slen & ~kFlagBits;
+        const bool ok = (job.slen & kJobToBf16) ? pglz_warp_decode<1>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels)
+                      : (job.slen & kJobU8Norm) ? pglz_warp_decode<2>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels)
+                                                : pglz_warp_decode<0>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels);
         if (lane == 0) {
             if (status) status[j] = ok ? CDS_OK : CDS_ERR_PGLZ_CORRUPT;
             if (!ok && st && job.err_key) report_key(st, job.err_key);

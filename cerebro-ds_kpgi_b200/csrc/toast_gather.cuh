@@ -25,10 +25,12 @@ constexpr int kGatherStages = 6;
 constexpr int kGatherConsumerWarps = 16;
 constexpr int kGatherThreads = 32 * (1 + kGatherConsumerWarps);
 constexpr int kGatherMaxStageOps = 48;
+constexpr uint32_t kMaxLutChannels = 4;
 constexpr size_t kGatherSmemBytes =
     (size_t)kGatherStages * kPage + 16 /* realign over-read pad */ +
     (size_t)kGatherStages * kGatherMaxStageOps * sizeof(CopyOp) +
-    (size_t)kGatherStages * 2 * sizeof(uint32_t) + (size_t)kGatherStages * 2 * sizeof(unsigned long long) + 64;
+    (size_t)kGatherStages * 2 * sizeof(uint32_t) + (size_t)kGatherStages * 2 * sizeof(unsigned long long) + 64 +
+    kMaxLutChannels * 256 * sizeof(float);
 
 __device__ __forceinline__ void st_stream_v4(void *gdst, uint4 v)
 {
@@ -113,9 +115,34 @@ __device__ __forceinline__ void copy_payload_bf16(const uint8_t *src, uint8_t *d
     if (tid < n - done) dh[done + tid] = __float2bfloat16_rn(sf[done + tid]);
 }
 
+// uint8 pixels -> normalised float32 through a [channels][256] table in shared memory (the reference's
+// (x/255 - mean)/std, evaluated once per table entry in double on the host: SURVEY.md §8c(3)).  `phase` is the
+// channel of the first payload byte.  len source bytes become 4*len bytes at dst (16-byte aligned here).
+__device__ __forceinline__ void copy_payload_u8norm(const uint8_t *src, float *dst, uint32_t len, uint32_t phase, uint32_t ch,
+                                                    const float *lut, uint32_t tid, uint32_t nth)
+{
+    const uint32_t quads = len >> 2;
+    const bool aligned = ((smem_u32(src) & 3u) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0);
+    for (uint32_t j = tid; j < quads; j += nth) {
+        uint32_t w;
+        if (aligned) w = *reinterpret_cast<const uint32_t *>(src + 4u * j);
+        else w = (uint32_t)src[4u * j] | ((uint32_t)src[4u * j + 1] << 8) | ((uint32_t)src[4u * j + 2] << 16) | ((uint32_t)src[4u * j + 3] << 24);
+        uint32_t c = (phase + 4u * j) % ch;
+        float4 o;
+        o.x = lut[c * 256u + (w & 0xFFu)];          c = (c + 1u == ch) ? 0u : c + 1u;
+        o.y = lut[c * 256u + ((w >> 8) & 0xFFu)];   c = (c + 1u == ch) ? 0u : c + 1u;
+        o.z = lut[c * 256u + ((w >> 16) & 0xFFu)];  c = (c + 1u == ch) ? 0u : c + 1u;
+        o.w = lut[c * 256u + (w >> 24)];
+        if (aligned) st_stream_v4(dst + 4u * j, make_uint4(__float_as_uint(o.x), __float_as_uint(o.y), __float_as_uint(o.z), __float_as_uint(o.w)));
+        else { dst[4u * j] = o.x; dst[4u * j + 1] = o.y; dst[4u * j + 2] = o.z; dst[4u * j + 3] = o.w; }
+    }
+    const uint32_t done = quads << 2;
+    if (tid < len - done) dst[done + tid] = lut[((phase + done + tid) % ch) * 256u + src[done + tid]];
+}
+
 __global__ void __launch_bounds__(kGatherThreads, 1)
 k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32_t *__restrict__ base,
-               const CopyOp *__restrict__ ops, const DevState *__restrict__ st)
+               const CopyOp *__restrict__ ops, const DevState *__restrict__ st, const float *__restrict__ lut, uint32_t lut_channels)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *stage_buf = smem;
@@ -124,6 +151,8 @@ k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32
     uint32_t *stage_n = stage_g0 + kGatherStages;
     unsigned long long *full = reinterpret_cast<unsigned long long *>(stage_n + kGatherStages);
     unsigned long long *empty = full + kGatherStages;
+    float *lut_s = reinterpret_cast<float *>(empty + kGatherStages);        // [channels][256], only in the u8 -> f32 mode
+    if (lut) for (uint32_t i = threadIdx.x; i < 256u * lut_channels; i += blockDim.x) lut_s[i] = lut[i];
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
@@ -165,7 +194,9 @@ k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32
             for (uint32_t j = 0; j < n; j++) {
                 const CopyOp op = j < (uint32_t)kGatherMaxStageOps ? stage_ops[s * kGatherMaxStageOps + j] : ops[g0 + j];
                 if (op.dst == 0 || op.len == 0) continue;
-                if (op.len & kOpToBf16) copy_payload_bf16(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len & ~kOpToBf16, ctid, cnth);
+                if (op.len & kOpToBf16) copy_payload_bf16(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len & ~kFlagBits, ctid, cnth);
+                else if (op.len & kOpU8Norm) copy_payload_u8norm(pg + (op.src_off & 0xFFFFu), reinterpret_cast<float *>(op.dst), op.len & ~kFlagBits,
+                                                                op.src_off >> 16, lut_channels, lut_s, ctid, cnth);
                 else copy_payload(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len, ctid, cnth);
             }
             __syncwarp();

@@ -42,7 +42,8 @@ def _load_catalog(file_path):
     return df_shape, sys_cat['relname'], table_page_path, toast_page_path
 
 
-def _decode_files(table_page_path, toast_page_path, ind_sample_bytes=0, dep_sample_bytes=0, ind_bf16=False):
+def _decode_files(table_page_path, toast_page_path, ind_sample_bytes=0, dep_sample_bytes=0, ind_bf16=False,
+                  u8_normalize=None):
     """Both relations -> pinned host memory -> HBM -> one fused decode.  Returns (part, partial flags)."""
     import torch
     _lib.require_device()
@@ -54,7 +55,7 @@ def _decode_files(table_page_path, toast_page_path, ind_sample_bytes=0, dep_samp
     logs("END READING TOAST: {}".format(toast_page_path))
     logs("START DETOASTING")
     status, part = _segment.decode_pages(d_heap, d_toast, ind_sample_bytes=ind_sample_bytes,
-                                         dep_sample_bytes=dep_sample_bytes, ind_bf16=ind_bf16)
+                                         dep_sample_bytes=dep_sample_bytes, ind_bf16=ind_bf16, u8_normalize=u8_normalize)
     torch.cuda.synchronize()
     # reference order of failures: heap scan, short heap page, TOAST walk, short TOAST page, detoast
     stage = part.summary.err_stage if status else 99
@@ -113,10 +114,13 @@ class DevicePartition:
         return out
 
 
-def input_fn_device(file_path, overwrite_table_page_path=None, overwrite_toast_page_path=None, dtype=None):
+def input_fn_device(file_path, overwrite_table_page_path=None, overwrite_toast_page_path=None, dtype=None,
+                    u8_normalize=None):
     """Same call as input_fn, result left on the GPU.  Sample shapes come from the catalog's shape
     frame (every buffer of a table shares its trailing dimensions).  dtype=torch.bfloat16 makes the decode
-    kernels emit bfloat16 images directly (round to nearest even); default: the stored float32 bits."""
+    kernels emit bfloat16 images directly (round to nearest even); default: the stored float32 bits.
+    u8_normalize = float32 [channels, 256] table: the table stores uint8 pixels and the kernels emit
+    float32 table[channel][x] (e.g. synth.norm_lut(): the reference's (x/255 - mean)/std, exact)."""
     import torch
     df_shape, table_name, table_page_path, toast_page_path = _load_catalog(file_path)
     if overwrite_table_page_path:
@@ -128,9 +132,9 @@ def input_fn_device(file_path, overwrite_table_page_path=None, overwrite_toast_p
         pg_page_reader.raise_for_status(_lib.CDS_ERR_CATALOG_MISS)
     ishape = tuple(int(x) for x in sub['independent_var_shape'].iloc[0][1:])
     dshape = tuple(int(x) for x in sub['dependent_var_shape'].iloc[0][1:])
-    isb, dsb = 4 * int(np.prod(ishape)), 2 * int(np.prod(dshape))
-    bf16 = dtype is not None and dtype == torch.bfloat16
-    part = _decode_files(table_page_path, toast_page_path, isb, dsb, ind_bf16=bf16)
+    isb, dsb = (1 if u8_normalize is not None else 4) * int(np.prod(ishape)), 2 * int(np.prod(dshape))
+    bf16 = dtype is not None and dtype == torch.bfloat16 and u8_normalize is None
+    part = _decode_files(table_page_path, toast_page_path, isb, dsb, ind_bf16=bf16, u8_normalize=u8_normalize)
     images = part.ind.view(torch.bfloat16 if bf16 else torch.float32).view((-1,) + ishape)
     onehot = part.dep.view(torch.int16).view((-1,) + dshape)
     labels = _segment.onehot_argmax(onehot.reshape(onehot.shape[0], -1))

@@ -85,9 +85,16 @@ class DeviceSegment:
         except Exception:  # noqa
             pass
 
-    def set_output_format(self, ind_bf16=False):
-        """independent_var as stored (float32 bytes, default) or converted to bfloat16 on the fly."""
-        _lib.check(self.L.cds_set_output_format(self._h, 1 if ind_bf16 else 0))
+    def set_output_format(self, ind_bf16=False, u8_normalize=None):
+        """independent_var as stored (default), float32 -> bfloat16 on the fly, or — with `u8_normalize` =
+        a float32 [channels, 256] table — uint8 pixels -> normalised float32 through that table."""
+        if u8_normalize is not None:
+            lut = np.ascontiguousarray(u8_normalize, dtype=np.float32)
+            assert lut.ndim == 2 and lut.shape[1] == 256
+            _lib.check(self.L.cds_set_normalize_lut(self._h, _ptr(lut), lut.shape[0]))
+            _lib.check(self.L.cds_set_output_format(self._h, 2))
+        else:
+            _lib.check(self.L.cds_set_output_format(self._h, 1 if ind_bf16 else 0))
 
     # ---- step API -------------------------------------------------------------------------
     def heap_scan(self, heap, stream=None):
@@ -275,7 +282,7 @@ class DecodedPartition:
 
 
 def decode_pages(heap, toast, device=None, ind_sample_bytes=0, dep_sample_bytes=0, rows=None, inline_blob=None,
-                 segment=None, ind_bf16=False):
+                 segment=None, ind_bf16=False, u8_normalize=None):
     """Two-phase decode of page buffers already on the GPU (uint8 CUDA tensors): scan + plan, one
     host sync to size the outputs, then materialize.  With `rows` (exported-row layout) the heap scan
     is replaced by an upload of those rows (`toast_page_read` path).  Returns (status, DecodedPartition)."""
@@ -285,7 +292,7 @@ def decode_pages(heap, toast, device=None, ind_sample_bytes=0, dep_sample_bytes=
         seg = segment or DeviceSegment(max(1, (heap.numel() // BLCKSZ) if heap is not None else (len(rows) // 400 + 1)),
                                        toast.numel() // BLCKSZ, device=dev.index)
         try:
-            seg.set_output_format(ind_bf16)
+            seg.set_output_format(ind_bf16, u8_normalize)
             if rows is None:
                 seg.heap_scan(heap)
             else:
@@ -295,7 +302,7 @@ def decode_pages(heap, toast, device=None, ind_sample_bytes=0, dep_sample_bytes=
             s1 = seg.finish()
             if s1.status != 0:
                 return int(s1.status), DecodedPartition(s1, None, None, None, None)
-            ind_out_bytes = int(s1.ind_bytes) // 2 if ind_bf16 else int(s1.ind_bytes)
+            ind_out_bytes = int(s1.ind_bytes) * 4 if u8_normalize is not None else (int(s1.ind_bytes) // 2 if ind_bf16 else int(s1.ind_bytes))
             ind = torch.empty(ind_out_bytes + 16, dtype=torch.uint8, device=dev)
             dep = torch.empty(int(s1.dep_bytes) + 16, dtype=torch.uint8, device=dev)
             seg.materialize(ind, dep)

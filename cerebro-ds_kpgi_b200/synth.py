@@ -210,7 +210,7 @@ def build_segment(ind_arrays, dep_arrays, ind_storage="ext_raw", dep_storage="in
 
     for r in range(n):
         ind, dep = ind_arrays[r], dep_arrays[r]
-        assert ind.dtype == np.float32 and dep.dtype == np.int16
+        assert ind.dtype in (np.float32, np.uint8) and dep.dtype == np.int16
         row = {"buffer_id": int(buffer_ids[r]), "dist_key": int(dist_key),
                "ind_storage": ind_st[r], "dep_storage": dep_st[r]}
         if not ind_st[r].startswith("ext_"):

@@ -87,8 +87,15 @@ int cds_segment_destroy(cds_segment *seg);
  * 0 (default) = the stored bytes (float32 for these tables; a bit copy, as ppr:165-182),
  * 1 = bfloat16, converted from the stored float32 with round-to-nearest-even inside the gather and the
  *     pglz decoder (no float32 copy is written); capacities and cds_summary.ind_bytes stay in float32
- *     bytes, the buffer needs ind_bytes / 2.  Not in the reference: an optional training-buffer dtype. */
+ *     bytes, the buffer needs ind_bytes / 2.  Not in the reference: an optional training-buffer dtype.
+ * 2 = the stored bytes are uint8 pixel components (HWC, `channels` interleaved) and leave as float32
+ *     lut[channel][x] — the normalisation the reference applied before loading,
+ *     ((x / 255.0) - mean[c]) / std[c] (preprocessing/imagenet/generate_h5_file.py:77-81), made exact by
+ *     evaluating it once per table entry in double on the host (cds_set_normalize_lut first).  The buffer
+ *     needs 4 * ind_bytes; values must start on a channel boundary (whole samples do). */
 int cds_set_output_format(cds_segment *seg, int independent_var_format);
+/* The [channels][256] float32 table for format 2 (channels <= 4), copied to the device. */
+int cds_set_normalize_lut(cds_segment *seg, const float *h_lut, uint32_t channels);
 
 /* ---- the path, step by step (each enqueues on `stream` and returns; no host sync) ---------- */
 

@@ -231,3 +231,37 @@ def test_fused_bf16_output_matches_rne_of_oracle(torch_cuda, coracle):
     assert status == 0
     ref = torch.from_numpy(want["out_ind"].view(np.float32).copy()).to(torch.bfloat16)
     assert torch.equal(part.ind.view(torch.bfloat16).cpu().view(torch.int16), ref.view(torch.int16))
+
+
+def test_fused_uint8_normalise_is_the_reference_formula_bit_for_bit(torch_cuda, coracle):
+    """north_star's "fused cast/normalise": uint8 pixel tables leave the decode as float32
+    ((x / 255.0) - mean) / std  (preprocessing/imagenet/generate_h5_file.py:77-81; evaluated in float64 and
+    stored to float32, as numpy does there) — 0 ULP, for uncompressed, pglz and literal-only values."""
+    from cerebro_ds_kpgi_b200 import synth
+    torch = torch_cuda
+    rng = np.random.default_rng(21)
+    mean, std = np.array([0.485, 0.456, 0.406]), np.array([0.229, 0.224, 0.225])
+    lut = synth.norm_lut()
+    want_lut = (((np.arange(256)[None, :] / 255.0) - mean[:, None]) / std[:, None]).astype(np.float32)
+    assert lut.tobytes() == want_lut.tobytes()
+    ind, dep = [], []
+    for i in range(18):
+        b = 1 + i % 2
+        px = rng.integers(0, 256, size=(b, 112, 112, 3), dtype=np.uint8)
+        if i % 3 == 1:
+            px[:, 20:90] = px[:, 20:21]                        # repeated rows: real matches for pglz
+        ind.append(px)
+        dep.append(np.eye(9, dtype=np.int16)[rng.integers(0, 9, b)])
+    st = [["ext_raw", "ext_pglz", "ext_literal"][i % 3] for i in range(18)]
+    seg = synth.build_segment(ind, dep, ind_storage=st, dep_storage="inline_pglz")
+    ref = coracle.decode(seg.heap, seg.toast)                   # the stored uint8 bytes, in result order
+    px_all = ref["out_ind"].reshape(-1, 3)
+    img = px_all.astype(np.float64) / 255.0                     # the reference's three statements
+    img = img - mean
+    img = img / std
+    want = img.astype(np.float32).reshape(-1)
+    status, part = gpu_decode(torch, seg.heap, seg.toast, u8_normalize=lut, ind_sample_bytes=112 * 112 * 3, dep_sample_bytes=18)
+    assert status == 0
+    got = part.ind.view(torch.float32).cpu().numpy()
+    assert got.shape == want.shape and got.tobytes() == want.tobytes()
+    assert part.dep.cpu().numpy().tobytes() == ref["out_dep"].tobytes()
