@@ -1,0 +1,164 @@
+"""Randomised differential tests: CUDA path vs. the oracle over many generated segment layouts and pglz streams.
+Seeds are fixed, so a failure reproduces."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("GPU tests need a CUDA device")
+    return torch
+
+
+def structured_bytes(rng, n):
+    """Bytes with the redundancy shapes an LZ decoder has to get right: runs, repeats at every distance up to the
+    4095 window, near-random stretches, repeated float patterns."""
+    out = np.empty(n, dtype=np.uint8)
+    i = 0
+    while i < n:
+        kind = int(rng.integers(0, 6))
+        m = int(min(n - i, rng.integers(1, 700)))
+        if kind == 0:
+            out[i:i + m] = rng.integers(0, 256, m, dtype=np.uint8)
+        elif kind == 1:
+            out[i:i + m] = rng.integers(0, 256)
+        elif kind == 2 and i > 0:
+            d = int(rng.integers(1, min(i, 4095) + 1))
+            for k in range(m):                       # overlapping copy semantics, byte by byte
+                out[i + k] = out[i + k - d]
+        elif kind == 3 and i > 0:
+            d = min(i, 4095)
+            out[i:i + min(m, d)] = out[i - d:i - d + min(m, d)]
+            m = min(m, d)
+        elif kind == 4:
+            pat = rng.integers(0, 256, int(rng.integers(1, 13)), dtype=np.uint8)
+            out[i:i + m] = np.resize(pat, m)
+        else:
+            out[i:i + m] = rng.integers(0, 4, m, dtype=np.uint8)
+        i += m
+    return out
+
+
+def test_pglz_fuzz_structured_streams(torch_cuda, coracle):
+    from cerebro_ds_kpgi_b200 import segment, synth
+    rng = np.random.default_rng(2024)
+    datums, raws = [], []
+    for t in range(160):
+        n = int(rng.choice([0, 1, 7, 8, 9, 63, 64, 65, 2047, 2048, 2049, 4095, 4096, 4097, 8191, 8192, 8193,
+                            int(rng.integers(1, 70000))]))
+        raw = structured_bytes(rng, n)
+        mode = "literal" if t % 11 == 0 else "lz"
+        datums.append(synth.pglz_varlena(raw, mode, effort=int(rng.integers(1, 40))))
+        raws.append(raw.tobytes())
+    out, codes = segment.pglz_decompress_batch(datums)
+    assert codes == [0] * len(datums)
+    for i, (got, want) in enumerate(zip(out, raws)):
+        assert got == want, "datum %d (%d bytes)" % (i, len(want))
+    # and the oracle agrees with the encoder too (so a mismatch above is the decoder's)
+    for d, want in zip(datums[:40], raws[:40]):
+        assert bytes(coracle.pglz_decompress(d)) == want
+
+
+def test_segment_layout_fuzz(torch_cuda, coracle):
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    rng = np.random.default_rng(777)
+    sizes = [1, 2, 3, 2034, 2035, 2036, 4069, 4070, 4071, 6105, 8140 // 4 * 3]      # float counts around the 8140-byte chunk edge
+    ds = segment.DeviceSegment(64, 2048)
+    for trial in range(40):
+        n_rows = int(rng.integers(1, 50))
+        ind, dep, st_i, st_d = [], [], [], []
+        for r in range(n_rows):
+            b = int(rng.integers(1, 4))
+            k = int(rng.choice(sizes)) if rng.random() < 0.6 else int(rng.integers(1, 9000))
+            kind = rng.integers(0, 3)
+            if kind == 0:
+                x = rng.standard_normal((b, k)).astype(np.float32)
+            elif kind == 1:
+                x = np.zeros((b, k), dtype=np.float32)
+                x[:, ::7] = 1.0
+            else:
+                x = np.resize(rng.standard_normal(int(rng.integers(1, 40))).astype(np.float32), (b, k))
+            ind.append(x)
+            dep.append(rng.integers(-2, 3, size=(b, int(rng.integers(1, 40)))).astype(np.int16))
+            st_i.append(str(rng.choice(["ext_raw", "ext_pglz", "ext_literal"])))
+            st_d.append(str(rng.choice(["ext_raw", "ext_pglz", "inline_pglz", "inline_literal", "ext_literal"])))
+        n_ext = n_rows + sum(1 for s in st_d if s.startswith("ext"))
+        perm = list(rng.permutation(n_ext)) if rng.random() < 0.5 else None
+        seg = synth.build_segment(ind, dep, ind_storage=st_i, dep_storage=st_d, toast_perm=perm,
+                                  buffer_ids=list(rng.permutation(100000)[:n_rows]), first_valueid=int(rng.integers(16384, 2 ** 31)),
+                                  effort=int(rng.integers(1, 20)))
+        want = coracle.decode(seg.heap, seg.toast)
+        out_i = torch.full((want["out_ind"].size + 32,), 0x5A, dtype=torch.uint8, device="cuda")
+        out_d = torch.full((want["out_dep"].size + 32,), 0x5A, dtype=torch.uint8, device="cuda")
+        s = ds.decode_device(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(seg.toast).cuda(), out_i, out_d)
+        assert s.status == 0, (trial, s.status)
+        assert s.ind_bytes == want["out_ind"].size and s.dep_bytes == want["out_dep"].size, trial
+        lay = ds.layout(int(s.n_rows), int(s.n_positions))
+        assert np.array_equal(lay["order"], want["order"]), trial
+        gi, gd = out_i.cpu().numpy(), out_d.cpu().numpy()
+        assert gi[:want["out_ind"].size].tobytes() == want["out_ind"].tobytes(), trial
+        assert gd[:want["out_dep"].size].tobytes() == want["out_dep"].tobytes(), trial
+        assert (gi[want["out_ind"].size:] == 0x5A).all() and (gd[want["out_dep"].size:] == 0x5A).all(), trial   # nothing past the end
+    ds.close()
+
+
+def test_corruption_fuzz_never_disagrees_silently(torch_cuda, coracle):
+    """Flip bytes in headers, line pointers, TOAST pointers, chunk headers and compressed streams.  The oracle either
+    decodes (then the CUDA path must return the same bytes) or refuses (then the CUDA path must refuse too: a non-zero
+    status, never a crash and never silent data).  Which error wins on multi-fault inputs is not compared."""
+    import da_oracle
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    rng = np.random.default_rng(31337)
+    ind, dep = synth.imagenet_rows(10, seed=6, shape=(36, 36, 3), classes=12, images_per_row=2)
+    base = synth.build_segment(ind, dep, ind_storage=["ext_pglz", "ext_raw", "ext_literal", "ext_pglz", "ext_raw"] * 2,
+                               dep_storage=["inline_pglz", "ext_raw", "ext_pglz", "inline_literal", "ext_literal"] * 2)
+    ds = segment.DeviceSegment(base.heap.size // 32768, base.toast.size // 32768)
+    cap_i, cap_d = 4 * sum(x.nbytes for x in ind), 4 * sum(x.nbytes for x in dep)
+    agree_ok = agree_err = 0
+    for trial in range(120):
+        heap, toast = base.heap.copy(), base.toast.copy()
+        target = heap if rng.random() < 0.4 else toast
+        for _ in range(int(rng.integers(1, 4))):
+            page = int(rng.integers(0, target.size // 32768)) * 32768
+            where = rng.random()
+            if where < 0.3:
+                pos = page + int(rng.integers(0, 64))                        # page header / first line pointers
+            elif where < 0.7:
+                lower = int(target[page + 12]) | (int(target[page + 13]) << 8)
+                n_items = max(1, (lower - 24) // 4)
+                iid = int.from_bytes(target[page + 24 + 4 * int(rng.integers(0, n_items)):][:4].tobytes(), "little")
+                pos = page + (iid & 0x7FFF) + int(rng.integers(0, 80))         # tuple header, pointers, chunk header, stream start
+            else:
+                pos = page + int(rng.integers(0, 32768))
+            pos = min(pos, target.size - 1)
+            target[pos] ^= int(rng.integers(1, 256))
+        try:
+            want = coracle.decode(heap, toast, ind_cap=cap_i, dep_cap=cap_d)
+            err = 0
+        except da_oracle.OracleError as e:
+            want, err = None, e.code
+        out_i = torch.zeros(cap_i, dtype=torch.uint8, device="cuda")
+        out_d = torch.zeros(cap_d, dtype=torch.uint8, device="cuda")
+        try:
+            s = ds.decode_device(torch.from_numpy(heap).cuda(), torch.from_numpy(toast).cuda(), out_i, out_d)
+            status = int(s.status)
+        except Exception as e:                                                # capacity refusals surface as CdsError
+            status = getattr(e, "code", -1)
+        if err == 0 and status == 9:
+            continue       # documented deviation: repeated / out-of-range chunk_seq is refused, the reference joins it
+        if err == 0:
+            assert status == 0, (trial, status)
+            assert out_i.cpu().numpy()[:want["out_ind"].size].tobytes() == want["out_ind"].tobytes(), trial
+            assert out_d.cpu().numpy()[:want["out_dep"].size].tobytes() == want["out_dep"].tobytes(), trial
+            agree_ok += 1
+        else:
+            assert status != 0, (trial, "oracle refused with %d, the CUDA path decoded" % err)
+            agree_err += 1
+    ds.close()
+    assert agree_ok > 10 and agree_err > 10, (agree_ok, agree_err)
