@@ -24,7 +24,7 @@ class Summary(ctypes.Structure):
     _fields_ = [("n_rows", ctypes.c_uint64), ("n_positions", ctypes.c_uint64), ("ind_bytes", ctypes.c_uint64),
                 ("dep_bytes", ctypes.c_uint64), ("n_chunks", ctypes.c_uint64), ("n_inline", ctypes.c_uint64),
                 ("scratch_bytes", ctypes.c_uint64), ("err_where", ctypes.c_uint64), ("status", ctypes.c_uint32),
-                ("err_stage", ctypes.c_uint32)]
+                ("err_stage", ctypes.c_uint32), ("n_wide_values", ctypes.c_uint64)]
 
 
 class CdsError(RuntimeError):
@@ -68,6 +68,9 @@ PROTOTYPES = {
     "cds_export_chunks": (_int, [_vp, _vp, _vp, _vp, _vp, _u64, _pu64, _vp]),
     "cds_pglz_decompress_batch": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp]),
     "cds_pglz_decompress_batch_static": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
+    "cds_set_wide_pglz_threshold": (_int, [_u32]),
+    "cds_set_wide_pglz": (_int, [_vp, _int]),
+    "cds_wide_decoded_count": (ctypes.c_ulonglong, []),
     "pglz_decompress": (None, [ctypes.c_char_p, ctypes.c_char_p]),
     "cds_onehot_argmax_i16": (_int, [_vp, _u64, _u32, _vp, _vp]),
     "cds_nhwc_to_nchw_f32": (_int, [_vp, _u64, _u32, _u32, _vp, _vp]),

@@ -39,6 +39,8 @@ struct DevState {
     uint32_t pglz_ticket;         // work counter of k_pglz_decode
     uint32_t n_jobs_front;        // compacted pglz jobs: large values from slot 0 up ...
     uint32_t n_jobs_back;         // ... small values from the last slot down
+    uint32_t n_wide;              // compressed values at or above the wide-decode threshold (pglz_wide.cuh)
+    uint32_t pad_[3];
 };
 
 // One TOAST chunk -> one copy.  dst == 0: chunk not referenced (or refused); nothing is copied.

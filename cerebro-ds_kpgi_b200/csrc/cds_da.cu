@@ -14,6 +14,7 @@
 #include "cds_common.cuh"
 #include "page_scan.cuh"
 #include "pglz_decode.cuh"
+#include "pglz_wide.cuh"
 #include "text_etl.cuh"
 #include "toast_gather.cuh"
 
@@ -22,6 +23,8 @@ using namespace cds;
 static thread_local char g_last_error[512] = "";
 static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py reports it)
 #define LAUNCHED(n) (g_launches += (n))
+static uint32_t g_wide_threshold = 1u << 20;   // cds_set_wide_pglz_threshold
+static unsigned long long g_wide_decoded = 0;  // values decoded by the wide decoder so far (cds_wide_decoded_count)
 
 static int cuda_fail(cudaError_t e, const char *what)
 {
@@ -46,6 +49,11 @@ struct cds_segment {
     int coop_blocks = 0;            // co-resident grid for k_plan_fused (0: cooperative launch unavailable)
     int ind_format = 0;             // cds_set_output_format: 0 stored bytes, 1 f32 -> bf16, 2 u8 -> f32 through the table
     float *d_lut = nullptr;         // cds_set_normalize_lut: [channels][256]
+    int wide_mode = 2;              // cds_set_wide_pglz: 0 never, 1 always, 2 when the last summary counted large values
+    bool wide_hint = false;
+    bool wide_launched = false;     // this decode ran the wide decoder: cds_finish reads its counters
+    uint8_t *wide_mem = nullptr;    // work area of the intra-value parallel pglz decoder (pglz_wide.cuh)
+    WideArea wide;
     uint32_t lut_channels = 0;
     // device buffers
     uint8_t *stage_heap = nullptr, *stage_toast = nullptr;
@@ -127,6 +135,40 @@ extern "C" int cds_host_free(void *ptr)
     return CDS_OK;
 }
 
+// ---- intra-value parallel pglz (pglz_wide.cuh) -----------------------------------------------------
+
+static cudaError_t wide_prepare()
+{
+    cudaError_t e = cudaFuncSetAttribute(k_wide_blocks<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_blocks<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
+    return e;
+}
+
+// Classify the job list and decode the large values; the jobs taken are blanked, so the warp decoder that
+// runs afterwards skips them.
+static int launch_wide(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int num_sms, cudaStream_t st)
+{
+    const uint32_t sms = (uint32_t)num_sms;
+    CU(cudaMemsetAsync(wa.state, 0, sizeof(WideState), st));
+    k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa);
+    k_wide_maps<<<sms * 4u, 256, 0, st>>>(wa);
+    k_wide_super<<<sms * 4u, 128, 0, st>>>(wa);
+    k_wide_chain<<<sms, 32, 0, st>>>(wa);
+    k_wide_entries<<<sms * 4u, 128, 0, st>>>(wa);
+    k_wide_blocks<1><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
+    k_wide_tails<<<sms, 1024, 0, st>>>(wa);
+    k_wide_blocks<3><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
+    CU(cudaGetLastError());
+    LAUNCHED(8);
+    return CDS_OK;
+}
+
+extern "C" int cds_set_wide_pglz_threshold(uint32_t decoded_bytes)
+{
+    g_wide_threshold = decoded_bytes;
+    return CDS_OK;
+}
+
 // ---- handle ------------------------------------------------------------------------------------
 
 template <typename T>
@@ -142,7 +184,7 @@ extern "C" int cds_segment_destroy(cds_segment *s)
     void *bufs[] = {s->stage_heap, s->stage_toast, s->heap_base, s->toast_base, s->rows, s->zero_region, s->scan_vals, s->dir_id, s->dir_loc,
                     s->dir_ref, s->chunk_flag, s->vfirst, s->vcount, s->vseq0, s->vbytes, s->vscr, s->inline_flag,
                     s->row_first, s->pos_of_row, s->row_at_pos, s->ind_len, s->dep_len, s->pos_ind, s->pos_dep,
-                    s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch};
+                    s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch, s->wide_mem};
     for (void *b : bufs) if (b) cudaFree(b);
     if (s->h_state) cudaFreeHost(s->h_state);
     if (s->d_lut) cudaFree(s->d_lut);
@@ -208,10 +250,19 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
         }
     }
     if (stage_pages) { A(stage_heap, max_heap_pages * (uint64_t)kPage); A(stage_toast, max_toast_pages * (uint64_t)kPage); }
+    if (s->cap_scratch) {
+        // wide pglz: 8 bytes per 512-byte source segment of the staged (compressed) values
+        const uint64_t cj = 4096, cs = s->cap_scratch / kWideSeg + cj * kWideSuper, cb = s->cap_scratch / kWideSeg + cj;
+        if (cs < 0xFFFFFFFFull && cb < 0xFFFFFFFFull) {
+            A(wide_mem, wide_area_bytes((uint32_t)cj, (uint32_t)cs, (uint32_t)cb));
+            if (e == cudaSuccess) s->wide = wide_area_carve(s->wide_mem, (uint32_t)cj, (uint32_t)cs, (uint32_t)cb);
+        }
+    }
 #undef A
     if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&s->h_state), sizeof(DevState), cudaHostAllocPortable);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_toast_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGatherSmemBytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
+    if (e == cudaSuccess) e = wide_prepare();
     if (e == cudaSuccess) {
         int coop = 0, per_sm = 0;
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
@@ -233,6 +284,13 @@ extern "C" int cds_set_output_format(cds_segment *s, int independent_var_format)
     if (!s || independent_var_format < 0 || independent_var_format > 2) return CDS_ERR_ARG;
     if (independent_var_format == 2 && !s->d_lut) return CDS_ERR_ARG;       // set the table first
     s->ind_format = independent_var_format;
+    return CDS_OK;
+}
+
+extern "C" int cds_set_wide_pglz(cds_segment *s, int mode)
+{
+    if (!s || mode < 0 || mode > 2) return CDS_ERR_ARG;
+    s->wide_mode = mode;
     return CDS_OK;
 }
 
@@ -260,6 +318,7 @@ static int reset_state(cds_segment *s, cudaStream_t st)
 {
     CU(cudaMemsetAsync(s->zero_region, 0, s->zero_bytes, st));
     s->have_rows = s->have_chunks = s->have_plan = s->have_ops = false;
+    s->wide_launched = false;
     return CDS_OK;
 }
 
@@ -352,6 +411,7 @@ static PlanArgs plan_args(cds_segment *s, uint32_t isb, uint32_t dsb, void *out_
     A.ind_bf16 = s->ind_format == 1 ? 1u : 0u;
     A.ind_u8norm = s->ind_format == 2 ? 1u : 0u;
     A.lut_channels = s->lut_channels ? s->lut_channels : 1u;
+    A.wide_threshold = s->wide_mem && s->ind_format == 0 ? g_wide_threshold : 0u;
     A.out_ind = static_cast<uint8_t *>(out_ind); A.out_dep = static_cast<uint8_t *>(out_dep); A.scratch = s->scratch;
     A.cap_ind = ind_cap; A.cap_dep = dep_cap; A.cap_scratch = s->cap_scratch;
     return A;
@@ -405,6 +465,14 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
         LAUNCHED(1);
         if (timed) { CU(cudaEventRecord(s->ev[2 * s->ev_used + 1], st)); s->ev_used++; }
     }
+    if (s->wide_mem && g_wide_threshold && (s->wide_mode == 1 || (s->wide_mode == 2 && s->wide_hint))) {
+        WideArea wa = s->wide;
+        wa.threshold = g_wide_threshold;
+        wa.st = s->state;
+        int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st);
+        if (rc) return rc;
+        s->wide_launched = true;
+    }
     // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
     k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
         s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket, s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels);
@@ -441,12 +509,18 @@ extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
     cudaStream_t st = (cudaStream_t)stream;
     CU(cudaSetDevice(s->device));
     CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
+    WideState wide_counts;
+    memset(&wide_counts, 0, sizeof(wide_counts));
+    if (s->wide_launched) CU(cudaMemcpyAsync(&wide_counts, s->wide.state, sizeof(WideState), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    if (s->wide_launched) { g_wide_decoded += wide_counts.n_taken; s->wide_launched = false; }
     cds_summary local;
     memset(&local, 0, sizeof(local));
     const DevState &h = *s->h_state;
     local.n_rows = h.n_rows; local.n_positions = h.n_pos; local.ind_bytes = h.ind_bytes; local.dep_bytes = h.dep_bytes;
     local.n_chunks = h.n_chunks; local.n_inline = h.n_inline; local.scratch_bytes = h.scratch_bytes;
+    local.n_wide_values = h.n_wide;
+    s->wide_hint = h.n_wide != 0;
     decode_key(~h.err_inv, &local);
     if (sum) *sum = local;
     return (int)local.status;
@@ -517,6 +591,7 @@ extern "C" int cds_decode_host(cds_segment *s, const void *h_heap, uint64_t n_he
 // ---- measurement hooks ---------------------------------------------------------------------------
 
 extern "C" unsigned long long cds_launch_count(void) { return g_launches; }
+extern "C" unsigned long long cds_wide_decoded_count(void) { return g_wide_decoded; }
 
 extern "C" int cds_timing_enable(cds_segment *s, uint32_t max_samples)
 {
@@ -669,10 +744,35 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, h_src_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_off + n + 1, h_dst_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
+    // values large enough for the intra-value parallel decoder?  (room bounds rawsize from above)
+    uint8_t *d_wide = nullptr;
+    bool any_wide = false;
+    const uint32_t thr = g_wide_threshold;
+    for (uint64_t i = 0; thr && i < n && !any_wide; i++) any_wide = h_dst_off[i + 1] - h_dst_off[i] >= (thr > kWideMinRaw ? thr : kWideMinRaw);
+    uint32_t wj = 0, ws_ = 0, wb = 0;
+    if (e == cudaSuccess && any_wide) {
+        const uint64_t src_bytes = h_src_off[n] - h_src_off[0], dst_bytes = h_dst_off[n] - h_dst_off[0];
+        const uint64_t cj = n < 65536 ? n : 65536, cs = src_bytes / kWideSeg + (cj + 1) * kWideSuper, cb = dst_bytes / kWideBlock + cj + 1;
+        if (cs < 0xFFFFFFFFull && cb < 0xFFFFFFFFull) {
+            wj = (uint32_t)cj; ws_ = (uint32_t)cs; wb = (uint32_t)cb;
+            e = dalloc(&d_wide, wide_area_bytes(wj, ws_, wb));
+            if (e == cudaSuccess) e = wide_prepare();
+        } else {
+            any_wide = false;
+        }
+    }
     if (e == cudaSuccess) {
         k_build_pglz_jobs<<<(uint32_t)((n + 255) / 256), 256, 0, st>>>(static_cast<const uint8_t *>(d_src), d_off,
                                                                        static_cast<uint8_t *>(d_dst), d_off + n + 1, (uint32_t)n,
                                                                        d_jobs, d_stat, nullptr);
+        if (any_wide) {
+            WideArea wa = wide_area_carve(d_wide, wj, ws_, wb);
+            wa.threshold = thr;
+            wa.status = d_stat;
+            int sms = 148;
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+            if (launch_wide(d_jobs, nullptr, (uint32_t)n, wa, sms, st) != CDS_OK) e = cudaErrorUnknown;
+        }
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > 148u * 7u) grid = 148u * 7u;
         k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, (uint32_t)n, d_stat, nullptr,
@@ -682,9 +782,15 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
     }
     if (e == cudaSuccess && h_status) e = cudaMemcpyAsync(h_status, d_stat, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess && any_wide) {
+        WideState wc;
+        e = cudaMemcpy(&wc, d_wide, sizeof(wc), cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) g_wide_decoded += wc.n_taken;
+    }
     if (d_off) cudaFree(d_off);
     if (d_jobs) cudaFree(d_jobs);
     if (d_stat) cudaFree(d_stat);
+    if (d_wide) cudaFree(d_wide);
     if (e != cudaSuccess) return cuda_fail(e, "cds_pglz_decompress_batch");
     return CDS_OK;
 }

@@ -241,6 +241,7 @@ struct PlanArgs {
     uint32_t ind_bf16;            // independent_var leaves as bfloat16 (stored float32): output offsets are halved
     uint32_t ind_u8norm;          // independent_var is uint8 pixels, leaves as float32 through the table: offsets x 4
     uint32_t lut_channels;
+    uint32_t wide_threshold;      // count compressed values of at least this many decoded bytes (0: do not count)
     uint8_t *out_ind, *out_dep, *scratch;
     unsigned long long cap_ind, cap_dep, cap_scratch;
 };
@@ -281,6 +282,7 @@ __device__ __forceinline__ void d_plan_rows(const PlanArgs &A)
                         len[a] = ld_u32(A.toast + (size_t)loc.x * kPage + (loc.y & 0xFFFFu));
                 }
                 A.vscr[v] = ((unsigned long long)va_extsize + 15ull) & ~15ull;
+                if (A.wide_threshold && len[a] >= A.wide_threshold) atomicAdd(&st->n_wide, 1u);
             }
         }
         A.ind_len[r] = len[0];

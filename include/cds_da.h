@@ -62,6 +62,7 @@ typedef struct cds_summary {
     uint64_t err_where;     /* page / row / chunk index the first error refers to           */
     uint32_t status;        /* first data error in the reference's processing order, or 0   */
     uint32_t err_stage;     /* 0 heap scan, 1 TOAST scan, 2 inline rows, 3 external, 4 plan */
+    uint64_t n_wide_values; /* compressed values large enough for the intra-value parallel decoder  */
 } cds_summary;
 
 /* ---- library ------------------------------------------------------------------------------ */
@@ -183,6 +184,21 @@ int cds_export_chunks(cds_segment *seg, uint32_t *h_chunk_id, uint32_t *h_chunk_
  * CDS_OK or CDS_ERR_PGLZ_CORRUPT.  Offsets are host arrays of n+1 entries.  Synchronous. */
 int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_src_off, void *d_dst,
                               const uint64_t *h_dst_off, uint64_t n, int32_t *h_status, void *stream);
+
+/* Intra-value parallel pglz (the paper's packed buffers, one value = 3210 images = 483 MB,
+ * load_imagenet.py:27-31,118-135).  pglz_decompress (ppr:191-231, pg_lzcompress.c:49-143) is serial inside a
+ * value; values whose decoded size is at least the threshold are decoded by the whole GPU instead of by one
+ * warp (csrc/pglz_wide.cuh), same bytes, same corrupt/ok verdict.  Process-wide threshold in decoded bytes
+ * (default 1 MiB; 0 switches the wide decoder off; values under 1024 bytes never take it). */
+int cds_set_wide_pglz_threshold(uint32_t decoded_bytes);
+/* Per handle: 0 = never launch the wide decoder, 1 = always launch it (eight small kernels that find no work
+ * when no value is large), 2 = automatic (default): launch it when the plan counted large values.  In the
+ * step-by-step flow that is this decode's own plan (cds_plan + cds_finish before cds_materialize); the
+ * one-call entry points have no host sync before the decode and go by the last summary read on the handle. */
+int cds_set_wide_pglz(cds_segment *seg, int mode);
+/* Measurement hook: values decoded by the wide decoder so far in this process (counted when a decode's
+ * summary is read / a batch call returns). */
+unsigned long long cds_wide_decoded_count(void);
 
 /* No counterpart in the reference.  cds_pglz_decompress_batch for callers that are not allowed to
  * allocate device memory while they decode — a loader thread beside a framework that has claimed the

@@ -1,0 +1,164 @@
+"""Intra-value parallel pglz (csrc/pglz_wide.cuh) against the oracle: the same streams the
+warp decoder is tested with, pushed through the wide path by lowering its threshold, plus values of many
+output blocks, corrupt streams, and a segment whose values are packed buffers of many images."""
+import struct
+
+import numpy as np
+import pytest
+
+from test_gpu_fuzz import structured_bytes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("GPU tests need a CUDA device")
+    return torch
+
+
+@pytest.fixture()
+def wide_threshold():
+    """Lower the wide-decode threshold for one test, restore the default afterwards."""
+    from cerebro_ds_kpgi_b200 import _lib
+    L = _lib.require_device()
+
+    def set_to(n):
+        _lib.check(L.cds_set_wide_pglz_threshold(int(n)))
+    yield set_to
+    _lib.check(L.cds_set_wide_pglz_threshold(1 << 20))
+
+
+def wide_count():
+    from cerebro_ds_kpgi_b200 import _lib
+    return int(_lib.load().cds_wide_decoded_count())
+
+
+def image_like(rng, n):
+    """float32 bytes with 256 distinct patterns per channel (normalised uint8 pixels): short matches everywhere."""
+    lut = ((np.arange(256)[None, :] / 255.0 - np.array([0.485, 0.456, 0.406])[:, None]) /
+           np.array([0.229, 0.224, 0.225])[:, None]).astype(np.float32)
+    k = n // 4 + 1
+    px = rng.integers(0, 256, k)
+    vals = lut[np.arange(k) % 3, px]
+    return vals.view(np.uint8)[:n].copy()
+
+
+def sparse_like(rng, n):
+    """Criteo-like: float32 zeros with a few ones (long offset-1 runs chained through earlier runs)."""
+    x = np.zeros(n // 4 + 1, dtype=np.float32)
+    x[rng.integers(0, x.size, max(1, x.size // 180))] = 1.0
+    return x.view(np.uint8)[:n].copy()
+
+
+def test_wide_matches_oracle_on_structured_streams(torch_cuda, coracle, wide_threshold):
+    from cerebro_ds_kpgi_b200 import segment, synth
+    wide_threshold(1024)
+    rng = np.random.default_rng(4242)
+    datums, raws = [], []
+    sizes = [1024, 1025, 4095, 4096, 4097, 57343, 57344, 57345, 61439, 2 * 57344, 2 * 57344 + 1, 3 * 57344 - 1, 300001]
+    for t, n in enumerate(sizes + [int(rng.integers(1024, 400000)) for _ in range(24)]):
+        kind = t % 4
+        raw = (structured_bytes(rng, n) if kind == 0 else image_like(rng, n) if kind == 1 else
+               sparse_like(rng, n) if kind == 2 else rng.integers(0, 256, n, dtype=np.uint8))
+        mode = "literal" if t % 7 == 3 else "lz"
+        datums.append(synth.pglz_varlena(raw, mode, effort=int(rng.integers(1, 40))))
+        raws.append(raw.tobytes())
+    # small values in the same batch keep going through the warp decoder
+    for n in (0, 1, 9, 500, 1023):
+        raw = structured_bytes(rng, n)
+        datums.append(synth.pglz_varlena(raw, "lz"))
+        raws.append(raw.tobytes())
+    before = wide_count()
+    out, codes = segment.pglz_decompress_batch(datums)
+    assert wide_count() - before == len(datums) - 5              # every value of >= 1024 bytes took the wide path
+    assert codes == [0] * len(datums)
+    for i, (got, want) in enumerate(zip(out, raws)):
+        assert got == want, "datum %d (%d bytes)" % (i, len(want))
+    for d, want in zip(datums[:6], raws[:6]):
+        assert bytes(coracle.pglz_decompress(d)) == want
+
+
+def test_wide_large_values(torch_cuda, coracle, wide_threshold):
+    """Values of hundreds of output blocks with the default threshold (1 MiB)."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    rng = np.random.default_rng(99)
+    raws = [image_like(rng, 9 * 1024 * 1024 + 13), sparse_like(rng, 7306 * 4 * 300), structured_bytes(rng, 3_000_000),
+            rng.integers(0, 256, 2_500_000, dtype=np.uint8)]
+    modes = ["lz", "lz", "lz", "literal"]
+    datums = [synth.pglz_varlena(r, m) for r, m in zip(raws, modes)]
+    before = wide_count()
+    out, codes = segment.pglz_decompress_batch(datums)
+    assert wide_count() - before == 4
+    assert codes == [0, 0, 0, 0]
+    for got, want, d in zip(out, raws, datums):
+        assert got == want.tobytes()
+        assert bytes(coracle.pglz_decompress(d)) == want.tobytes()
+
+
+def test_wide_corrupt_streams_agree_with_oracle(torch_cuda, coracle, wide_threshold):
+    """Damage streams that take the wide path: wherever the oracle refuses, the wide decoder refuses; wherever it
+    decodes, the bytes are identical."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    wide_threshold(1024)
+    rng = np.random.default_rng(5150)
+    base = [synth.pglz_varlena(structured_bytes(rng, 150000), "lz"), synth.pglz_varlena(image_like(rng, 200000), "lz"),
+            synth.pglz_varlena(sparse_like(rng, 180000), "lz")]
+    datums = []
+    for t in range(90):
+        d = bytearray(base[t % 3])
+        kind = t % 6
+        if kind == 0:                                   # flip one stream byte
+            d[int(rng.integers(8, len(d)))] ^= int(rng.integers(1, 256))
+        elif kind == 1:                                 # early flip: offsets before the output start are likely
+            d[int(rng.integers(8, 40))] ^= int(rng.integers(1, 256))
+        elif kind == 2:                                 # truncate the stream (header adjusted)
+            cut = int(rng.integers(9, len(d)))
+            d = d[:cut]
+            d[0:4] = struct.pack(">I", 0x40000000 | cut)
+        elif kind == 3:                                 # rawsize off by a little
+            raw = struct.unpack_from("<I", d, 4)[0]
+            d[4:8] = struct.pack("<I", max(1024, raw + int(rng.integers(-3, 4))))
+        elif kind == 4:                                 # append junk (header adjusted)
+            d += bytes(rng.integers(0, 256, int(rng.integers(1, 30)), dtype=np.uint8))
+            d[0:4] = struct.pack(">I", 0x40000000 | len(d))
+        else:                                           # zero an offset byte somewhere
+            d[int(rng.integers(8, len(d)))] = 0
+        datums.append(bytes(d))
+    before = wide_count()
+    out, codes = segment.pglz_decompress_batch(datums)
+    assert wide_count() - before >= 60            # (a damaged header can push a stream back to the warp decoder)
+    n_bad = 0
+    for i, d in enumerate(datums):
+        try:
+            want = bytes(coracle.pglz_decompress(d))
+        except Exception:
+            want = None
+        if want is None:
+            n_bad += 1
+            assert codes[i] == 11, i
+        else:
+            assert codes[i] == 0 and out[i] == want, i
+    assert 10 < n_bad < 90
+
+
+def test_packed_buffer_segment_takes_the_wide_path(torch_cuda, coracle, wide_threshold):
+    """B images per buffer (the paper's layout, B = 3210 there): few huge external values per segment."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    ind, dep = synth.imagenet_rows(3, seed=11, shape=(112, 112, 3), classes=1000, images_per_row=24)     # 3.6 MB per value
+    seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="ext_pglz")
+    want = coracle.decode(seg.heap, seg.toast)
+    before = wide_count()
+    st, part = segment.decode_pages(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(seg.toast).cuda())
+    assert st == 0
+    assert part.summary.n_wide_values == 3 and wide_count() - before == 3
+    assert part.ind.cpu().numpy().tobytes() == want["out_ind"].tobytes()
+    assert part.dep.cpu().numpy().tobytes() == want["out_dep"].tobytes()
+    # the same segment with the wide decoder switched off gives the same bytes
+    wide_threshold(0)
+    st2, part2 = segment.decode_pages(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(seg.toast).cuda())
+    assert st2 == 0 and part2.summary.n_wide_values == 0
+    assert torch.equal(part2.ind, part.ind) and torch.equal(part2.dep, part.dep)
