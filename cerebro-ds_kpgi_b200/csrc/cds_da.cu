@@ -149,17 +149,21 @@ static cudaError_t wide_prepare()
 static int launch_wide(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int num_sms, cudaStream_t st)
 {
     const uint32_t sms = (uint32_t)num_sms;
-    CU(cudaMemsetAsync(wa.state, 0, sizeof(WideState), st));
+    CU(cudaMemsetAsync(wa.state, 0, wa.zero_bytes, st));
     k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa);
-    k_wide_maps<<<sms * 4u, 256, 0, st>>>(wa);
+    k_wide_maps<<<sms * 8u, 256, 0, st>>>(wa);
     k_wide_super<<<sms * 4u, 128, 0, st>>>(wa);
     k_wide_chain<<<sms, 32, 0, st>>>(wa);
     k_wide_entries<<<sms * 4u, 128, 0, st>>>(wa);
+    k_wide_outs<<<sms * 8u, 256, 0, st>>>(wa);
+    k_wide_scan<<<sms * 2u, kScanThreads, 0, st>>>(wa);
+    k_wide_check<<<8, 256, 0, st>>>(wa);
+    k_wide_fine<<<sms * 8u, 256, 0, st>>>(wa);
     k_wide_blocks<1><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
     k_wide_tails<<<sms, 1024, 0, st>>>(wa);
     k_wide_blocks<3><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
     CU(cudaGetLastError());
-    LAUNCHED(8);
+    LAUNCHED(12);
     return CDS_OK;
 }
 
@@ -252,7 +256,7 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
     if (stage_pages) { A(stage_heap, max_heap_pages * (uint64_t)kPage); A(stage_toast, max_toast_pages * (uint64_t)kPage); }
     if (s->cap_scratch) {
         // wide pglz: 8 bytes per 512-byte source segment of the staged (compressed) values
-        const uint64_t cj = 4096, cs = s->cap_scratch / kWideSeg + cj * kWideSuper, cb = s->cap_scratch / kWideSeg + cj;
+        const uint64_t cj = 1024, cs = s->cap_scratch / kWideSeg + cj * kWideSuper, cb = s->cap_scratch / kWideSeg + cj;
         if (cs < 0xFFFFFFFFull && cb < 0xFFFFFFFFull) {
             A(wide_mem, wide_area_bytes((uint32_t)cj, (uint32_t)cs, (uint32_t)cb));
             if (e == cudaSuccess) s->wide = wide_area_carve(s->wide_mem, (uint32_t)cj, (uint32_t)cs, (uint32_t)cb);

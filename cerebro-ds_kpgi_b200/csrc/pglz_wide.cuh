@@ -40,6 +40,8 @@ constexpr uint32_t kWideSeg = 512;                 // source bytes per segment
 constexpr uint32_t kWideChunkSegs = 8;             // segments per k_wide_maps step (one per warp)
 constexpr uint32_t kWideChunk = kWideSeg * kWideChunkSegs;
 constexpr uint32_t kWideSuper = 256;               // segments per folded map
+constexpr uint32_t kWideSub = 64;                  // source bytes per sub-segment (one emitting thread each)
+constexpr uint32_t kWideSubs = kWideSeg / kWideSub;
 constexpr uint32_t kWideWin = 4095;                // largest pglz offset
 constexpr uint32_t kWideBlock = 57344;             // output bytes per block
 constexpr uint32_t kWideIdx = 61440;               // index space of a block: [previous tail | block], rounded up
@@ -61,41 +63,61 @@ struct __align__(16) WideJob {
 
 struct WideState {       // zero when a decode starts
     uint32_t n_jobs, n_segs, n_blks;
-    uint32_t t_maps, t_l1, t_l3;
+    uint32_t t_maps, t_l1, t_l3, t_scan;
     uint32_t n_taken;    // values this decoder accepted (the rest stay with the warp decoder)
-    uint32_t pad[9];
+    uint32_t pad[8];
 };
 
 struct WideArea {
-    WideState *state;
+    WideState *state;        // followed by the scan's status words; `zero_bytes` from here are cleared per decode
+    uint32_t *scan_status;
+    unsigned long long *scan_agg, *scan_incl;
     WideJob *jobs;
-    uint2 *seg_entry;        // per flat segment: (output position at its first group, entry offset)
-    uint32_t *supermap;      // per flat super-segment: 32 words
-    uint2 *sseg_entry;       // per flat super-segment: (output position, entry offset)
-    uint32_t *blk_seg0;      // per flat block: local segment holding the group that produces its first byte
+    uint8_t *seg_e;          // per flat segment: entry offset of its first group (0..24; 30: the stream ended before it)
+    uint32_t *seg_out;       // per flat segment: output bytes of the groups that start in it
+    unsigned long long *seg_base;   // exclusive prefix of seg_out over all flat segments (+ total)
+    uint8_t *supermap;       // per flat super-segment: 32 entries
+    uint8_t *sseg_e;         // per flat super-segment: entry offset
+    uint2 *sub_entry;        // per flat sub-segment: (output position at its first group, its offset; kNone: no group starts here)
+    uint32_t *blk_sub0;      // per flat block: local sub-segment holding the group that produces its first byte
     uint32_t cap_jobs, cap_segs, cap_blks;
+    uint32_t zero_bytes;
     uint32_t threshold;      // values with rawsize >= threshold take this path
     int32_t *status;         // per job slot (may be null)
     DevState *st;            // first-error word (may be null)
 };
 
+__host__ __device__ inline size_t wide_align(size_t x) { return (x + 255) & ~(size_t)255; }
+__host__ __device__ inline size_t wide_scan_tiles(uint32_t cap_segs) { return (size_t)cap_segs / (kScanThreads * 8) + 2; }
 __host__ __device__ inline size_t wide_area_bytes(uint32_t cap_jobs, uint32_t cap_segs, uint32_t cap_blks)
 {
-    return 256 + sizeof(WideJob) * (size_t)cap_jobs + 8 * (size_t)cap_segs + (128 + 8) * (size_t)(cap_segs / kWideSuper + 1) +
-           4 * (size_t)(cap_blks + 1) + 256;
+    const size_t tiles = wide_scan_tiles(cap_segs), nss = (size_t)cap_segs / kWideSuper + 1;
+    return wide_align(256 + 4 * tiles) + wide_align(16 * tiles) + wide_align(sizeof(WideJob) * (size_t)cap_jobs) +
+           wide_align((size_t)cap_segs) + wide_align(4 * (size_t)cap_segs) + wide_align(8 * ((size_t)cap_segs + 1)) +
+           wide_align(32 * nss) + wide_align(nss) + wide_align(8 * (size_t)cap_segs * kWideSubs) + wide_align(4 * ((size_t)cap_blks + 1));
 }
 
-// Carve the work area out of one 16-byte aligned allocation (host side).
+// Carve the work area out of one 256-byte aligned allocation (host side).
 inline WideArea wide_area_carve(uint8_t *base, uint32_t cap_jobs, uint32_t cap_segs, uint32_t cap_blks)
 {
     WideArea wa;
+    cap_segs -= cap_segs % kWideSuper;
+    const size_t tiles = wide_scan_tiles(cap_segs), nss = (size_t)cap_segs / kWideSuper + 1;
     uint8_t *p = base;
-    wa.state = reinterpret_cast<WideState *>(p); p += 256;
-    wa.jobs = reinterpret_cast<WideJob *>(p); p += sizeof(WideJob) * (size_t)cap_jobs;
-    wa.seg_entry = reinterpret_cast<uint2 *>(p); p += 8 * (size_t)cap_segs;
-    wa.supermap = reinterpret_cast<uint32_t *>(p); p += 128 * (size_t)(cap_segs / kWideSuper + 1);
-    wa.sseg_entry = reinterpret_cast<uint2 *>(p); p += 8 * (size_t)(cap_segs / kWideSuper + 1);
-    wa.blk_seg0 = reinterpret_cast<uint32_t *>(p);
+    wa.state = reinterpret_cast<WideState *>(p);
+    wa.scan_status = reinterpret_cast<uint32_t *>(p + 256);
+    wa.zero_bytes = (uint32_t)wide_align(256 + 4 * tiles);
+    p += wa.zero_bytes;
+    wa.scan_agg = reinterpret_cast<unsigned long long *>(p);
+    wa.scan_incl = wa.scan_agg + tiles; p += wide_align(16 * tiles);
+    wa.jobs = reinterpret_cast<WideJob *>(p); p += wide_align(sizeof(WideJob) * (size_t)cap_jobs);
+    wa.seg_e = p; p += wide_align((size_t)cap_segs);
+    wa.seg_out = reinterpret_cast<uint32_t *>(p); p += wide_align(4 * (size_t)cap_segs);
+    wa.seg_base = reinterpret_cast<unsigned long long *>(p); p += wide_align(8 * ((size_t)cap_segs + 1));
+    wa.supermap = p; p += wide_align(32 * nss);
+    wa.sseg_e = p; p += wide_align(nss);
+    wa.sub_entry = reinterpret_cast<uint2 *>(p); p += wide_align(8 * (size_t)cap_segs * kWideSubs);
+    wa.blk_sub0 = reinterpret_cast<uint32_t *>(p);
     wa.cap_jobs = cap_jobs; wa.cap_segs = cap_segs; wa.cap_blks = cap_blks;
     wa.threshold = 0; wa.status = nullptr; wa.st = nullptr;
     return wa;
@@ -128,11 +150,6 @@ __device__ inline uint32_t wide_find_blk(const WideArea &wa, uint32_t n, uint32_
         if (wa.jobs[mid].blk0 <= key) lo = mid; else hi = mid;
     }
     return lo;
-}
-
-__device__ inline uint32_t *wide_maps_of(const WideJob &wj)       // segment maps: start of the output region
-{
-    return reinterpret_cast<uint32_t *>((wj.dst + 3ull) & ~3ull);
 }
 
 // ---- classification: which jobs take this path -----------------------------------------------------
@@ -203,51 +220,61 @@ k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, 
     }
     if (threadIdx.x == 0) {
         wa.state->n_jobs = min(sh_base[0], wa.cap_jobs);
-        wa.state->n_segs = sh_base[1];
-        wa.state->n_blks = sh_base[2];
+        wa.state->n_segs = min(sh_base[1], wa.cap_segs);                     // values that fit form a prefix of the list
+        wa.state->n_blks = min(sh_base[2], wa.cap_blks);
     }
 }
 
 // ---- A: group starts ---------------------------------------------------------------------------------
 
-// The group that would start at stream offset a (a < slen), read from `b` (b[0] = the control byte).
-// Returns its length in bytes (0: a tag runs past the source, or the control byte has no item: both
-// end in "corrupt", ppr:229-230) and its output bytes.
-__device__ __forceinline__ uint32_t wide_group(const uint8_t *b, uint32_t a, uint32_t slen, uint32_t *out_bytes)
+// Length in bytes of the group that would start `avail` bytes before the end of the stream, given its control
+// byte and the "length-extension" bits of the following bytes (bit i of `ext`: byte i after the control byte
+// is 0x?F).  0: a tag runs past the source, or the control byte has no item; both end in "corrupt"
+// (ppr:229-230).  Register-only: where a group ends depends on nothing but these bits.
+__device__ __forceinline__ uint32_t wide_group_len(uint32_t ctrl, uint32_t ext, uint32_t avail)
 {
-    const uint32_t ctrl = b[0], avail = slen - a;                            // >= 1
-    uint32_t q = 1, out = 0;
+    uint32_t q = 1;
+    if (avail >= 26u) {                                                      // the whole group lies inside the stream
+#pragma unroll
+        for (uint32_t k = 0; k < 8; k++) q += ((ctrl >> k) & 1u) ? 2u + ((ext >> (q - 1u)) & 1u) : 1u;
+        return q;
+    }
 #pragma unroll
     for (uint32_t k = 0; k < 8; k++) {
         if (q < avail) {                                                     // `sp < srcend` of the inner loop (ppr:203)
             if ((ctrl >> k) & 1u) {
-                const uint32_t b0 = b[q], ext = (b0 & 0x0Fu) == 0x0Fu ? 1u : 0u;
-                if (q + 2u + ext > avail) { *out_bytes = 0; return 0; }
-                out += (b0 & 0x0Fu) + 3u + (ext ? (uint32_t)b[q + 2u] : 0u);  // ppr:205,210-212
-                q += 2u + ext;
+                const uint32_t sz = 2u + ((ext >> (q - 1u)) & 1u);
+                if (q + sz > avail) return 0;
+                q += sz;
             } else {
-                out += 1u;
                 q += 1u;
             }
         }
     }
-    *out_bytes = out;
     return q == 1u ? 0u : q;
 }
 
+__device__ __forceinline__ uint32_t wide_ext_bits(uint32_t w)                // 4 bytes -> 4 bits "(byte & 0x0F) == 0x0F"
+{
+    const uint32_t t = w & (w >> 1) & (w >> 2) & (w >> 3) & 0x01010101u;
+    return (t | (t >> 7) | (t >> 14) | (t >> 21)) & 0xFu;
+}
+
+// Per 4 KB of source: the group length at EVERY position (16 positions per thread, from registers), then one
+// warp per 512-byte segment chases the 25 candidate entries to their exits.
 __global__ void __launch_bounds__(256)
 k_wide_maps(WideArea wa)
 {
-    __shared__ uint8_t sb[kWideChunk + 64];
-    __shared__ uint8_t sdelta[kWideChunk + 32];
-    __shared__ uint16_t sgout[kWideChunk + 32];
+    __shared__ uint16_t sext[kWideChunk / 16 + 8];                           // extension bits, 16 positions per entry
+    __shared__ uint8_t sctrl_extra[64];                                      // source bytes 4096..4159 of the chunk
+    __shared__ __align__(16) uint8_t sdelta[kWideChunk + 32];
     __shared__ uint32_t sh_c;
     const uint32_t n_jobs = wa.state->n_jobs, n_chunks = wa.state->n_segs / kWideChunkSegs;
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, t = threadIdx.x;
     if (n_jobs == 0) return;
     for (;;) {
         __syncthreads();
-        if (threadIdx.x == 0) sh_c = atomicAdd(&wa.state->t_maps, 1u);
+        if (t == 0) sh_c = atomicAdd(&wa.state->t_maps, 1u);
         __syncthreads();
         const uint32_t c = sh_c;
         if (c >= n_chunks) break;
@@ -257,17 +284,56 @@ k_wide_maps(WideArea wa)
         if (wj.state != 0u || lseg >= wj.nseg) continue;
         const uint32_t coff = lseg * kWideSeg, slen = wj.slen;
         const uint8_t *src = reinterpret_cast<const uint8_t *>(wj.src);
-        for (uint32_t i = threadIdx.x; i < kWideChunk + 64; i += blockDim.x) sb[i] = coff + i < slen ? __ldg(src + coff + i) : (uint8_t)0;
+        // my 16 source bytes (zeros past the end of the stream)
+        uint32_t w[4];
+        const uint32_t p0 = coff + 16u * t;
+        if (p0 + 16u <= slen) {
+#pragma unroll
+            for (uint32_t j = 0; j < 4; j++) w[j] = ld_u32(src + p0 + 4u * j);
+        } else {
+#pragma unroll
+            for (uint32_t j = 0; j < 4; j++) {
+                w[j] = 0;
+#pragma unroll
+                for (uint32_t k = 0; k < 4; k++)
+                    if (p0 + 4u * j + k < slen) w[j] |= (uint32_t)__ldg(src + p0 + 4u * j + k) << (8u * k);
+            }
+        }
+        sext[t] = (uint16_t)(wide_ext_bits(w[0]) | (wide_ext_bits(w[1]) << 4) | (wide_ext_bits(w[2]) << 8) | (wide_ext_bits(w[3]) << 12));
+        if (t < 64) {                                                        // the 64 bytes after the chunk
+            const uint32_t a = coff + kWideChunk + t;
+            const uint32_t bv = a < slen ? __ldg(src + a) : 0u;
+            sctrl_extra[t] = (uint8_t)bv;
+            const uint32_t bits = __ballot_sync(0xffffffffu, (bv & 0x0Fu) == 0x0Fu);
+            if ((t & 31u) == 0u) { sext[256 + (t >> 4)] = (uint16_t)bits; sext[257 + (t >> 4)] = (uint16_t)(bits >> 16); }
+        }
+        if (t < 4) sext[260 + t] = 0;
         __syncthreads();
-        for (uint32_t p = threadIdx.x; p < kWideChunk + 25; p += blockDim.x) {
-            uint32_t d = 0, o = 0;
-            if (coff + p < slen) d = wide_group(sb + p, coff + p, slen, &o);
-            sdelta[p] = (uint8_t)d;
-            sgout[p] = (uint16_t)o;
+        {
+            // bits for positions 16t .. 16t+63
+            const unsigned long long e = (unsigned long long)sext[t] | ((unsigned long long)sext[t + 1] << 16) |
+                                         ((unsigned long long)sext[t + 2] << 32) | ((unsigned long long)sext[t + 3] << 48);
+            uint32_t packed[4];
+#pragma unroll
+            for (uint32_t j = 0; j < 16; j++) {
+                const uint32_t a = p0 + j;
+                uint32_t d = 0;
+                if (a < slen) d = wide_group_len((w[j >> 2] >> (8u * (j & 3u))) & 0xFFu, (uint32_t)(e >> (j + 1u)), slen - a);
+                if ((j & 3u) == 0u) packed[j >> 2] = d; else packed[j >> 2] |= d << (8u * (j & 3u));
+            }
+            *reinterpret_cast<uint4 *>(sdelta + 16u * t) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+        }
+        if (t < 32) {                                                        // positions 4096..4127: entries of the next chunk's first segment
+            const uint32_t a = coff + kWideChunk + t;
+            const unsigned long long e = (unsigned long long)sext[256 + (t >> 4)] | ((unsigned long long)sext[257 + (t >> 4)] << 16) |
+                                         ((unsigned long long)sext[258 + (t >> 4)] << 32);
+            uint32_t d = 0;
+            if (a < slen) d = wide_group_len(sctrl_extra[t], (uint32_t)(e >> ((t & 15u) + 1u)), slen - a);
+            sdelta[kWideChunk + t] = (uint8_t)d;
         }
         __syncthreads();
         if (lseg + warp < wj.nseg) {
-            uint32_t p = warp * kWideSeg + lane, out = 0, e;
+            uint32_t p = warp * kWideSeg + lane, e;
             const uint32_t end = (warp + 1u) * kWideSeg;
             if (lane >= 25u) {
                 e = kWideBad;
@@ -278,11 +344,10 @@ k_wide_maps(WideArea wa)
                     if (p >= end) { e = p - end; break; }
                     const uint32_t d = sdelta[p];
                     if (d == 0u) { e = kWideBad; break; }
-                    out += sgout[p];
                     p += d;
                 }
             }
-            wide_maps_of(wj)[(size_t)(lseg + warp) * 32u + lane] = e | (out << 5);
+            reinterpret_cast<uint8_t *>(wj.dst)[(size_t)(lseg + warp) * 32u + lane] = (uint8_t)e;
         }
     }
 }
@@ -301,8 +366,8 @@ k_wide_super(WideArea wa)
         const uint32_t lseg0 = seg - wj.seg0;
         if (wj.state != 0u || lseg0 >= wj.nseg) continue;
         const uint32_t n = min(kWideSuper, wj.nseg - lseg0);
-        const uint32_t *maps = wide_maps_of(wj) + (size_t)lseg0 * 32u;
-        uint32_t e = lane < 25u ? lane : kWideBad, out = 0;
+        const uint8_t *maps = reinterpret_cast<const uint8_t *>(wj.dst) + (size_t)lseg0 * 32u;
+        uint32_t e = lane < 25u ? lane : kWideBad;
         for (uint32_t s = 0; s < n; s += 8) {
             uint32_t r[8];
 #pragma unroll
@@ -310,16 +375,15 @@ k_wide_super(WideArea wa)
 #pragma unroll
             for (uint32_t i = 0; i < 8; i++) {
                 const uint32_t v = __shfl_sync(0xffffffffu, r[i], e < 25u ? e : 0u);
-                if (s + i < n && e < 25u) { out += v >> 5; e = v & 31u; }
+                if (s + i < n && e < 25u) e = v;
             }
         }
-        wa.supermap[(size_t)ss * 32u + lane] = e | (out << 5);
+        wa.supermap[(size_t)ss * 32u + lane] = (uint8_t)e;
     }
 }
 
-// One warp per value: walk its folded maps from the true start (entry 0, output 0), record where every
-// super-segment is entered, and decide ppr:229-230: the chain must end exactly at srcend with exactly
-// rawsize bytes produced.
+// One warp per value: walk its folded maps from the true start (entry 0), record where every super-segment
+// is entered, and decide the first half of ppr:229-230: the chain of groups must end exactly at srcend.
 __global__ void __launch_bounds__(32)
 k_wide_chain(WideArea wa)
 {
@@ -329,7 +393,6 @@ k_wide_chain(WideArea wa)
         if (wj.state != 0u) continue;
         const uint32_t nss = (wj.nseg + kWideSuper - 1) / kWideSuper, ss0 = wj.seg0 / kWideSuper;
         uint32_t e = 0;
-        unsigned long long ob = 0;
         for (uint32_t s = 0; s < nss; s += 8) {
             uint32_t r[8];
 #pragma unroll
@@ -337,17 +400,17 @@ k_wide_chain(WideArea wa)
 #pragma unroll
             for (uint32_t i = 0; i < 8; i++) {
                 if (s + i < nss) {
-                    if (lane == 0) wa.sseg_entry[ss0 + s + i] = make_uint2((uint32_t)ob, e);
+                    if (lane == 0) wa.sseg_e[ss0 + s + i] = (uint8_t)e;
                     const uint32_t v = __shfl_sync(0xffffffffu, r[i], e < 25u ? e : 0u);
-                    if (e < 25u) { ob += v >> 5; e = v & 31u; }
+                    if (e < 25u) e = v;
                 }
             }
         }
-        if (lane == 0 && !(e == kWideEnd && ob == (unsigned long long)wj.rawsize)) wide_fail(wa, jn);
+        if (lane == 0 && e != kWideEnd) wide_fail(wa, jn);
     }
 }
 
-// Unfold: true (output position, entry offset) of every segment, and the segment each output block starts in.
+// Unfold: the true entry offset of every segment.
 __global__ void __launch_bounds__(128)
 k_wide_entries(WideArea wa)
 {
@@ -361,28 +424,133 @@ k_wide_entries(WideArea wa)
         const uint32_t lseg0 = seg - wj.seg0;
         if (wj.state != 0u || lseg0 >= wj.nseg) continue;
         const uint32_t n = min(kWideSuper, wj.nseg - lseg0);
-        const uint32_t *maps = wide_maps_of(wj) + (size_t)lseg0 * 32u;
-        const uint2 ent = wa.sseg_entry[ss];
-        uint32_t ob = ent.x, e = ent.y;
+        const uint8_t *maps = reinterpret_cast<const uint8_t *>(wj.dst) + (size_t)lseg0 * 32u;
+        uint32_t e = wa.sseg_e[ss];
         for (uint32_t s = 0; s < n; s += 8) {
             uint32_t r[8];
 #pragma unroll
             for (uint32_t i = 0; i < 8; i++) r[i] = s + i < n ? maps[(size_t)(s + i) * 32u + lane] : 0u;
 #pragma unroll
             for (uint32_t i = 0; i < 8; i++) {
-                if (s + i < n && e < 25u) {
-                    const uint32_t v = __shfl_sync(0xffffffffu, r[i], e);
-                    const uint32_t nb = ob + (v >> 5);
-                    if (lane == 0) {
-                        wa.seg_entry[seg + s + i] = make_uint2(ob, e);
-                        const uint32_t k = (ob + kWideBlock - 1) / kWideBlock;       // first block boundary at or after ob
-                        if ((unsigned long long)k * kWideBlock < nb && k < wj.nblk) wa.blk_seg0[wj.blk0 + k] = lseg0 + s + i;
-                    }
-                    ob = nb;
-                    e = v & 31u;
+                if (s + i < n) {
+                    if (lane == 0) wa.seg_e[seg + s + i] = (uint8_t)e;
+                    const uint32_t v = __shfl_sync(0xffffffffu, r[i], e < 25u ? e : 0u);
+                    if (e < 25u) e = v;
                 }
             }
         }
+    }
+}
+
+// The group at stream offset a of a well-formed stream: its end and its output bytes.
+__device__ __forceinline__ uint32_t wide_group_walk(const uint8_t *__restrict__ src, uint32_t a, uint32_t slen, uint32_t *out_bytes)
+{
+    const uint32_t ctrl = __ldg(src + a);
+    uint32_t q = a + 1u, out = 0;
+#pragma unroll 1
+    for (uint32_t it = 0; it < 8 && q < slen; it++) {
+        if ((ctrl >> it) & 1u) {
+            const uint32_t b0 = __ldg(src + q);
+            const bool ext = (b0 & 0x0Fu) == 0x0Fu;
+            out += (b0 & 0x0Fu) + 3u + (ext && q + 2u < slen ? (uint32_t)__ldg(src + q + 2u) : 0u);   // ppr:205,210-212
+            q += ext ? 3u : 2u;
+        } else {
+            out += 1u;
+            q += 1u;
+        }
+    }
+    *out_bytes = out;
+    return q;
+}
+
+// One thread per segment: output bytes of the groups that start in it (padding segments and values already
+// refused count 0, so one flat prefix sum serves all values).
+__global__ void __launch_bounds__(256)
+k_wide_outs(WideArea wa)
+{
+    const uint32_t n_jobs = wa.state->n_jobs, n_segs = wa.state->n_segs;
+    if (n_jobs == 0) return;
+    for (uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x; seg < n_segs; seg += gridDim.x * blockDim.x) {
+        const uint32_t jn = wide_find_seg(wa, n_jobs, seg);
+        const WideJob *wjp = &wa.jobs[jn];
+        const uint32_t lseg = seg - wjp->seg0, slen = wjp->slen;
+        uint32_t total = 0;
+        if (wjp->state == 0u && lseg < wjp->nseg) {
+            const uint32_t e = wa.seg_e[seg];
+            if (e < 25u) {
+                const uint8_t *src = reinterpret_cast<const uint8_t *>(wjp->src);
+                const uint32_t end = min((lseg + 1u) * kWideSeg, slen);
+                uint32_t a = lseg * kWideSeg + e;
+                while (a < end) {
+                    uint32_t out;
+                    a = wide_group_walk(src, a, slen, &out);
+                    total += out;
+                }
+            }
+        }
+        wa.seg_out[seg] = total;
+    }
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+k_wide_scan(WideArea wa)
+{
+    bool last;
+    const uint32_t *x = wa.seg_out;
+    ScanWs ws;
+    ws.ticket = &wa.state->t_scan; ws.status = wa.scan_status; ws.agg = wa.scan_agg; ws.incl = wa.scan_incl;
+    device_exclusive_scan<unsigned long long, 8>([&](uint32_t i) { return (unsigned long long)x[i]; }, wa.seg_base, wa.state->n_segs, ws, true, &last);
+}
+
+// Second half of ppr:229-230: exactly rawsize bytes produced.
+__global__ void __launch_bounds__(256)
+k_wide_check(WideArea wa)
+{
+    const uint32_t n_jobs = wa.state->n_jobs;
+    for (uint32_t jn = blockIdx.x * blockDim.x + threadIdx.x; jn < n_jobs; jn += gridDim.x * blockDim.x) {
+        const WideJob *wjp = &wa.jobs[jn];
+        if (wjp->state != 0u) continue;
+        const uint32_t pseg = (wjp->nseg + kWideSuper - 1) / kWideSuper * kWideSuper;
+        if (wa.seg_base[wjp->seg0 + pseg] - wa.seg_base[wjp->seg0] != (unsigned long long)wjp->rawsize) wide_fail(wa, jn);
+    }
+}
+
+// One thread per segment walks its chain of groups again, now knowing the output position it starts at, and
+// records, for each 64-byte sub-segment, where its first group starts and which output byte that group produces
+// first; also the sub-segment every output block starts in.  Sub-segments are the units the block kernels hand
+// to their threads.
+__global__ void __launch_bounds__(256)
+k_wide_fine(WideArea wa)
+{
+    const uint32_t n_jobs = wa.state->n_jobs, n_segs = wa.state->n_segs;
+    if (n_jobs == 0) return;
+    for (uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x; seg < n_segs; seg += gridDim.x * blockDim.x) {
+        const uint32_t jn = wide_find_seg(wa, n_jobs, seg);
+        const WideJob *wjp = &wa.jobs[jn];
+        const uint32_t lseg = seg - wjp->seg0, nseg = wjp->nseg, slen = wjp->slen;
+        if (wjp->state != 0u || lseg >= nseg) continue;
+        const uint8_t *src = reinterpret_cast<const uint8_t *>(wjp->src);
+        const uint32_t nblk = wjp->nblk, blk0 = wjp->blk0;
+        const uint32_t e = wa.seg_e[seg];
+        uint2 *fine = wa.sub_entry + (size_t)seg * kWideSubs;
+        const uint32_t end = min((lseg + 1u) * kWideSeg, slen);
+        uint32_t sub = 0;                                                    // next sub-segment of this segment without a record
+        if (e < 25u) {
+            uint32_t a = lseg * kWideSeg + e, o = (uint32_t)(wa.seg_base[seg] - wa.seg_base[wjp->seg0]);
+            while (a < end) {
+                const uint32_t my_sub = (a - lseg * kWideSeg) / kWideSub;
+                if (my_sub >= sub) { fine[my_sub] = make_uint2(o, a - (lseg * kWideSeg + my_sub * kWideSub)); sub = my_sub + 1u; }
+                uint32_t out;
+                a = wide_group_walk(src, a, slen, &out);
+                const uint32_t k = (o + kWideBlock - 1u) / kWideBlock;       // first block boundary at or after o
+                if ((unsigned long long)k * kWideBlock < (unsigned long long)o + out && k < nblk)
+                    wa.blk_sub0[blk0 + k] = lseg * kWideSubs + my_sub;
+                o += out;
+            }
+        }
+        // sub-segments of the stream's end in which no group starts
+        const uint32_t nsub_here = (end - lseg * kWideSeg + kWideSub - 1u) / kWideSub;
+        for (; sub < nsub_here; sub++) fine[sub] = make_uint2(0u, kNone);
     }
 }
 
@@ -434,13 +602,14 @@ k_wide_blocks(WideArea wa)
         for (uint32_t i = tid; i < kWideIdx / 32; i += kWideThreads) heads[i] = 0;
         __syncthreads();
 
-        // ---- item starts: one thread per source segment that feeds this block
-        const uint32_t s0 = wa.blk_seg0[b], s1 = k + 1u < wj.nblk ? wa.blk_seg0[b + 1] : wj.nseg - 1u;
-        if (tid <= s1 - s0) {
-            const uint32_t s = s0 + tid;
-            const uint2 ent = wa.seg_entry[wj.seg0 + s];
-            uint32_t a = s * kWideSeg + ent.y, o = ent.x;
-            const uint32_t send = min((s + 1u) * kWideSeg, slen);
+        // ---- item starts: one thread per 64-byte source sub-segment that feeds this block
+        const uint32_t sub0 = wa.blk_sub0[b], sub1 = k + 1u < wj.nblk ? wa.blk_sub0[b + 1] : (slen ? (slen - 1u) / kWideSub : 0u);
+        const uint2 *fine = wa.sub_entry + (size_t)wj.seg0 * kWideSubs;
+        for (uint32_t sb = sub0 + tid; sb <= sub1; sb += kWideThreads) {
+            const uint2 ent = fine[sb];
+            if (ent.y == kNone) continue;
+            uint32_t a = sb * kWideSub + ent.y, o = ent.x;
+            const uint32_t send = min((sb + 1u) * kWideSub, slen);
             while (a < send && o < o1) {
                 const uint32_t ctrl = __ldg(src + a);
                 uint32_t q = a + 1u;
@@ -560,7 +729,9 @@ k_wide_blocks(WideArea wa)
 }
 
 // One CTA per value: run down its blocks turning the tail maps of pass 1 into tail bytes, written where
-// pass 3 of the next block expects them (the end of each block's own output region).
+// pass 3 of the next block expects them (the end of each block's own output region).  The maps do not
+// depend on the chain, so they are fetched kTailAhead blocks ahead; the serial step is a shared-memory gather.
+constexpr uint32_t kTailAhead = 6;
 __global__ void __launch_bounds__(1024)
 k_wide_tails(WideArea wa)
 {
@@ -570,22 +741,45 @@ k_wide_tails(WideArea wa)
         const WideJob wj = wa.jobs[jn];
         if (wj.state != 0u || wj.nblk < 2u) continue;
         uint8_t *dst = reinterpret_cast<uint8_t *>(wj.dst);
+        const uint32_t nsteps = wj.nblk - 1u;
+        auto map_of = [&](uint32_t k) {
+            return reinterpret_cast<const uint16_t *>((reinterpret_cast<uintptr_t>(dst + (size_t)k * kWideBlock) + 1u) & ~(uintptr_t)1u);
+        };
         __syncthreads();
         for (uint32_t i = tid; i < 4096; i += blockDim.x) tail[0][i] = 0;
+        // thread t owns entries t, t + 1024, t + 2048, t + 3072 (the last one only below 4095)
+        uint32_t m[kTailAhead][4];
+#pragma unroll
+        for (uint32_t a = 0; a < kTailAhead; a++) {
+#pragma unroll
+            for (uint32_t j = 0; j < 4; j++) {
+                const uint32_t i = tid + 1024u * j;
+                m[a][j] = a < nsteps && i < kWideWin ? map_of(a)[i] : 0x8000u;
+            }
+        }
         __syncthreads();
         uint32_t cur = 0;
-        for (uint32_t k = 0; k + 1u < wj.nblk; k++) {
-            const size_t o0 = (size_t)k * kWideBlock;
-            const uint16_t *map = reinterpret_cast<const uint16_t *>((reinterpret_cast<uintptr_t>(dst + o0) + 1u) & ~(uintptr_t)1u);
-            uint8_t *out = dst + o0 + kWideBlock - kWideWin;
-            for (uint32_t i = tid; i < kWideWin; i += blockDim.x) {
-                const uint32_t m = map[i];
-                const uint8_t v = (m & 0x8000u) ? (uint8_t)m : tail[cur][m & 4095u];
-                tail[cur ^ 1u][i] = v;
-                out[i] = v;
+        for (uint32_t k0 = 0; k0 < nsteps; k0 += kTailAhead) {
+#pragma unroll
+            for (uint32_t a = 0; a < kTailAhead; a++) {
+                const uint32_t k = k0 + a;
+                if (k < nsteps) {                                            // uniform
+                    uint8_t *out = dst + (size_t)k * kWideBlock + kWideBlock - kWideWin;
+#pragma unroll
+                    for (uint32_t j = 0; j < 4; j++) {
+                        const uint32_t i = tid + 1024u * j, mm = m[a][j];
+                        if (i < kWideWin) {
+                            const uint8_t v = (mm & 0x8000u) ? (uint8_t)mm : tail[cur][mm & 4095u];
+                            tail[cur ^ 1u][i] = v;
+                            out[i] = v;
+                        }
+                        const uint32_t kn = k + kTailAhead;
+                        m[a][j] = kn < nsteps && i < kWideWin ? map_of(kn)[i] : 0x8000u;
+                    }
+                    __syncthreads();
+                    cur ^= 1u;
+                }
             }
-            __syncthreads();
-            cur ^= 1u;
         }
     }
 }
