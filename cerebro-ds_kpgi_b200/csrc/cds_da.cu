@@ -160,10 +160,12 @@ static int launch_wide(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs
     k_wide_check<<<8, 256, 0, st>>>(wa);
     k_wide_fine<<<sms * 8u, 256, 0, st>>>(wa);
     k_wide_blocks<1><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
-    k_wide_tails<<<sms, 1024, 0, st>>>(wa);
+    k_wide_tails<0><<<sms, 1024, 0, st>>>(wa);
+    k_wide_tails<1><<<sms, 1024, 0, st>>>(wa);
+    k_wide_tails<2><<<sms, 1024, 0, st>>>(wa);
     k_wide_blocks<3><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
     CU(cudaGetLastError());
-    LAUNCHED(12);
+    LAUNCHED(14);
     return CDS_OK;
 }
 

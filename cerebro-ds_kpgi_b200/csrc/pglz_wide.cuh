@@ -728,25 +728,63 @@ k_wide_blocks(WideArea wa)
     }
 }
 
-// One CTA per value: run down its blocks turning the tail maps of pass 1 into tail bytes, written where
-// pass 3 of the next block expects them (the end of each block's own output region).  The maps do not
-// depend on the chain, so they are fetched kTailAhead blocks ahead; the serial step is a shared-memory gather.
-constexpr uint32_t kTailAhead = 6;
+// Tail chain.  Block k's pass-1 map says, for each of its last 4095 bytes, "value" or "index into the tail of block
+// k-1"; applying the maps in order turns them into bytes.  That is a chain of nblk-1 dependent gathers per value,
+// so it is run in three phases over groups of kTailGroup blocks:
+//   phase 0  one CTA per group folds the group's maps into one (entries stay "value" or "index into the tail
+//            that enters the group"), in parallel over groups;
+//   phase 1  one CTA per value walks the folded maps: the tail entering every group;
+//   phase 2  one CTA per group replays its blocks from that tail and writes every block's tail bytes where pass 3
+//            of the next block reads them (the end of the block's own output region).
+// The maps do not depend on the chain, so they are fetched kTailAhead steps ahead; the serial step is a
+// shared-memory gather.  Folded maps and entering tails live in the group's first block's output region.
+constexpr uint32_t kTailGroup = 32, kTailAhead = 6;
+constexpr uint32_t kTailGmapOff = 8192, kTailGtailOff = 16384;               // inside the first block of a group
+
+__device__ __forceinline__ const uint16_t *wide_u16_at(const uint8_t *p)
+{
+    return reinterpret_cast<const uint16_t *>((reinterpret_cast<uintptr_t>(p) + 1u) & ~(uintptr_t)1u);
+}
+
+template <int kPhase>
 __global__ void __launch_bounds__(1024)
 k_wide_tails(WideArea wa)
 {
-    __shared__ uint8_t tail[2][4096];
+    __shared__ uint16_t tail[2][4096];                                       // 0x8000 | byte, or an index (phase 0 only)
+    __shared__ uint32_t sh_j;
     const uint32_t n_jobs = wa.state->n_jobs, tid = threadIdx.x;
-    for (uint32_t jn = blockIdx.x; jn < n_jobs; jn += gridDim.x) {
-        const WideJob wj = wa.jobs[jn];
-        if (wj.state != 0u || wj.nblk < 2u) continue;
-        uint8_t *dst = reinterpret_cast<uint8_t *>(wj.dst);
-        const uint32_t nsteps = wj.nblk - 1u;
-        auto map_of = [&](uint32_t k) {
-            return reinterpret_cast<const uint16_t *>((reinterpret_cast<uintptr_t>(dst + (size_t)k * kWideBlock) + 1u) & ~(uintptr_t)1u);
-        };
+    if (n_jobs == 0) return;
+    const uint32_t n_units = kPhase == 1 ? n_jobs : wa.state->n_blks;        // phase 1: values; phases 0, 2: group leaders
+    for (uint32_t u = blockIdx.x; u < n_units; u += gridDim.x) {
         __syncthreads();
-        for (uint32_t i = tid; i < 4096; i += blockDim.x) tail[0][i] = 0;
+        if (tid == 0) sh_j = kPhase == 1 ? u : wide_find_blk(wa, n_jobs, u);
+        __syncthreads();
+        const WideJob wj = wa.jobs[sh_j];
+        if (wj.state != 0u || wj.nblk < 2u) continue;
+        const uint32_t nlinks = wj.nblk - 1u;                                // blocks 0 .. nblk-2 hand a tail on
+        uint8_t *dst = reinterpret_cast<uint8_t *>(wj.dst);
+        uint32_t first, nsteps;                                              // steps of this unit; step = block (phases 0, 2) or group (1)
+        if (kPhase == 1) {
+            first = 0;
+            nsteps = (nlinks + kTailGroup - 1u) / kTailGroup;
+        } else {
+            const uint32_t k = u - wj.blk0;
+            if (k >= nlinks || k % kTailGroup) continue;
+            first = k;
+            nsteps = min(kTailGroup, nlinks - k);
+        }
+        auto map_of = [&](uint32_t step) {
+            return kPhase == 1 ? wide_u16_at(dst + (size_t)step * kTailGroup * kWideBlock + kTailGmapOff)
+                               : wide_u16_at(dst + (size_t)(first + step) * kWideBlock);
+        };
+        // state entering the unit
+        for (uint32_t i = tid; i < 4096; i += blockDim.x) {
+            uint32_t v;
+            if (kPhase == 0) v = i;
+            else if (kPhase == 1) v = 0x8000u;
+            else v = 0x8000u | dst[(size_t)first * kWideBlock + kTailGtailOff + i];
+            tail[0][i] = (uint16_t)v;
+        }
         // thread t owns entries t, t + 1024, t + 2048, t + 3072 (the last one only below 4095)
         uint32_t m[kTailAhead][4];
 #pragma unroll
@@ -764,14 +802,18 @@ k_wide_tails(WideArea wa)
             for (uint32_t a = 0; a < kTailAhead; a++) {
                 const uint32_t k = k0 + a;
                 if (k < nsteps) {                                            // uniform
-                    uint8_t *out = dst + (size_t)k * kWideBlock + kWideBlock - kWideWin;
+                    if (kPhase == 1) {                                       // the tail entering group k
+                        uint8_t *gt = dst + (size_t)k * kTailGroup * kWideBlock + kTailGtailOff;
+                        for (uint32_t i = tid; i < 4096; i += blockDim.x) gt[i] = (uint8_t)tail[cur][i];
+                    }
+                    uint8_t *out = dst + (size_t)(first + k) * kWideBlock + kWideBlock - kWideWin;
 #pragma unroll
                     for (uint32_t j = 0; j < 4; j++) {
                         const uint32_t i = tid + 1024u * j, mm = m[a][j];
                         if (i < kWideWin) {
-                            const uint8_t v = (mm & 0x8000u) ? (uint8_t)mm : tail[cur][mm & 4095u];
-                            tail[cur ^ 1u][i] = v;
-                            out[i] = v;
+                            const uint32_t v = (mm & 0x8000u) ? mm : tail[cur][mm & 4095u];
+                            tail[cur ^ 1u][i] = (uint16_t)v;
+                            if (kPhase == 2) out[i] = (uint8_t)v;
                         }
                         const uint32_t kn = k + kTailAhead;
                         m[a][j] = kn < nsteps && i < kWideWin ? map_of(kn)[i] : 0x8000u;
@@ -780,6 +822,10 @@ k_wide_tails(WideArea wa)
                     cur ^= 1u;
                 }
             }
+        }
+        if (kPhase == 0) {                                                   // the folded map of this group
+            uint16_t *gm = const_cast<uint16_t *>(wide_u16_at(dst + (size_t)first * kWideBlock + kTailGmapOff));
+            for (uint32_t i = tid; i < kWideWin; i += blockDim.x) gm[i] = tail[cur][i];
         }
     }
 }
