@@ -10,6 +10,8 @@ plan, gather, pglz, int64 labels).  Workloads (BASELINE.json `configs`):
                    configuration the metric is quoted on)
     imagenet_pglz  configs[2]: mixed pglz-compressed / incompressible rows
     criteo         configs[3]: Criteo-shaped buffers (256 x 7306 f32, pglz) + inline labels
+    imagenet_packed  SURVEY.md 8 f-3: the paper's packed buffers (--images-per-buffer B, default 3210 = 483 MB per
+                   value, pglz): decoded by the intra-value parallel decoder
 
 One JSON line on stdout (rank 0).  `value` = rows/s over all ranks with pages resident in HBM;
 `e2e` = the same through cds_decode_host with pinned HOST page buffers (H2D inside the timed
@@ -30,6 +32,7 @@ REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REPO)
 
 IMAGENET_ROW_BYTES = 112 * 112 * 3 * 4
+IMAGES_PER_BUFFER = int(os.environ.get("CDS_BENCH_IMAGES_PER_BUFFER", "3210"))   # imagenet_packed (--images-per-buffer); workers of the reference arm inherit it through the environment
 LABEL_ROW_BYTES = 1000 * 2
 NVSMI_QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
                "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -80,6 +83,15 @@ def make_workload(name, seed, toast_mib):
                                   keep_expected=False, effort=4)
         meta = dict(isb=7306 * 4, dsb=4, samples=n * B, classes=2,
                     desc="Criteo-shaped buffers (256 x 7306 f32 pglz, int16[256,2] inline pglz)")
+    elif name == "imagenet_packed":
+        # the paper's table layout (load_imagenet.py:27-31): B images per buffer, one huge pglz value each
+        B = IMAGES_PER_BUFFER
+        n = max(1, int(target // (B * IMAGENET_ROW_BYTES * 0.67)))
+        ind, dep = synth.imagenet_rows(n, seed=seed, kind="norm_u8", images_per_row=B)
+        seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="ext_pglz", dist_key=seed - 2018,
+                                  keep_expected=False, effort=4)
+        meta = dict(isb=IMAGENET_ROW_BYTES, dsb=LABEL_ROW_BYTES, samples=n * B, classes=1000,
+                    desc="ImageNet-shaped packed buffers: %d images per buffer (%d MB per value), pglz-compressed" % (B, B * IMAGENET_ROW_BYTES // 10 ** 6))
     else:
         raise SystemExit("unknown workload " + name)
     meta["ind_bytes"] = meta["samples"] * meta["isb"]
@@ -519,12 +531,16 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="imagenet_raw", choices=["imagenet_raw", "imagenet_pglz", "criteo"])
+    ap.add_argument("--workload", default="imagenet_raw", choices=["imagenet_raw", "imagenet_pglz", "criteo", "imagenet_packed"])
+    ap.add_argument("--images-per-buffer", type=int, default=3210, help="imagenet_packed: images per packed buffer (the paper's tables: 3210)")
     ap.add_argument("--toast-mib", type=int, default=1024, help="TOAST file size per segment (config: 1 GiB)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--out-dtype", default="f32", choices=["f32", "bf16"],
                     help="independent_var output: f32 = the reference's bits (default); bf16 = fused conversion (extra, not the metric)")
     args = ap.parse_args()
+    global IMAGES_PER_BUFFER
+    IMAGES_PER_BUFFER = args.images_per_buffer
+    os.environ["CDS_BENCH_IMAGES_PER_BUFFER"] = str(args.images_per_buffer)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference_arm(args)

@@ -48,6 +48,7 @@ constexpr uint32_t kWideIdx = 61440;               // index space of a block: [p
 constexpr uint32_t kWideThreads = 1024;
 constexpr uint32_t kWidePer = kWideIdx / kWideThreads;   // 60 entries per thread
 constexpr uint32_t kWideEnd = 30, kWideBad = 31;   // map states besides the entry offsets 0..24
+constexpr uint32_t kWideShort = 16;                // matches up to this long are written byte by byte by the emitting thread
 constexpr uint32_t kWideMinRaw = 1024;             // below this the maps would not fit the output region
 constexpr size_t kWideBlockSmem = (size_t)kWideIdx * 3 + kWideIdx / 8;
 
@@ -600,9 +601,16 @@ k_wide_blocks(WideArea wa)
         const uint32_t slen = wj.slen;
 
         for (uint32_t i = tid; i < kWideIdx / 32; i += kWideThreads) heads[i] = 0;
+        // the previous tail: terminal entries (their bytes are known in pass 3 only)
+        for (uint32_t e = tid; e < kWideWin; e += kWideThreads) {
+            ptr[e] = (uint16_t)e;
+            if (kMode == 3) val[e] = k > 0u ? dst[o0 - kWideWin + e] : (uint8_t)0;
+        }
         __syncthreads();
 
-        // ---- item starts: one thread per 64-byte source sub-segment that feeds this block
+        // ---- items: one thread per 64-byte source sub-segment that feeds this block.  ptr[] of a marked entry holds
+        //      the distance back to the byte it copies (0: literal).  Literals, item starts and every byte of a match
+        //      of up to kWideShort bytes are marked here; the bodies of longer matches are filled in below.
         const uint32_t sub0 = wa.blk_sub0[b], sub1 = k + 1u < wj.nblk ? wa.blk_sub0[b + 1] : (slen ? (slen - 1u) / kWideSub : 0u);
         const uint2 *fine = wa.sub_entry + (size_t)wj.seg0 * kWideSubs;
         for (uint32_t sb = sub0 + tid; sb <= sub1; sb += kWideThreads) {
@@ -624,10 +632,27 @@ k_wide_blocks(WideArea wa)
                         q += ext ? 3u : 2u;
                         const uint32_t lo = max(o, o0), hi = min(o + len, o1);
                         if (lo < hi) {
-                            if (off == 0u) sh_bad = 1u;
-                            const uint32_t e = kWideWin + (lo - o0);
-                            ptr[e] = (uint16_t)off;
-                            atomicOr(&heads[e >> 5], 1u << (e & 31u));
+                            // (a match cut by the block start is the same match started at the cut: it is periodic in off)
+                            const uint32_t e0 = kWideWin + (lo - o0), n = hi - lo, sh = e0 & 31u;
+                            if (off == 0u) {
+                                sh_bad = 1u;
+                            } else if (n <= kWideShort) {
+                                if (off >= n) {                                  // no overlap: every byte copies the byte `off` back
+                                    for (uint32_t kk = 0; kk < n; kk++) ptr[e0 + kk] = (uint16_t)off;
+                                } else {
+                                    uint32_t r = 0;
+                                    for (uint32_t kk = 0; kk < n; kk++) {        // byte kk copies start - off + kk mod off (ppr:216-219)
+                                        ptr[e0 + kk] = (uint16_t)(kk - r + off);
+                                        if (++r == off) r = 0;
+                                    }
+                                }
+                                const uint32_t mask = (1u << n) - 1u;
+                                atomicOr(&heads[e0 >> 5], mask << sh);
+                                if (sh + n > 32u) atomicOr(&heads[(e0 >> 5) + 1u], mask >> (32u - sh));
+                            } else {
+                                ptr[e0] = (uint16_t)off;
+                                atomicOr(&heads[e0 >> 5], 1u << sh);
+                            }
                         }
                         o += len;
                     } else {
@@ -646,7 +671,7 @@ k_wide_blocks(WideArea wa)
         }
         __syncthreads();
 
-        // ---- every other byte of a match: point at the byte it copies (always before its own item)
+        // ---- bodies of long matches: point at the byte they copy (always before their own item)
         const uint32_t floor_idx = k == 0u ? kWideWin : 0u;                  // nothing exists before the output start
 #pragma unroll 4
         for (uint32_t i = 0; i < kWidePer; i++) {
@@ -663,39 +688,43 @@ k_wide_blocks(WideArea wa)
             ptr[e] = (uint16_t)sidx;
         }
         __syncthreads();
-        // ---- item starts themselves, and the previous tail
-#pragma unroll 4
+        // ---- marked entries: distance -> index
+        uint32_t act[2] = {0u, 0u};                                          // my entries that are not yet resolved
+#pragma unroll
         for (uint32_t i = 0; i < kWidePer; i++) {
             const uint32_t e = i * kWideThreads + tid;
-            if (e < kWideWin) {
-                ptr[e] = (uint16_t)e;
-                if (kMode == 3) val[e] = k > 0u ? dst[o0 - kWideWin + e] : (uint8_t)0;
-            } else if (e < kWideWin + n_out && wide_is_head(heads, e)) {
-                const uint32_t off = ptr[e];
-                uint32_t sidx = e - off;                                      // literal: off == 0
-                if (off && sidx < floor_idx) { sh_bad = 1u; sidx = e; }
-                ptr[e] = (uint16_t)sidx;
+            if (e >= kWideWin && e < kWideWin + n_out) {
+                act[i >> 5] |= 1u << (i & 31u);
+                if (wide_is_head(heads, e)) {
+                    const uint32_t d = ptr[e];
+                    uint32_t sidx = e - d;
+                    if (d && sidx < floor_idx) { sh_bad = 1u; sidx = e; }
+                    ptr[e] = (uint16_t)sidx;
+                }
             }
         }
         __syncthreads();
 
-        // ---- pointer jumping until every byte points at a literal of the block or into the previous tail
-        unsigned long long done = 0;
-#pragma unroll 4
-        for (uint32_t i = 0; i < kWidePer; i++) {
-            const uint32_t e = i * kWideThreads + tid;
-            if (e < kWideWin || e >= kWideWin + n_out) done |= 1ull << i;
-        }
+        // ---- pointer jumping (two hops a round) until every byte points at a literal of the block or into the
+        //      previous tail; resolved entries leave the per-thread work mask
         for (;;) {
             int changed = 0;
-#pragma unroll 4
-            for (uint32_t i = 0; i < kWidePer; i++) {
-                if ((done >> i) & 1ull) continue;
-                const uint32_t e = i * kWideThreads + tid;
-                const uint32_t p = ptr[e];
-                const uint32_t q = ptr[p];
-                if (q == p) done |= 1ull << i;
-                else { ptr[e] = (uint16_t)q; changed = 1; }
+#pragma unroll
+            for (uint32_t half = 0; half < 2; half++) {
+                uint32_t m = act[half];
+                while (m) {
+                    const uint32_t i = (uint32_t)__ffs((int)m) - 1u;
+                    m &= m - 1u;
+                    const uint32_t e = (32u * half + i) * kWideThreads + tid;
+                    const uint32_t p = ptr[e];
+                    const uint32_t q = ptr[p];
+                    if (q == p) {
+                        act[half] &= ~(1u << i);
+                    } else {
+                        ptr[e] = ptr[q];
+                        changed = 1;
+                    }
+                }
             }
             if (!__syncthreads_or(changed)) break;
         }
