@@ -337,6 +337,7 @@ def run_ours(args):
     ds = segment.DeviceSegment(heap_pages, toast_pages, device=local, stage=True)
     bf16 = args.out_dtype == "bf16"
     ds.set_output_format(bf16)
+    _lib.check(L.cds_set_wide_pglz(ds._h, {"off": 0, "force": 1, "auto": 2}[args.wide]))
     d_heap = torch.from_numpy(seg.heap).cuda()
     d_toast = torch.from_numpy(seg.toast).cuda()
     out_ind = torch.empty(meta["ind_bytes"] // (2 if bf16 else 1), dtype=torch.uint8, device="cuda")
@@ -532,6 +533,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="imagenet_raw", choices=["imagenet_raw", "imagenet_pglz", "criteo", "imagenet_packed"])
+    ap.add_argument("--wide", default="auto", choices=["off", "auto", "force"],
+                    help="intra-value parallel pglz decoder: never / decided per decode by the device-side cost model / always")
     ap.add_argument("--images-per-buffer", type=int, default=3210, help="imagenet_packed: images per packed buffer (the paper's tables: 3210)")
     ap.add_argument("--toast-mib", type=int, default=1024, help="TOAST file size per segment (config: 1 GiB)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -68,7 +68,7 @@ PROTOTYPES = {
     "cds_export_chunks": (_int, [_vp, _vp, _vp, _vp, _vp, _u64, _pu64, _vp]),
     "cds_pglz_decompress_batch": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp]),
     "cds_pglz_decompress_batch_static": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
-    "cds_set_wide_pglz_threshold": (_int, [_u32]),
+    "cds_set_wide_pglz_threshold": (_int, [_u32, _int]),
     "cds_set_wide_pglz": (_int, [_vp, _int]),
     "cds_wide_decoded_count": (ctypes.c_ulonglong, []),
     "pglz_decompress": (None, [ctypes.c_char_p, ctypes.c_char_p]),

@@ -24,6 +24,7 @@ static thread_local char g_last_error[512] = "";
 static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py reports it)
 #define LAUNCHED(n) (g_launches += (n))
 static uint32_t g_wide_threshold = 1u << 20;   // cds_set_wide_pglz_threshold
+static int g_wide_force = 0;                   // ... its second argument: skip the cost model
 static unsigned long long g_wide_decoded = 0;  // values decoded by the wide decoder so far (cds_wide_decoded_count)
 
 static int cuda_fail(cudaError_t e, const char *what)
@@ -169,9 +170,10 @@ static int launch_wide(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs
     return CDS_OK;
 }
 
-extern "C" int cds_set_wide_pglz_threshold(uint32_t decoded_bytes)
+extern "C" int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model)
 {
     g_wide_threshold = decoded_bytes;
+    g_wide_force = skip_cost_model ? 1 : 0;
     return CDS_OK;
 }
 
@@ -474,6 +476,7 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
     if (s->wide_mem && g_wide_threshold && (s->wide_mode == 1 || (s->wide_mode == 2 && s->wide_hint))) {
         WideArea wa = s->wide;
         wa.threshold = g_wide_threshold;
+        wa.force = (s->wide_mode == 1 || g_wide_force) ? 1u : 0u;
         wa.st = s->state;
         int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st);
         if (rc) return rc;
@@ -774,6 +777,7 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
         if (any_wide) {
             WideArea wa = wide_area_carve(d_wide, wj, ws_, wb);
             wa.threshold = thr;
+            wa.force = g_wide_force ? 1u : 0u;
             wa.status = d_stat;
             int sms = 148;
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);

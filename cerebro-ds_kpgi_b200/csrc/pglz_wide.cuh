@@ -83,7 +83,8 @@ struct WideArea {
     uint32_t *blk_sub0;      // per flat block: local sub-segment holding the group that produces its first byte
     uint32_t cap_jobs, cap_segs, cap_blks;
     uint32_t zero_bytes;
-    uint32_t threshold;      // values with rawsize >= threshold take this path
+    uint32_t threshold;      // values with rawsize >= threshold are candidates for this path
+    uint32_t force;          // 1: take every candidate; 0: only when the cost model below says it pays
     int32_t *status;         // per job slot (may be null)
     DevState *st;            // first-error word (may be null)
 };
@@ -120,7 +121,7 @@ inline WideArea wide_area_carve(uint8_t *base, uint32_t cap_jobs, uint32_t cap_s
     wa.sub_entry = reinterpret_cast<uint2 *>(p); p += wide_align(8 * (size_t)cap_segs * kWideSubs);
     wa.blk_sub0 = reinterpret_cast<uint32_t *>(p);
     wa.cap_jobs = cap_jobs; wa.cap_segs = cap_segs; wa.cap_blks = cap_blks;
-    wa.threshold = 0; wa.status = nullptr; wa.st = nullptr;
+    wa.threshold = 0; wa.force = 0; wa.status = nullptr; wa.st = nullptr;
     return wa;
 }
 
@@ -158,6 +159,22 @@ __device__ inline uint32_t wide_find_blk(const WideArea &wa, uint32_t n, uint32_
 // the large values to the wide list with their flat segment / block ranges; taken jobs are blanked in the
 // job array so that the warp decoder skips them.  A value also needs slen <= 9/8 rawsize + 9 (anything
 // longer cannot be well-formed and is left to the warp decoder to refuse) and no output conversion.
+//
+// Whether the wide path pays is decided for the whole list from measured rates (profiles/README.md): one warp
+// decodes about 0.06 GB/s of ordinary data and about 0.6 GB/s of run-dominated data (stream under 1/8 of the
+// output: sparse Criteo features), and every value has a warp of its own up to ~4000 values; the wide decoder
+// produces about 55 GB/s in total however few values there are.  So few huge values (the paper's 483 MB
+// buffers) go wide, a thousand 7 MB Criteo buffers stay with their warps.
+constexpr unsigned long long kWarpUnitsDense = 10, kWarpUnitsSparse = 1;    // cost per byte, unit = 1 / 0.6 GB/s
+constexpr unsigned long long kWideBytesPerUnit = 92;                        // 55 GB/s in the same unit
+constexpr unsigned long long kWarpsResident = 4144;                         // 148 SMs x 7 CTAs x 4 warps
+
+__device__ __forceinline__ bool wide_candidate(const PglzJob &job, uint32_t threshold)
+{
+    return job.slen != kNone && (job.slen & kFlagBits) == 0u && job.rawsize >= threshold && job.rawsize >= kWideMinRaw &&
+           (unsigned long long)job.slen <= (unsigned long long)job.rawsize * 9ull / 8ull + 9ull;
+}
+
 __global__ void __launch_bounds__(1024)
 k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa)
 {
@@ -168,15 +185,45 @@ k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, 
     const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
     const uint32_t n_jobs = front + back, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x < 3) sh_base[threadIdx.x] = 0;
+    __shared__ unsigned long long sh_sum_raw, sh_sum_units, sh_max_units;
+    if (threadIdx.x == 0) { sh_sum_raw = 0; sh_sum_units = 0; sh_max_units = 0; }
     __syncthreads();
+    if (!wa.force) {
+        unsigned long long sum_raw = 0, sum_units = 0, max_units = 0;
+        for (uint32_t t = threadIdx.x; t < n_jobs; t += blockDim.x) {
+            const PglzJob job = jobs[t < front ? t : last_slot - (t - front)];
+            if (!wide_candidate(job, wa.threshold)) continue;
+            const unsigned long long units = (unsigned long long)job.rawsize *
+                                             ((unsigned long long)job.slen * 8ull < job.rawsize ? kWarpUnitsSparse : kWarpUnitsDense);
+            sum_raw += job.rawsize;
+            sum_units += units;
+            max_units = max(max_units, units);
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            sum_raw += __shfl_xor_sync(0xffffffffu, sum_raw, d);
+            sum_units += __shfl_xor_sync(0xffffffffu, sum_units, d);
+            max_units = max(max_units, __shfl_xor_sync(0xffffffffu, max_units, d));
+        }
+        if (lane == 0 && sum_raw) {
+            atomicAdd(&sh_sum_raw, sum_raw);
+            atomicAdd(&sh_sum_units, sum_units);
+            atomicMax(&sh_max_units, max_units);
+        }
+        __syncthreads();
+        const unsigned long long warp_units = max(sh_max_units, sh_sum_units / kWarpsResident);
+        if (sh_sum_raw / kWideBytesPerUnit >= warp_units) {                   // the warps are at least as fast: nothing goes wide
+            if (threadIdx.x == 0) { wa.state->n_jobs = 0; wa.state->n_segs = 0; wa.state->n_blks = 0; }
+            return;
+        }
+    }
     for (uint32_t base = 0; base < n_jobs; base += blockDim.x) {
         const uint32_t t = base + threadIdx.x;
         const uint32_t j = t < front ? t : last_slot - (t - front);
         PglzJob job;
         job.slen = kNone;
         if (t < n_jobs) job = jobs[j];
-        bool big = t < n_jobs && job.slen != kNone && (job.slen & kFlagBits) == 0u && job.rawsize >= wa.threshold &&
-                   job.rawsize >= kWideMinRaw && (unsigned long long)job.slen <= (unsigned long long)job.rawsize * 9ull / 8ull + 9ull;
+        bool big = t < n_jobs && wide_candidate(job, wa.threshold);
         uint32_t nseg = 0, nblk = 0;
         if (big) {
             nseg = job.slen ? (job.slen + kWideSeg - 1) / kWideSeg : 1u;

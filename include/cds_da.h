@@ -187,14 +187,18 @@ int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_s
 
 /* Intra-value parallel pglz (the paper's packed buffers, one value = 3210 images = 483 MB,
  * load_imagenet.py:27-31,118-135).  pglz_decompress (ppr:191-231, pg_lzcompress.c:49-143) is serial inside a
- * value; values whose decoded size is at least the threshold are decoded by the whole GPU instead of by one
- * warp (csrc/pglz_wide.cuh), same bytes, same corrupt/ok verdict.  Process-wide threshold in decoded bytes
- * (default 1 MiB; 0 switches the wide decoder off; values under 1024 bytes never take it). */
-int cds_set_wide_pglz_threshold(uint32_t decoded_bytes);
-/* Per handle: 0 = never launch the wide decoder, 1 = always launch it (eight small kernels that find no work
- * when no value is large), 2 = automatic (default): launch it when the plan counted large values.  In the
- * step-by-step flow that is this decode's own plan (cds_plan + cds_finish before cds_materialize); the
- * one-call entry points have no host sync before the decode and go by the last summary read on the handle. */
+ * value; values whose decoded size is at least the threshold can be decoded by the whole GPU instead of by one
+ * warp (csrc/pglz_wide.cuh), same bytes, same corrupt/ok verdict.  Whether they are is decided on the device,
+ * per decode, from the sizes in the job list: few huge values go wide, many medium ones (a thousand 7 MB
+ * Criteo buffers) keep one warp each, which is faster then.  Process-wide settings: threshold in decoded bytes
+ * (default 1 MiB; 0 switches the wide decoder off; values under 1024 bytes never take it);
+ * skip_cost_model != 0 sends every value at or above the threshold through it (tests, measurements). */
+int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model);
+/* Per handle: 0 = never launch the wide decoder, 1 = always launch it and skip the cost model, 2 = automatic
+ * (default): launch it (14 small kernels that find no work when nothing qualifies) when the plan counted large
+ * values.  In the step-by-step flow that is this decode's own plan (cds_plan + cds_finish before
+ * cds_materialize); the one-call entry points have no host sync before the decode and go by the last summary
+ * read on the handle. */
 int cds_set_wide_pglz(cds_segment *seg, int mode);
 /* Measurement hook: values decoded by the wide decoder so far in this process (counted when a decode's
  * summary is read / a batch call returns). */

@@ -25,10 +25,10 @@ def wide_threshold():
     from cerebro_ds_kpgi_b200 import _lib
     L = _lib.require_device()
 
-    def set_to(n):
-        _lib.check(L.cds_set_wide_pglz_threshold(int(n)))
+    def set_to(n, force=1):
+        _lib.check(L.cds_set_wide_pglz_threshold(int(n), int(force)))
     yield set_to
-    _lib.check(L.cds_set_wide_pglz_threshold(1 << 20))
+    _lib.check(L.cds_set_wide_pglz_threshold(1 << 20, 0))
 
 
 def wide_count():
@@ -96,6 +96,21 @@ def test_wide_large_values(torch_cuda, coracle, wide_threshold):
     for got, want, d in zip(out, raws, datums):
         assert got == want.tobytes()
         assert bytes(coracle.pglz_decompress(d)) == want.tobytes()
+
+
+def test_cost_model_keeps_many_medium_values_on_their_warps(torch_cuda, wide_threshold):
+    """A thousand 7 MB Criteo buffers decode faster with one warp each; only few, huge values go wide."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    rng = np.random.default_rng(3)
+    raw = sparse_like(rng, 1_100_000)
+    datum = synth.pglz_varlena(raw, "lz")
+    before = wide_count()
+    out, codes = segment.pglz_decompress_batch([datum] * 120)
+    assert wide_count() == before                               # not taken: 120 run-dominated values keep 120 warps busy
+    assert codes == [0] * 120 and all(o == raw.tobytes() for o in out)
+    out, codes = segment.pglz_decompress_batch([datum] * 3)
+    assert wide_count() - before == 3                           # three of them alone would leave the GPU idle
+    assert codes == [0] * 3 and all(o == raw.tobytes() for o in out)
 
 
 def test_wide_corrupt_streams_agree_with_oracle(torch_cuda, coracle, wide_threshold):

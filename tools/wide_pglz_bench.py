@@ -68,7 +68,7 @@ def main():
     res = {"kind": args.kind, "raw_bytes": n, "stream_bytes": len(datum) - 8, "ratio": round((len(datum) - 8) / n, 4),
            "encode_s": round(t_enc, 2)}
 
-    _lib.check(L.cds_set_wide_pglz_threshold(1 << 20))
+    _lib.check(L.cds_set_wide_pglz_threshold(1 << 20, 0))
     before = L.cds_wide_decoded_count()
     t_wide, out = time_batch(L, torch, datum, args.reps)
     assert L.cds_wide_decoded_count() - before == args.reps
@@ -78,10 +78,10 @@ def main():
 
     nw = min(n, int(args.warp_mib * 2 ** 20))
     small = synth.pglz_varlena(raw[:nw], "literal" if args.kind == "literal" else "lz")
-    _lib.check(L.cds_set_wide_pglz_threshold(0))
+    _lib.check(L.cds_set_wide_pglz_threshold(0, 0))
     t_warp, out = time_batch(L, torch, small, 2)
     assert out.cpu().numpy().tobytes() == raw[:nw].tobytes()
-    _lib.check(L.cds_set_wide_pglz_threshold(1 << 20))
+    _lib.check(L.cds_set_wide_pglz_threshold(1 << 20, 0))
     res["warp_bytes"] = nw
     res["warp_ms"] = round(t_warp * 1e3, 3)
     res["warp_out_GBps"] = round(nw / t_warp / 1e9, 3)
