@@ -419,7 +419,7 @@ static PlanArgs plan_args(cds_segment *s, uint32_t isb, uint32_t dsb, void *out_
     A.ind_bf16 = s->ind_format == 1 ? 1u : 0u;
     A.ind_u8norm = s->ind_format == 2 ? 1u : 0u;
     A.lut_channels = s->lut_channels ? s->lut_channels : 1u;
-    A.wide_threshold = s->wide_mem && s->ind_format == 0 ? g_wide_threshold : 0u;
+    A.wide_threshold = s->wide_mem ? g_wide_threshold : 0u;
     A.out_ind = static_cast<uint8_t *>(out_ind); A.out_dep = static_cast<uint8_t *>(out_dep); A.scratch = s->scratch;
     A.cap_ind = ind_cap; A.cap_dep = dep_cap; A.cap_scratch = s->cap_scratch;
     return A;
@@ -478,6 +478,8 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
         wa.threshold = g_wide_threshold;
         wa.force = (s->wide_mode == 1 || g_wide_force) ? 1u : 0u;
         wa.st = s->state;
+        wa.lut = s->ind_format == 2 ? s->d_lut : nullptr;
+        wa.lut_channels = s->lut_channels ? s->lut_channels : 1u;
         int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st);
         if (rc) return rc;
         s->wide_launched = true;

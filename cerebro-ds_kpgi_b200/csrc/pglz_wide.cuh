@@ -32,6 +32,8 @@
 // Work memory: 8 bytes per source segment.  The segment maps, the tail maps and the resolved tails live
 // inside the value's own (not yet written) output region and are overwritten by pass 3.
 #pragma once
+#include <cuda_bf16.h>
+
 #include "cds_common.cuh"
 
 namespace cds {
@@ -60,7 +62,12 @@ struct __align__(16) WideJob {
     uint32_t blk0;       // first flat output block
     uint32_t nseg, nblk;
     uint32_t state;      // 0 well-formed so far, 1 corrupt, 2 not taken (capacity)
+    uint32_t fmt;        // output: 0 the decoded bytes, 1 float32 -> bfloat16, 2 uint8 -> float32 through the table
 };
+
+// Output address of decoded byte x of a value (x a multiple of 4 for fmt 1).
+__host__ __device__ __forceinline__ size_t wide_scale(uint32_t fmt, size_t x) { return fmt == 1u ? x >> 1 : fmt == 2u ? x << 2 : x; }
+
 
 struct WideState {       // zero when a decode starts
     uint32_t n_jobs, n_segs, n_blks;
@@ -70,8 +77,9 @@ struct WideState {       // zero when a decode starts
 };
 
 struct WideArea {
-    WideState *state;        // followed by the scan's status words; `zero_bytes` from here are cleared per decode
+    WideState *state;        // followed by the scan's status words and the block flags; `zero_bytes` from here are cleared per decode
     uint32_t *scan_status;
+    uint32_t *blk_flag;      // per flat block: pass 3 has read the previous block's tail
     unsigned long long *scan_agg, *scan_incl;
     WideJob *jobs;
     uint8_t *seg_e;          // per flat segment: entry offset of its first group (0..24; 30: the stream ended before it)
@@ -87,6 +95,8 @@ struct WideArea {
     uint32_t force;          // 1: take every candidate; 0: only when the cost model below says it pays
     int32_t *status;         // per job slot (may be null)
     DevState *st;            // first-error word (may be null)
+    const float *lut;        // fmt 2: [channels][256]
+    uint32_t lut_channels;
 };
 
 __host__ __device__ inline size_t wide_align(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -94,7 +104,7 @@ __host__ __device__ inline size_t wide_scan_tiles(uint32_t cap_segs) { return (s
 __host__ __device__ inline size_t wide_area_bytes(uint32_t cap_jobs, uint32_t cap_segs, uint32_t cap_blks)
 {
     const size_t tiles = wide_scan_tiles(cap_segs), nss = (size_t)cap_segs / kWideSuper + 1;
-    return wide_align(256 + 4 * tiles) + wide_align(16 * tiles) + wide_align(sizeof(WideJob) * (size_t)cap_jobs) +
+    return wide_align(256 + 4 * tiles + 4 * ((size_t)cap_blks + 1)) + wide_align(16 * tiles) + wide_align(sizeof(WideJob) * (size_t)cap_jobs) +
            wide_align((size_t)cap_segs) + wide_align(4 * (size_t)cap_segs) + wide_align(8 * ((size_t)cap_segs + 1)) +
            wide_align(32 * nss) + wide_align(nss) + wide_align(8 * (size_t)cap_segs * kWideSubs) + wide_align(4 * ((size_t)cap_blks + 1));
 }
@@ -108,7 +118,8 @@ inline WideArea wide_area_carve(uint8_t *base, uint32_t cap_jobs, uint32_t cap_s
     uint8_t *p = base;
     wa.state = reinterpret_cast<WideState *>(p);
     wa.scan_status = reinterpret_cast<uint32_t *>(p + 256);
-    wa.zero_bytes = (uint32_t)wide_align(256 + 4 * tiles);
+    wa.blk_flag = wa.scan_status + tiles;
+    wa.zero_bytes = (uint32_t)wide_align(256 + 4 * tiles + 4 * ((size_t)cap_blks + 1));
     p += wa.zero_bytes;
     wa.scan_agg = reinterpret_cast<unsigned long long *>(p);
     wa.scan_incl = wa.scan_agg + tiles; p += wide_align(16 * tiles);
@@ -121,7 +132,7 @@ inline WideArea wide_area_carve(uint8_t *base, uint32_t cap_jobs, uint32_t cap_s
     wa.sub_entry = reinterpret_cast<uint2 *>(p); p += wide_align(8 * (size_t)cap_segs * kWideSubs);
     wa.blk_sub0 = reinterpret_cast<uint32_t *>(p);
     wa.cap_jobs = cap_jobs; wa.cap_segs = cap_segs; wa.cap_blks = cap_blks;
-    wa.threshold = 0; wa.force = 0; wa.status = nullptr; wa.st = nullptr;
+    wa.threshold = 0; wa.force = 0; wa.status = nullptr; wa.st = nullptr; wa.lut = nullptr; wa.lut_channels = 1;
     return wa;
 }
 
@@ -158,7 +169,7 @@ __device__ inline uint32_t wide_find_blk(const WideArea &wa, uint32_t n, uint32_
 // One block walks the job list in order (two-ended list of k_resolve when st_counts is given) and appends
 // the large values to the wide list with their flat segment / block ranges; taken jobs are blanked in the
 // job array so that the warp decoder skips them.  A value also needs slen <= 9/8 rawsize + 9 (anything
-// longer cannot be well-formed and is left to the warp decoder to refuse) and no output conversion.
+// longer cannot be well-formed and is left to the warp decoder to refuse).
 //
 // Whether the wide path pays is decided for the whole list from measured rates (profiles/README.md): one warp
 // decodes about 0.06 GB/s of ordinary data and about 0.6 GB/s of run-dominated data (stream under 1/8 of the
@@ -171,8 +182,8 @@ constexpr unsigned long long kWarpsResident = 4144;                         // 1
 
 __device__ __forceinline__ bool wide_candidate(const PglzJob &job, uint32_t threshold)
 {
-    return job.slen != kNone && (job.slen & kFlagBits) == 0u && job.rawsize >= threshold && job.rawsize >= kWideMinRaw &&
-           (unsigned long long)job.slen <= (unsigned long long)job.rawsize * 9ull / 8ull + 9ull;
+    return job.slen != kNone && job.rawsize >= threshold && job.rawsize >= kWideMinRaw &&
+           (unsigned long long)(job.slen & ~kFlagBits) <= (unsigned long long)job.rawsize * 9ull / 8ull + 9ull;
 }
 
 __global__ void __launch_bounds__(1024)
@@ -194,7 +205,7 @@ k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, 
             const PglzJob job = jobs[t < front ? t : last_slot - (t - front)];
             if (!wide_candidate(job, wa.threshold)) continue;
             const unsigned long long units = (unsigned long long)job.rawsize *
-                                             ((unsigned long long)job.slen * 8ull < job.rawsize ? kWarpUnitsSparse : kWarpUnitsDense);
+                                             ((unsigned long long)(job.slen & ~kFlagBits) * 8ull < job.rawsize ? kWarpUnitsSparse : kWarpUnitsDense);
             sum_raw += job.rawsize;
             sum_units += units;
             max_units = max(max_units, units);
@@ -225,8 +236,9 @@ k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, 
         if (t < n_jobs) job = jobs[j];
         bool big = t < n_jobs && wide_candidate(job, wa.threshold);
         uint32_t nseg = 0, nblk = 0;
+        const uint32_t slen = job.slen & ~kFlagBits;
         if (big) {
-            nseg = job.slen ? (job.slen + kWideSeg - 1) / kWideSeg : 1u;
+            nseg = slen ? (slen + kWideSeg - 1) / kWideSeg : 1u;
             nblk = (job.rawsize + kWideBlock - 1) / kWideBlock;
         }
         const uint32_t pseg = (nseg + kWideSuper - 1) / kWideSuper * kWideSuper;
@@ -255,7 +267,8 @@ k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, 
             if (ex[0] < wa.cap_jobs) {
                 WideJob wj;
                 wj.src = job.src; wj.dst = job.dst; wj.err_key = job.err_key;
-                wj.slen = job.slen; wj.rawsize = job.rawsize; wj.job = j;
+                wj.slen = slen; wj.rawsize = job.rawsize; wj.job = j;
+                wj.fmt = (job.slen & kJobToBf16) ? 1u : (job.slen & kJobU8Norm) ? 2u : 0u;
                 wj.seg0 = ex[1]; wj.blk0 = ex[2]; wj.nseg = nseg; wj.nblk = nblk;
                 wj.state = fits ? 0u : 2u;
                 wa.jobs[ex[0]] = wj;
@@ -632,11 +645,11 @@ k_wide_blocks(WideArea wa)
         if (tid == 0) {
             sh_b = atomicAdd(ticket, 1u);
             sh_bad = 0;
-            if (sh_b < n_blks) sh_j = wide_find_blk(wa, n_jobs, sh_b);
+            if (sh_b < n_blks) sh_j = wide_find_blk(wa, n_jobs, kMode == 3 ? n_blks - 1u - sh_b : sh_b);
         }
         __syncthreads();
-        const uint32_t b = sh_b;
-        if (b >= n_blks) break;
+        if (sh_b >= n_blks) break;
+        const uint32_t b = kMode == 3 ? n_blks - 1u - sh_b : sh_b;           // pass 3 runs down the blocks (see the flags below)
         const uint32_t jn = sh_j;
         const WideJob wj = wa.jobs[jn];
         const uint32_t k = b - wj.blk0;
@@ -645,15 +658,21 @@ k_wide_blocks(WideArea wa)
         const uint32_t o0 = k * kWideBlock, o1 = min(o0 + kWideBlock, wj.rawsize), n_out = o1 - o0;
         const uint8_t *src = reinterpret_cast<const uint8_t *>(wj.src);
         uint8_t *dst = reinterpret_cast<uint8_t *>(wj.dst);
+        uint8_t *region = dst + wide_scale(wj.fmt, o0);                      // this block's part of the output buffer
         const uint32_t slen = wj.slen;
 
         for (uint32_t i = tid; i < kWideIdx / 32; i += kWideThreads) heads[i] = 0;
-        // the previous tail: terminal entries (their bytes are known in pass 3 only)
+        // the previous tail: terminal entries (their bytes are known in pass 3 only: k_wide_tails left them at the end
+        // of the previous block's region)
         for (uint32_t e = tid; e < kWideWin; e += kWideThreads) {
             ptr[e] = (uint16_t)e;
-            if (kMode == 3) val[e] = k > 0u ? dst[o0 - kWideWin + e] : (uint8_t)0;
+            if (kMode == 3) val[e] = k > 0u ? *(region - kWideWin + e) : (uint8_t)0;
         }
         __syncthreads();
+        if (kMode == 3 && tid == 0) {                                        // the previous block may now overwrite its region
+            __threadfence();
+            *reinterpret_cast<volatile uint32_t *>(&wa.blk_flag[b]) = 1u;
+        }
 
         // ---- items: one thread per 64-byte source sub-segment that feeds this block.  ptr[] of a marked entry holds
         //      the distance back to the byte it copies (0: literal).  Literals, item starts and every byte of a match
@@ -782,13 +801,39 @@ k_wide_blocks(WideArea wa)
 
         if (kMode == 1) {
             // the block's last 4095 bytes, each as "value" or "index into the previous tail"
-            uint16_t *map = reinterpret_cast<uint16_t *>((reinterpret_cast<uintptr_t>(dst + o0) + 1u) & ~(uintptr_t)1u);
+            uint16_t *map = reinterpret_cast<uint16_t *>((reinterpret_cast<uintptr_t>(region) + 1u) & ~(uintptr_t)1u);
             for (uint32_t i = tid; i < kWideWin; i += kWideThreads) {
                 const uint32_t r = ptr[kWideWin + kWideBlock - kWideWin + i];
                 map[i] = (uint16_t)(r >= kWideWin ? 0x8000u | val[r] : r);
             }
+            continue;
+        }
+        // Pass 3 overwrites the whole region, including the tail bytes the NEXT block's pass 3 reads: wait until it has
+        // read them.  Blocks are handed out from the last to the first, so that block already runs (or is done).
+        if (k + 1u < wj.nblk) {
+            if (tid == 0) {
+                while (*reinterpret_cast<volatile uint32_t *>(&wa.blk_flag[b + 1]) == 0u) { }
+                __threadfence();
+            }
+            __syncthreads();
+        }
+        if (wj.fmt == 1u) {
+            // float32 -> bfloat16 (round to nearest even), one element per thread and step
+            __nv_bfloat16 *g = reinterpret_cast<__nv_bfloat16 *>(region);
+            for (uint32_t f = tid; f < (n_out >> 2); f += kWideThreads) {
+                const uint32_t e0 = kWideWin + 4u * f;
+                const uint32_t x = (uint32_t)val[ptr[e0]] | ((uint32_t)val[ptr[e0 + 1u]] << 8) |
+                                   ((uint32_t)val[ptr[e0 + 2u]] << 16) | ((uint32_t)val[ptr[e0 + 3u]] << 24);
+                g[f] = __float2bfloat16_rn(__uint_as_float(x));
+            }
+        } else if (wj.fmt == 2u) {
+            // uint8 pixel component -> float32 table[channel][x]
+            float *g = reinterpret_cast<float *>(region);
+            const uint32_t ch = wa.lut_channels;
+            for (uint32_t i = tid; i < n_out; i += kWideThreads)
+                __stcs(g + i, __ldg(wa.lut + ((o0 + i) % ch) * 256u + val[ptr[kWideWin + i]]));
         } else {
-            uint8_t *g = dst + o0;
+            uint8_t *g = region;
             const uint32_t head = min(n_out, (uint32_t)((4u - (reinterpret_cast<uintptr_t>(g) & 3u)) & 3u));
             if (tid < head) g[tid] = val[ptr[kWideWin + tid]];
             const uint32_t nw = (n_out - head) >> 2;
@@ -813,7 +858,8 @@ k_wide_blocks(WideArea wa)
 //   phase 2  one CTA per group replays its blocks from that tail and writes every block's tail bytes where pass 3
 //            of the next block reads them (the end of the block's own output region).
 // The maps do not depend on the chain, so they are fetched kTailAhead steps ahead; the serial step is a
-// shared-memory gather.  Folded maps and entering tails live in the group's first block's output region.
+// shared-memory gather.  Folded maps and entering tails live in the group's first block's output region (regions
+// are at least 28672 bytes: float32 -> bfloat16 output halves them).
 constexpr uint32_t kTailGroup = 32, kTailAhead = 6;
 constexpr uint32_t kTailGmapOff = 8192, kTailGtailOff = 16384;               // inside the first block of a group
 
@@ -849,16 +895,18 @@ k_wide_tails(WideArea wa)
             first = k;
             nsteps = min(kTailGroup, nlinks - k);
         }
+        const uint32_t fmt = wj.fmt;
+        auto region = [&](uint32_t blk) { return dst + wide_scale(fmt, (size_t)blk * kWideBlock); };   // block's part of the output buffer
+        const size_t region_bytes = wide_scale(fmt, (size_t)kWideBlock);
         auto map_of = [&](uint32_t step) {
-            return kPhase == 1 ? wide_u16_at(dst + (size_t)step * kTailGroup * kWideBlock + kTailGmapOff)
-                               : wide_u16_at(dst + (size_t)(first + step) * kWideBlock);
+            return kPhase == 1 ? wide_u16_at(region(step * kTailGroup) + kTailGmapOff) : wide_u16_at(region(first + step));
         };
         // state entering the unit
         for (uint32_t i = tid; i < 4096; i += blockDim.x) {
             uint32_t v;
             if (kPhase == 0) v = i;
             else if (kPhase == 1) v = 0x8000u;
-            else v = 0x8000u | dst[(size_t)first * kWideBlock + kTailGtailOff + i];
+            else v = 0x8000u | region(first)[kTailGtailOff + i];
             tail[0][i] = (uint16_t)v;
         }
         // thread t owns entries t, t + 1024, t + 2048, t + 3072 (the last one only below 4095)
@@ -879,10 +927,10 @@ k_wide_tails(WideArea wa)
                 const uint32_t k = k0 + a;
                 if (k < nsteps) {                                            // uniform
                     if (kPhase == 1) {                                       // the tail entering group k
-                        uint8_t *gt = dst + (size_t)k * kTailGroup * kWideBlock + kTailGtailOff;
+                        uint8_t *gt = region(k * kTailGroup) + kTailGtailOff;
                         for (uint32_t i = tid; i < 4096; i += blockDim.x) gt[i] = (uint8_t)tail[cur][i];
                     }
-                    uint8_t *out = dst + (size_t)(first + k) * kWideBlock + kWideBlock - kWideWin;
+                    uint8_t *out = region(first + k) + region_bytes - kWideWin;
 #pragma unroll
                     for (uint32_t j = 0; j < 4; j++) {
                         const uint32_t i = tid + 1024u * j, mm = m[a][j];
@@ -900,7 +948,7 @@ k_wide_tails(WideArea wa)
             }
         }
         if (kPhase == 0) {                                                   // the folded map of this group
-            uint16_t *gm = const_cast<uint16_t *>(wide_u16_at(dst + (size_t)first * kWideBlock + kTailGmapOff));
+            uint16_t *gm = const_cast<uint16_t *>(wide_u16_at(region(first) + kTailGmapOff));
             for (uint32_t i = tid; i < kWideWin; i += blockDim.x) gm[i] = tail[cur][i];
         }
     }

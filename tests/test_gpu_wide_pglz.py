@@ -177,3 +177,36 @@ def test_packed_buffer_segment_takes_the_wide_path(torch_cuda, coracle, wide_thr
     st2, part2 = segment.decode_pages(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(seg.toast).cuda())
     assert st2 == 0 and part2.summary.n_wide_values == 0
     assert torch.equal(part2.ind, part.ind) and torch.equal(part2.dep, part.dep)
+
+
+def test_packed_buffers_bf16_and_uint8_outputs_take_the_wide_path(torch_cuda, coracle, wide_threshold):
+    """The output conversions of the warp decoder (float32 -> bfloat16, uint8 -> float32 through the table) on the
+    wide path: same results as converting the oracle's bytes."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    ind, dep = synth.imagenet_rows(3, seed=12, shape=(112, 112, 3), classes=1000, images_per_row=20)     # 3 MB per value
+    seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="ext_pglz")
+    want = coracle.decode(seg.heap, seg.toast)
+    before = wide_count()
+    st, part = segment.decode_pages(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(seg.toast).cuda(), ind_bf16=True)
+    assert st == 0 and wide_count() - before == 3
+    ref = torch.from_numpy(want["out_ind"].view(np.float32).copy()).to(torch.bfloat16)
+    got = part.ind.view(torch.bfloat16).cpu()
+    assert got.shape == ref.shape and torch.equal(got.view(torch.int16), ref.view(torch.int16))
+    assert part.dep.cpu().numpy().tobytes() == want["out_dep"].tobytes()
+
+    rng = np.random.default_rng(77)
+    px = []
+    for i in range(3):
+        x = rng.integers(0, 256, size=(30, 112, 112, 3), dtype=np.uint8)        # 1.1 MB per value
+        x[:, 30:80] = x[:, 30:31]                                                # repeated rows: real matches
+        px.append(x)
+    seg = synth.build_segment(px, dep, ind_storage="ext_pglz", dep_storage="ext_pglz")
+    lut = synth.norm_lut()
+    flat = np.concatenate([p.reshape(-1, 3) for p in px])
+    want_f = lut[np.arange(3)[None, :], flat].astype(np.float32).reshape(-1)
+    before = wide_count()
+    st, part = segment.decode_pages(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(seg.toast).cuda(), u8_normalize=lut)
+    assert st == 0 and wide_count() - before == 3
+    got = part.ind.view(torch.float32).cpu().numpy()
+    assert got.shape == want_f.shape and got.tobytes() == want_f.tobytes()
