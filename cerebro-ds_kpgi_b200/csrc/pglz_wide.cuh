@@ -50,6 +50,7 @@ constexpr uint32_t kWideIdx = 61440;               // index space of a block: [p
 constexpr uint32_t kWideThreads = 1024;
 constexpr uint32_t kWidePer = kWideIdx / kWideThreads;   // 60 entries per thread
 constexpr uint32_t kWideEnd = 30, kWideBad = 31;   // map states besides the entry offsets 0..24
+constexpr uint32_t kWideChase = 48;                // pass 1 follows a tail byte's chain this many hops before resolving the whole block
 constexpr uint32_t kWideShort = 16;                // matches up to this long are written byte by byte by the emitting thread
 constexpr uint32_t kWideMinRaw = 1024;             // below this the maps would not fit the output region
 constexpr size_t kWideBlockSmem = (size_t)kWideIdx * 3 + kWideIdx / 8;
@@ -771,9 +772,26 @@ k_wide_blocks(WideArea wa)
         }
         __syncthreads();
 
+        // Pass 1 only needs the roots of the block's last 4095 bytes: follow those chains directly, a bounded number
+        // of hops; only when a chain is longer (run-dominated data) resolve the whole block as pass 3 does.
+        bool resolve_all = true;
+        uint32_t tail_root[4];
+        if (kMode == 1) {
+            int unfinished = 0;
+#pragma unroll
+            for (uint32_t j = 0; j < 4; j++) {
+                const uint32_t i = tid + kWideThreads * j;
+                uint32_t r = i < kWideWin ? (uint32_t)ptr[kWideBlock + i] : 0u;      // entry kWideWin + (kWideBlock - kWideWin) + i
+                uint32_t q = ptr[r];
+                for (uint32_t hop = 0; hop < kWideChase && q != r; hop++) { r = q; q = ptr[r]; }
+                if (q != r) unfinished = 1;
+                tail_root[j] = r;
+            }
+            resolve_all = __syncthreads_or(unfinished) != 0;
+        }
         // ---- pointer jumping (two hops a round) until every byte points at a literal of the block or into the
         //      previous tail; resolved entries leave the per-thread work mask
-        for (;;) {
+        for (; resolve_all;) {
             int changed = 0;
 #pragma unroll
             for (uint32_t half = 0; half < 2; half++) {
@@ -802,9 +820,13 @@ k_wide_blocks(WideArea wa)
         if (kMode == 1) {
             // the block's last 4095 bytes, each as "value" or "index into the previous tail"
             uint16_t *map = reinterpret_cast<uint16_t *>((reinterpret_cast<uintptr_t>(region) + 1u) & ~(uintptr_t)1u);
-            for (uint32_t i = tid; i < kWideWin; i += kWideThreads) {
-                const uint32_t r = ptr[kWideWin + kWideBlock - kWideWin + i];
-                map[i] = (uint16_t)(r >= kWideWin ? 0x8000u | val[r] : r);
+#pragma unroll
+            for (uint32_t j = 0; j < 4; j++) {
+                const uint32_t i = tid + kWideThreads * j;
+                if (i < kWideWin) {
+                    const uint32_t r = resolve_all ? (uint32_t)ptr[kWideBlock + i] : tail_root[j];
+                    map[i] = (uint16_t)(r >= kWideWin ? 0x8000u | val[r] : r);
+                }
             }
             continue;
         }
