@@ -654,7 +654,11 @@ k_wide_blocks(WideArea wa)
         const uint32_t jn = sh_j;
         const WideJob wj = wa.jobs[jn];
         const uint32_t k = b - wj.blk0;
-        if (wj.state != 0u || k >= wj.nblk) continue;
+        if (wj.state != 0u || k >= wj.nblk) {
+            // (a block that is skipped still answers its predecessor, which may have started before the value was refused)
+            if (kMode == 3 && tid == 0) *reinterpret_cast<volatile uint32_t *>(&wa.blk_flag[b]) = 1u;
+            continue;
+        }
         if (kMode == 1 && k + 1u == wj.nblk) continue;                       // nobody needs the last block's tail
         const uint32_t o0 = k * kWideBlock, o1 = min(o0 + kWideBlock, wj.rawsize), n_out = o1 - o0;
         const uint8_t *src = reinterpret_cast<const uint8_t *>(wj.src);
