@@ -679,9 +679,10 @@ k_wide_blocks(WideArea wa)
             *reinterpret_cast<volatile uint32_t *>(&wa.blk_flag[b]) = 1u;
         }
 
-        // ---- items: one thread per 64-byte source sub-segment that feeds this block.  ptr[] of a marked entry holds
-        //      the distance back to the byte it copies (0: literal).  Literals, item starts and every byte of a match
-        //      of up to kWideShort bytes are marked here; the bodies of longer matches are filled in below.
+        // ---- items: one thread per 64-byte source sub-segment that feeds this block.  Literals and every byte of a
+        //      match of up to kWideShort bytes get their pointer here and are marked in the bitmap; of a longer match
+        //      only the first byte is (its offset is parked in the two unused value bytes), the body is filled in below.
+        const uint32_t floor_idx = k == 0u ? kWideWin : 0u;                  // nothing exists before the output start
         const uint32_t sub0 = wa.blk_sub0[b], sub1 = k + 1u < wj.nblk ? wa.blk_sub0[b + 1] : (slen ? (slen - 1u) / kWideSub : 0u);
         const uint2 *fine = wa.sub_entry + (size_t)wj.seg0 * kWideSubs;
         for (uint32_t sb = sub0 + tid; sb <= sub1; sb += kWideThreads) {
@@ -705,15 +706,15 @@ k_wide_blocks(WideArea wa)
                         if (lo < hi) {
                             // (a match cut by the block start is the same match started at the cut: it is periodic in off)
                             const uint32_t e0 = kWideWin + (lo - o0), n = hi - lo, sh = e0 & 31u;
-                            if (off == 0u) {
+                            if (off == 0u || e0 - off < floor_idx) {             // offset 0, or before the start of the output
                                 sh_bad = 1u;
                             } else if (n <= kWideShort) {
                                 if (off >= n) {                                  // no overlap: every byte copies the byte `off` back
-                                    for (uint32_t kk = 0; kk < n; kk++) ptr[e0 + kk] = (uint16_t)off;
+                                    for (uint32_t kk = 0; kk < n; kk++) ptr[e0 + kk] = (uint16_t)(e0 + kk - off);
                                 } else {
                                     uint32_t r = 0;
                                     for (uint32_t kk = 0; kk < n; kk++) {        // byte kk copies start - off + kk mod off (ppr:216-219)
-                                        ptr[e0 + kk] = (uint16_t)(kk - r + off);
+                                        ptr[e0 + kk] = (uint16_t)(e0 - off + r);
                                         if (++r == off) r = 0;
                                     }
                                 }
@@ -721,7 +722,9 @@ k_wide_blocks(WideArea wa)
                                 atomicOr(&heads[e0 >> 5], mask << sh);
                                 if (sh + n > 32u) atomicOr(&heads[(e0 >> 5) + 1u], mask >> (32u - sh));
                             } else {
-                                ptr[e0] = (uint16_t)off;
+                                ptr[e0] = (uint16_t)(e0 - off);
+                                val[e0] = (uint8_t)off;
+                                val[e0 + 1u] = (uint8_t)(off >> 8);
                                 atomicOr(&heads[e0 >> 5], 1u << sh);
                             }
                         }
@@ -730,7 +733,7 @@ k_wide_blocks(WideArea wa)
                         if (o >= o0) {
                             const uint32_t e = kWideWin + (o - o0);
                             val[e] = __ldg(src + q);
-                            ptr[e] = 0;
+                            ptr[e] = (uint16_t)e;
                             atomicOr(&heads[e >> 5], 1u << (e & 31u));
                         }
                         o += 1u;
@@ -743,36 +746,21 @@ k_wide_blocks(WideArea wa)
         __syncthreads();
 
         // ---- bodies of long matches: point at the byte they copy (always before their own item)
-        const uint32_t floor_idx = k == 0u ? kWideWin : 0u;                  // nothing exists before the output start
+        uint32_t act[2] = {0u, 0u};                                          // my entries that are not yet resolved
 #pragma unroll 4
         for (uint32_t i = 0; i < kWidePer; i++) {
             const uint32_t e = i * kWideThreads + tid;
-            if (e < kWideWin || e >= kWideWin + n_out || wide_is_head(heads, e)) continue;
+            if (e < kWideWin || e >= kWideWin + n_out) continue;
+            act[i >> 5] |= 1u << (i & 31u);
+            if (wide_is_head(heads, e)) continue;
             const uint32_t h = wide_head_of(heads, e);
             if (h == kNone) { sh_bad = 1u; ptr[e] = (uint16_t)e; continue; }  // cannot happen on a stream k_wide_chain accepted
-            const uint32_t off = ptr[h], kk = e - h;
+            const uint32_t off = (uint32_t)val[h] | ((uint32_t)val[h + 1u] << 8), kk = e - h;
             uint32_t sidx;
             if (off > kk) sidx = e - off;
             else if (off <= 1u) sidx = h - 1u;                                // runs of one byte value
             else sidx = h - off + kk % off;                                   // overlapping copy (ppr:216-219)
-            if (sidx < floor_idx || off == 0u) { sh_bad = 1u; sidx = e; }
             ptr[e] = (uint16_t)sidx;
-        }
-        __syncthreads();
-        // ---- marked entries: distance -> index
-        uint32_t act[2] = {0u, 0u};                                          // my entries that are not yet resolved
-#pragma unroll
-        for (uint32_t i = 0; i < kWidePer; i++) {
-            const uint32_t e = i * kWideThreads + tid;
-            if (e >= kWideWin && e < kWideWin + n_out) {
-                act[i >> 5] |= 1u << (i & 31u);
-                if (wide_is_head(heads, e)) {
-                    const uint32_t d = ptr[e];
-                    uint32_t sidx = e - d;
-                    if (d && sidx < floor_idx) { sh_bad = 1u; sidx = e; }
-                    ptr[e] = (uint16_t)sidx;
-                }
-            }
         }
         __syncthreads();
 
