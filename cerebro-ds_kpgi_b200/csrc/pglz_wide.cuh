@@ -42,7 +42,7 @@ constexpr uint32_t kWideSeg = 512;                 // source bytes per segment
 constexpr uint32_t kWideChunkSegs = 8;             // segments per k_wide_maps step (one per warp)
 constexpr uint32_t kWideChunk = kWideSeg * kWideChunkSegs;
 constexpr uint32_t kWideSuper = 256;               // segments per folded map
-constexpr uint32_t kWideSub = 64;                  // source bytes per sub-segment (one emitting thread each)
+constexpr uint32_t kWideSub = 32;                  // source bytes per sub-segment (one emitting thread each; > 25, so a group starts in each)
 constexpr uint32_t kWideSubs = kWideSeg / kWideSub;
 constexpr uint32_t kWideWin = 4095;                // largest pglz offset
 constexpr uint32_t kWideBlock = 57344;             // output bytes per block
@@ -51,7 +51,7 @@ constexpr uint32_t kWideThreads = 1024;
 constexpr uint32_t kWidePer = kWideIdx / kWideThreads;   // 60 entries per thread
 constexpr uint32_t kWideEnd = 30, kWideBad = 31;   // map states besides the entry offsets 0..24
 constexpr uint32_t kWideChase = 48;                // pass 1 follows a tail byte's chain this many hops before resolving the whole block
-constexpr uint32_t kWideShort = 16;                // matches up to this long are written byte by byte by the emitting thread
+constexpr uint32_t kWideShort = 2;                 // (cut) matches up to this long are written byte by byte by the emitting thread
 constexpr uint32_t kWideMinRaw = 1024;             // below this the maps would not fit the output region
 constexpr size_t kWideBlockSmem = (size_t)kWideIdx * 3 + kWideIdx / 8;
 
@@ -88,7 +88,8 @@ struct WideArea {
     unsigned long long *seg_base;   // exclusive prefix of seg_out over all flat segments (+ total)
     uint8_t *supermap;       // per flat super-segment: 32 entries
     uint8_t *sseg_e;         // per flat super-segment: entry offset
-    uint2 *sub_entry;        // per flat sub-segment: (output position at its first group, its offset; kNone: no group starts here)
+    uint32_t *sub_entry;     // per flat sub-segment: (output position of its first group relative to the segment's) << 5 | its offset
+                             // (31: no group starts here)
     uint32_t *blk_sub0;      // per flat block: local sub-segment holding the group that produces its first byte
     uint32_t cap_jobs, cap_segs, cap_blks;
     uint32_t zero_bytes;
@@ -107,7 +108,7 @@ __host__ __device__ inline size_t wide_area_bytes(uint32_t cap_jobs, uint32_t ca
     const size_t tiles = wide_scan_tiles(cap_segs), nss = (size_t)cap_segs / kWideSuper + 1;
     return wide_align(256 + 4 * tiles + 4 * ((size_t)cap_blks + 1)) + wide_align(16 * tiles) + wide_align(sizeof(WideJob) * (size_t)cap_jobs) +
            wide_align((size_t)cap_segs) + wide_align(4 * (size_t)cap_segs) + wide_align(8 * ((size_t)cap_segs + 1)) +
-           wide_align(32 * nss) + wide_align(nss) + wide_align(8 * (size_t)cap_segs * kWideSubs) + wide_align(4 * ((size_t)cap_blks + 1));
+           wide_align(32 * nss) + wide_align(nss) + wide_align(4 * (size_t)cap_segs * kWideSubs) + wide_align(4 * ((size_t)cap_blks + 1));
 }
 
 // Carve the work area out of one 256-byte aligned allocation (host side).
@@ -130,7 +131,7 @@ inline WideArea wide_area_carve(uint8_t *base, uint32_t cap_jobs, uint32_t cap_s
     wa.seg_base = reinterpret_cast<unsigned long long *>(p); p += wide_align(8 * ((size_t)cap_segs + 1));
     wa.supermap = p; p += wide_align(32 * nss);
     wa.sseg_e = p; p += wide_align(nss);
-    wa.sub_entry = reinterpret_cast<uint2 *>(p); p += wide_align(8 * (size_t)cap_segs * kWideSubs);
+    wa.sub_entry = reinterpret_cast<uint32_t *>(p); p += wide_align(4 * (size_t)cap_segs * kWideSubs);
     wa.blk_sub0 = reinterpret_cast<uint32_t *>(p);
     wa.cap_jobs = cap_jobs; wa.cap_segs = cap_segs; wa.cap_blks = cap_blks;
     wa.threshold = 0; wa.force = 0; wa.status = nullptr; wa.st = nullptr; wa.lut = nullptr; wa.lut_channels = 1;
@@ -594,14 +595,15 @@ k_wide_fine(WideArea wa)
         const uint8_t *src = reinterpret_cast<const uint8_t *>(wjp->src);
         const uint32_t nblk = wjp->nblk, blk0 = wjp->blk0;
         const uint32_t e = wa.seg_e[seg];
-        uint2 *fine = wa.sub_entry + (size_t)seg * kWideSubs;
+        uint32_t *fine = wa.sub_entry + (size_t)seg * kWideSubs;
         const uint32_t end = min((lseg + 1u) * kWideSeg, slen);
         uint32_t sub = 0;                                                    // next sub-segment of this segment without a record
         if (e < 25u) {
-            uint32_t a = lseg * kWideSeg + e, o = (uint32_t)(wa.seg_base[seg] - wa.seg_base[wjp->seg0]);
+            const uint32_t o_seg = (uint32_t)(wa.seg_base[seg] - wa.seg_base[wjp->seg0]);
+            uint32_t a = lseg * kWideSeg + e, o = o_seg;
             while (a < end) {
                 const uint32_t my_sub = (a - lseg * kWideSeg) / kWideSub;
-                if (my_sub >= sub) { fine[my_sub] = make_uint2(o, a - (lseg * kWideSeg + my_sub * kWideSub)); sub = my_sub + 1u; }
+                if (my_sub >= sub) { fine[my_sub] = ((o - o_seg) << 5) | (a - (lseg * kWideSeg + my_sub * kWideSub)); sub = my_sub + 1u; }
                 uint32_t out;
                 a = wide_group_walk(src, a, slen, &out);
                 const uint32_t k = (o + kWideBlock - 1u) / kWideBlock;       // first block boundary at or after o
@@ -612,7 +614,7 @@ k_wide_fine(WideArea wa)
         }
         // sub-segments of the stream's end in which no group starts
         const uint32_t nsub_here = (end - lseg * kWideSeg + kWideSub - 1u) / kWideSub;
-        for (; sub < nsub_here; sub++) fine[sub] = make_uint2(0u, kNone);
+        for (; sub < nsub_here; sub++) fine[sub] = 31u;
     }
 }
 
@@ -684,11 +686,13 @@ k_wide_blocks(WideArea wa)
         //      only the first byte is (its offset is parked in the two unused value bytes), the body is filled in below.
         const uint32_t floor_idx = k == 0u ? kWideWin : 0u;                  // nothing exists before the output start
         const uint32_t sub0 = wa.blk_sub0[b], sub1 = k + 1u < wj.nblk ? wa.blk_sub0[b + 1] : (slen ? (slen - 1u) / kWideSub : 0u);
-        const uint2 *fine = wa.sub_entry + (size_t)wj.seg0 * kWideSubs;
+        const uint32_t *fine = wa.sub_entry + (size_t)wj.seg0 * kWideSubs;
+        const unsigned long long value_base = wa.seg_base[wj.seg0];
         for (uint32_t sb = sub0 + tid; sb <= sub1; sb += kWideThreads) {
-            const uint2 ent = fine[sb];
-            if (ent.y == kNone) continue;
-            uint32_t a = sb * kWideSub + ent.y, o = ent.x;
+            const uint32_t ent = fine[sb];
+            if ((ent & 31u) == 31u) continue;
+            uint32_t a = sb * kWideSub + (ent & 31u);
+            uint32_t o = (uint32_t)(wa.seg_base[wj.seg0 + sb / kWideSubs] - value_base) + (ent >> 5);
             const uint32_t send = min((sb + 1u) * kWideSub, slen);
             while (a < send && o < o1) {
                 const uint32_t ctrl = __ldg(src + a);
