@@ -210,3 +210,58 @@ def test_packed_buffers_bf16_and_uint8_outputs_take_the_wide_path(torch_cuda, co
     assert st == 0 and wide_count() - before == 3
     got = part.ind.view(torch.float32).cpu().numpy()
     assert got.shape == want_f.shape and got.tobytes() == want_f.tobytes()
+
+
+def test_wide_periodic_streams(torch_cuda, coracle, wide_threshold):
+    """Streams whose bytes repeat with the period of a control group: a parse that starts out of phase stays out
+    of phase for ever, so guessing group boundaries would fail; the entry maps must still find them."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    wide_threshold(1024)
+    raws = [np.zeros(3_000_000, dtype=np.uint8),                                    # ctrl FF + 8 x (0F 01 FF): period 25
+            np.full(700_001, 0xFF, dtype=np.uint8),
+            np.resize(np.array([1, 2, 3], dtype=np.uint8), 1_000_003),              # offset-3 matches of maximum length
+            np.resize(np.arange(256, dtype=np.uint8), 900_000),
+            np.resize(np.frombuffer(b"\x00\x00\x80\x3f" + b"\x00" * 60, dtype=np.uint8), 1_500_000)]
+    datums = [synth.pglz_varlena(r, "lz") for r in raws] + [synth.pglz_varlena(raws[0][:200_000], "literal")]
+    raws.append(raws[0][:200_000])
+    before = wide_count()
+    out, codes = segment.pglz_decompress_batch(datums)
+    assert wide_count() - before == len(datums) and codes == [0] * len(datums)
+    for got, want, d in zip(out, raws, datums):
+        assert got == want.tobytes()
+        assert bytes(coracle.pglz_decompress(d)) == want.tobytes()
+
+
+def test_corrupt_packed_buffer_in_a_segment_is_refused_like_the_oracle(torch_cuda, coracle, wide_threshold):
+    """Damage the stream of one large external value inside the TOAST file: same status and same first-error position
+    as with the wide decoder switched off, and the oracle refuses too."""
+    import da_oracle
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    ind, dep = synth.imagenet_rows(3, seed=21, shape=(112, 112, 3), classes=1000, images_per_row=12)     # 1.8 MB per value
+    seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="inline_pglz")
+    rng = np.random.default_rng(1)
+    for trial in range(6):
+        toast = seg.toast.copy()
+        # a payload byte somewhere in the middle pages (page header 24 B + line pointers, tuples at the end of the page)
+        page = int(rng.integers(1, toast.size // 32768 - 1))
+        pos = page * 32768 + int(rng.integers(2000, 30000))
+        toast[pos] ^= int(rng.integers(1, 256))
+        try:
+            want = coracle.decode(seg.heap, toast)
+        except da_oracle.OracleError as e:
+            want = e.code
+        results = []
+        for thr in (1 << 20, 0):
+            wide_threshold(thr, force=0)
+            before = wide_count()
+            st, part = segment.decode_pages(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(toast).cuda())
+            results.append((st, int(part.summary.err_where), int(part.summary.err_stage)))
+            if thr:
+                assert wide_count() - before == 3
+            if st == 0:
+                assert part.ind.cpu().numpy().tobytes() == want["out_ind"].tobytes()
+        assert results[0] == results[1], (trial, results)
+        assert (results[0][0] == 0) == isinstance(want, dict), (trial, results, want if not isinstance(want, dict) else 0)
+        if not isinstance(want, dict):
+            assert results[0][0] == want
