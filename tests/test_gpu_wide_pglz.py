@@ -265,3 +265,51 @@ def test_corrupt_packed_buffer_in_a_segment_is_refused_like_the_oracle(torch_cud
         assert (results[0][0] == 0) == isinstance(want, dict), (trial, results, want if not isinstance(want, dict) else 0)
         if not isinstance(want, dict):
             assert results[0][0] == want
+
+
+def test_more_wide_candidates_than_the_work_area_holds(torch_cuda, coracle, wide_threshold):
+    """A handle's work area lists at most 1024 values; the rest stay with the warp decoder and the result is the same."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    wide_threshold(1024, force=1)
+    rng = np.random.default_rng(12)
+    n = 1300
+    ind = [np.resize(rng.standard_normal(int(rng.integers(20, 60))).astype(np.float32), (1, int(rng.integers(300, 900)))) for _ in range(n)]
+    dep = [rng.integers(0, 2, size=(1, 8)).astype(np.int16) for _ in range(n)]
+    seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="inline_pglz")
+    want = coracle.decode(seg.heap, seg.toast)
+    before = wide_count()
+    st, part = segment.decode_pages(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(seg.toast).cuda())
+    assert st == 0
+    assert part.summary.n_wide_values == n and wide_count() - before == 1024
+    assert part.ind.cpu().numpy().tobytes() == want["out_ind"].tobytes()
+    assert part.dep.cpu().numpy().tobytes() == want["out_dep"].tobytes()
+
+
+def test_wide_streams_ending_on_segment_and_block_boundaries(torch_cuda, coracle, wide_threshold):
+    """Literal-only streams of 4096 m bytes are 4608 m = 9 * 512 m bytes long: the stream ends exactly on a source
+    segment boundary; 57344-byte multiples end exactly on an output block boundary."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    wide_threshold(1024)
+    rng = np.random.default_rng(8)
+    sizes = [4096, 4096 * 2, 4096 * 13, 4096 * 14, 4096 * 15, 4096 * 28, 4096 * 29, 57344 * 3]
+    raws = [rng.integers(0, 256, n, dtype=np.uint8) for n in sizes]
+    datums = [synth.pglz_varlena(r, "literal") for r in raws]
+    for d, n in zip(datums, sizes):
+        assert (len(d) - 8) % 512 == 0, n
+    raws += [structured_bytes(rng, n) for n in (57344, 57344 * 2, 57344 * 4)]
+    datums += [synth.pglz_varlena(r, "lz") for r in raws[len(sizes):]]
+    out, codes = segment.pglz_decompress_batch(datums)
+    assert codes == [0] * len(datums)
+    for got, want in zip(out, raws):
+        assert got == want.tobytes()
+    # one byte short / one byte long at those boundaries is refused
+    bad = []
+    for d in datums[:4]:
+        t = bytearray(d[:-1]); t[0:4] = struct.pack(">I", 0x40000000 | len(t)); bad.append(bytes(t))
+        t = bytearray(d + b"\x00"); t[0:4] = struct.pack(">I", 0x40000000 | len(t)); bad.append(bytes(t))
+    out, codes = segment.pglz_decompress_batch(bad)
+    for d, c in zip(bad, codes):
+        with pytest.raises(Exception):
+            coracle.pglz_decompress(d)
+        assert c == 11
