@@ -8,7 +8,7 @@ import ctypes
 import os
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "libcds_da.so")
+LIB_PATH = os.environ.get("CDS_DA_LIB") or os.path.join(PKG_DIR, "libcds_da.so")     # (override: A/B runs of two builds)
 
 (CDS_OK, CDS_ERR_PARTIAL_PAGE, CDS_ERR_ITEMID_ALIGN, CDS_ERR_TOAST_SPECIAL, CDS_ERR_TUPLE, CDS_ERR_RAWSIZE,
  CDS_ERR_CHUNK_COUNT, CDS_ERR_CHUNK_EXTENDED, CDS_ERR_MAX_CHUNK, CDS_ERR_CHUNK_SIZE, CDS_ERR_FINAL_SIZE,

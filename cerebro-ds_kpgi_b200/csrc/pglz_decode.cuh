@@ -247,29 +247,28 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
                 const uint32_t klen = pk >> 12, kmoff = __shfl_sync(0xffffffffu, moff, k);
                 const uint32_t a0 = at + shift;                              // ring position of the first byte written
                 if (kmoff == 1u) {
-                    // run of one byte value (zero runs of sparse features): aligned 16-byte stores, at most 17 of them
+                    // run of one byte value (zero runs of sparse features): aligned 16-byte stores, at most 18 of them.
+                    // The last one may run up to 15 bytes past the item: those ring bytes belong to output that is not
+                    // produced yet (they alias history 8 KB back, beyond the 4095-byte window and already flushed).
                     const uint32_t b = ring[(a0 - 1u) & M], v = b * 0x01010101u;
                     const uint32_t head = min(klen, (16u - (a0 & 15u)) & 15u);
                     if (lane < head) ring[(a0 + lane) & M] = (uint8_t)b;
-                    const uint32_t nq = (klen - head) >> 4, q0 = a0 + head;
+                    const uint32_t nq = (klen - head + 15u) >> 4, q0 = a0 + head;
                     if (lane < nq) *reinterpret_cast<uint4 *>(ring + ((q0 + 16u * lane) & M)) = make_uint4(v, v, v, v);
-                    const uint32_t t0 = head + 16u * nq;
-                    if (lane < klen - t0) ring[(a0 + t0 + lane) & M] = (uint8_t)b;
                 } else if (kmoff >= klen && klen >= 8u) {
                     // source and destination do not overlap: aligned 32-bit stores, the source re-aligned with a funnel
                     // shift of two aligned words (bytes read beyond the source are shifted out)
                     const uint32_t s0 = a0 - kmoff;
                     const uint32_t head = (4u - (a0 & 3u)) & 3u;                  // < 8 <= klen
                     if (lane < head) ring[(a0 + lane) & M] = ring[(s0 + lane) & M];
-                    const uint32_t nw = (klen - head) >> 2, w0 = a0 + head, sw = s0 + head, r8 = (sw & 3u) * 8u;
+                    // (the last word may run up to 3 bytes past the item, as above)
+                    const uint32_t nw = (klen - head + 3u) >> 2, w0 = a0 + head, sw = s0 + head, r8 = (sw & 3u) * 8u;
                     for (uint32_t i = lane; i < nw; i += 32) {
                         const uint32_t sa = (sw + 4u * i) & ~3u;
                         const uint32_t lo = *reinterpret_cast<const uint32_t *>(ring + (sa & M));
                         const uint32_t hi = *reinterpret_cast<const uint32_t *>(ring + ((sa + 4u) & M));
                         *reinterpret_cast<uint32_t *>(ring + ((w0 + 4u * i) & M)) = __funnelshift_r(lo, hi, r8);
                     }
-                    const uint32_t t0 = head + 4u * nw;
-                    if (lane < klen - t0) ring[(a0 + t0 + lane) & M] = ring[(s0 + t0 + lane) & M];
                 } else if (kmoff >= klen) {
                     if (lane < klen) ring[(a0 + lane) & M] = ring[(a0 - kmoff + lane) & M];
                 } else {
