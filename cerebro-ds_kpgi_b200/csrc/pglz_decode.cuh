@@ -238,15 +238,24 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
     } else {
         // ---- long matches: item after item.  (Here total <= 2184 or <= 2048, so offsets fit 12 bits.)
         const uint32_t mbits = __ballot_sync(0xffffffffu, is_match);
+        const uint32_t runbits = __ballot_sync(0xffffffffu, is_match && moff == 1u);
         const uint32_t packed = my_o | (len << 12);
         constexpr uint32_t M = kRing - 1;
         for (uint32_t k = 0; k < nitems; k++) {
             const uint32_t pk = __shfl_sync(0xffffffffu, packed, k);
             const uint32_t at = dp + (pk & 0xFFFu);
             if ((mbits >> k) & 1u) {
-                const uint32_t klen = pk >> 12, kmoff = __shfl_sync(0xffffffffu, moff, k);
+                uint32_t klen = pk >> 12;
                 const uint32_t a0 = at + shift;                              // ring position of the first byte written
-                if (kmoff == 1u) {
+                if ((runbits >> k) & 1u) {
+                    // consecutive runs repeat the same byte: one fill for all of them
+                    const uint32_t more = k < 31u ? (uint32_t)__ffs((int)~(runbits >> (k + 1u))) - 1u : 0u;   // run items right after item k
+                    if (more) {
+                        const uint32_t last = k + more;                      // < nitems: runbits only has item lanes
+                        const uint32_t pl = __shfl_sync(0xffffffffu, packed, last);
+                        klen = (pl & 0xFFFu) + (pl >> 12) - (pk & 0xFFFu);
+                        k = last;
+                    }
                     // run of one byte value (zero runs of sparse features): aligned 16-byte stores, at most 18 of them.
                     // The last one may run up to 15 bytes past the item: those ring bytes belong to output that is not
                     // produced yet (they alias history 8 KB back, beyond the 4095-byte window and already flushed).
@@ -254,8 +263,13 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
                     const uint32_t head = min(klen, (16u - (a0 & 15u)) & 15u);
                     if (lane < head) ring[(a0 + lane) & M] = (uint8_t)b;
                     const uint32_t nq = (klen - head + 15u) >> 4, q0 = a0 + head;
-                    if (lane < nq) *reinterpret_cast<uint4 *>(ring + ((q0 + 16u * lane) & M)) = make_uint4(v, v, v, v);
-                } else if (kmoff >= klen && klen >= 8u) {
+                    for (uint32_t i = lane; i < nq; i += 32)
+                        *reinterpret_cast<uint4 *>(ring + ((q0 + 16u * i) & M)) = make_uint4(v, v, v, v);
+                    __syncwarp();
+                    continue;
+                }
+                const uint32_t kmoff = __shfl_sync(0xffffffffu, moff, k);
+                if (kmoff >= klen && klen >= 8u) {
                     // source and destination do not overlap: aligned 32-bit stores, the source re-aligned with a funnel
                     // shift of two aligned words (bytes read beyond the source are shifted out)
                     const uint32_t s0 = a0 - kmoff;
