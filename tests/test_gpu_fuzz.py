@@ -63,12 +63,28 @@ def test_pglz_fuzz_structured_streams(torch_cuda, coracle):
         assert bytes(coracle.pglz_decompress(d)) == want
 
 
-def test_segment_layout_fuzz(torch_cuda, coracle):
-    from cerebro_ds_kpgi_b200 import segment, synth
+@pytest.mark.parametrize("wide", [False, True])
+def test_segment_layout_fuzz(torch_cuda, coracle, wide):
+    """wide=True: every compressed value of at least 1024 bytes goes through the intra-value parallel decoder."""
+    from cerebro_ds_kpgi_b200 import _lib, segment, synth
     torch = torch_cuda
     rng = np.random.default_rng(777)
     sizes = [1, 2, 3, 2034, 2035, 2036, 4069, 4070, 4071, 6105, 8140 // 4 * 3]      # float counts around the 8140-byte chunk edge
     ds = segment.DeviceSegment(64, 2048)
+    L = _lib.load()
+    if wide:
+        _lib.check(L.cds_set_wide_pglz_threshold(1024, 1))
+        _lib.check(L.cds_set_wide_pglz(ds._h, 1))
+    taken0 = int(L.cds_wide_decoded_count())
+    try:
+        _segment_layout_fuzz_body(torch, coracle, segment, synth, rng, sizes, ds)
+    finally:
+        _lib.check(L.cds_set_wide_pglz_threshold(1 << 20, 0))
+    assert (int(L.cds_wide_decoded_count()) - taken0 > 100) == wide
+    ds.close()
+
+
+def _segment_layout_fuzz_body(torch, coracle, segment, synth, rng, sizes, ds):
     for trial in range(40):
         n_rows = int(rng.integers(1, 50))
         ind, dep, st_i, st_d = [], [], [], []
@@ -104,7 +120,6 @@ def test_segment_layout_fuzz(torch_cuda, coracle):
         assert gi[:want["out_ind"].size].tobytes() == want["out_ind"].tobytes(), trial
         assert gd[:want["out_dep"].size].tobytes() == want["out_dep"].tobytes(), trial
         assert (gi[want["out_ind"].size:] == 0x5A).all() and (gd[want["out_dep"].size:] == 0x5A).all(), trial   # nothing past the end
-    ds.close()
 
 
 def test_corruption_fuzz_never_disagrees_silently(torch_cuda, coracle):
