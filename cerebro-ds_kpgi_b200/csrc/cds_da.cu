@@ -51,7 +51,7 @@ struct cds_segment {
     int ind_format = 0;             // cds_set_output_format: 0 stored bytes, 1 f32 -> bf16, 2 u8 -> f32 through the table
     float *d_lut = nullptr;         // cds_set_normalize_lut: [channels][256]
     int wide_mode = 2;              // cds_set_wide_pglz: 0 never, 1 always, 2 when the last summary counted large values
-    bool wide_hint = false;
+    bool wide_hint = true;          // until a summary says otherwise: a handle's first decode launches the wide kernels
     bool wide_launched = false;     // this decode ran the wide decoder: cds_finish reads its counters
     uint8_t *wide_mem = nullptr;    // work area of the intra-value parallel pglz decoder (pglz_wide.cuh)
     WideArea wide;

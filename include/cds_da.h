@@ -198,7 +198,7 @@ int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model);
  * (default): launch it (14 small kernels that find no work when nothing qualifies) when the plan counted large
  * values.  In the step-by-step flow that is this decode's own plan (cds_plan + cds_finish before
  * cds_materialize); the one-call entry points have no host sync before the decode and go by the last summary
- * read on the handle. */
+ * read on the handle (a handle that has not produced a summary yet launches them). */
 int cds_set_wide_pglz(cds_segment *seg, int mode);
 /* Measurement hook: values decoded by the wide decoder so far in this process (counted when a decode's
  * summary is read / a batch call returns). */
