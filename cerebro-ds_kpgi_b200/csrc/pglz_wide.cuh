@@ -10,27 +10,30 @@
 //  A. Where do the control groups start?  A group is 1 control byte + 8 items of 1..3 bytes, so where a
 //     group ends depends on its bytes, and where the next one starts depends on that.  The stream is cut
 //     into 512-byte source segments.  The first group start at or after a segment boundary lies within
-//     25 bytes of it, so there are only 25 possible entries into a segment.  k_wide_maps evaluates
-//     "group length / output bytes if a group started here" for EVERY source position (shared memory,
-//     one thread per position), then 25 lanes of a warp chase the 25 candidate chains through the
-//     segment: entry -> (exit offset into the next segment, output bytes).  These 25-entry maps compose
+//     25 bytes of it, so there are only 25 possible entries into a segment.  k_wide_maps computes the
+//     group length at EVERY source position, from registers only (a length depends on the control byte
+//     and on one bit per following byte), then 25 lanes of a warp chase the 25 candidate chains through
+//     the segment: entry -> exit offset into the next segment.  These 25-entry maps compose
 //     associatively: k_wide_super folds 256 of them, one warp walks the folded maps of a value
-//     (k_wide_chain: also the stream's validity: it must end exactly at srcend having produced exactly
-//     rawsize bytes), k_wide_entries unfolds them into the true entry and output position of every segment.
+//     (k_wide_chain: the chain must end exactly at srcend), k_wide_entries unfolds them into the true
+//     entry of every segment.  k_wide_outs / k_wide_scan / k_wide_check then count the output bytes of
+//     each segment's groups, prefix-sum them (the total must be rawsize), and k_wide_fine records, per
+//     32-byte sub-segment, where its first group starts and which output byte that group produces.
 //
 //  B. What does a match copy?  Output is cut into blocks of 57344 bytes.  A block is rebuilt in shared
 //     memory as a forest: every output byte points at the byte it copies (a literal points at itself;
 //     byte k of a match points at start - off + (k mod off), i.e. always before its own item), offsets
 //     are <= 4095 so pointers leave the block only into the last 4095 bytes of the previous block.
-//     Pointer jumping (ptr[i] = ptr[ptr[i]]) resolves every byte to a literal of the block or to one of
-//     those 4095 previous bytes in O(log depth) rounds.  Pass 1 (k_wide_blocks<1>) does this with the
-//     previous tail unknown and publishes, for the block's own last 4095 bytes, "value" or "index into
-//     the previous tail"; k_wide_tails runs down each value applying these maps (4095 gathers per block
-//     from shared memory, the only serial step left); pass 3 (k_wide_blocks<3>) repeats the block
+//     Pointer jumping (ptr[i] = ptr[ptr[ptr[i]]], in place) resolves every byte to a literal of the block
+//     or to one of those 4095 previous bytes in O(log depth) rounds.  Pass 1 (k_wide_blocks<1>) does this
+//     with the previous tail unknown and publishes, for the block's own last 4095 bytes, "value" or
+//     "index into the previous tail"; k_wide_tails<0,1,2> turns these maps into bytes (folded over
+//     groups of 32 blocks, so the serial part is short); pass 3 (k_wide_blocks<3>) repeats the block
 //     with the previous tail known and writes the output, 128 contiguous bytes per warp store.
 //
-// Work memory: 8 bytes per source segment.  The segment maps, the tail maps and the resolved tails live
-// inside the value's own (not yet written) output region and are overwritten by pass 3.
+// Work memory: 4 bytes per 32 bytes of source + 13 bytes per 512-byte segment.  The segment maps, the tail
+// maps and the resolved tails live inside the value's own (not yet written) output region and are
+// overwritten by pass 3, which therefore runs from the last block to the first behind a flag per block.
 #pragma once
 #include <cuda_bf16.h>
 
@@ -579,7 +582,7 @@ k_wide_check(WideArea wa)
 }
 
 // One thread per segment walks its chain of groups again, now knowing the output position it starts at, and
-// records, for each 64-byte sub-segment, where its first group starts and which output byte that group produces
+// records, for each 32-byte sub-segment, where its first group starts and which output byte that group produces
 // first; also the sub-segment every output block starts in.  Sub-segments are the units the block kernels hand
 // to their threads.
 __global__ void __launch_bounds__(256)
@@ -681,7 +684,7 @@ k_wide_blocks(WideArea wa)
             *reinterpret_cast<volatile uint32_t *>(&wa.blk_flag[b]) = 1u;
         }
 
-        // ---- items: one thread per 64-byte source sub-segment that feeds this block.  Literals and every byte of a
+        // ---- items: one thread per 32-byte source sub-segment that feeds this block.  Literals and every byte of a
         //      match of up to kWideShort bytes get their pointer here and are marked in the bitmap; of a longer match
         //      only the first byte is (its offset is parked in the two unused value bytes), the body is filled in below.
         const uint32_t floor_idx = k == 0u ? kWideWin : 0u;                  // nothing exists before the output start
