@@ -246,6 +246,13 @@ class PythonPortPool:
             assert got == self.buffers, (got, self.buffers)
         return time.perf_counter() - t0
 
+    def one_process(self):
+        """Seconds one worker alone needs for its own sub-segment (the reference is a single process per partition)."""
+        t0 = time.perf_counter()
+        got = sum(self.pool.map(_ref_worker, range(1), chunksize=1))
+        assert got * self.procs == self.buffers
+        return time.perf_counter() - t0
+
     def close(self):
         self.pool.close()
         self.pool.join()
@@ -468,10 +475,12 @@ def run_ours(args):
             pool = PythonPortPool(args.workload, args.toast_mib, threads)
             pool.step(1)                                         # warm the workers up
             dt = min(pool.step(1), pool.step(1))
+            dt_one = min(pool.one_process(), pool.one_process())
             pool.close()
             c_rate, c_dt, c_threads = cpu_decode_rate(seg, meta, reps=3)
             cpu = {"value": pool.rows / dt, "unit": "rows/s", "cores": threads, "kind": "port",
                    "sample": pool.describe(1) + " (best of 2, %.0f ms)" % (dt * 1000.0),
+                   "one_process_rows_per_s": (pool.rows / threads) / dt_one,
                    "c_port_openmp_rows_per_s": c_rate,
                    "c_port_note": "oracle/da_oracle.c, whole path in C + OpenMP (%d threads, %.0f ms per segment): much faster "
                                   "than the reference's Python reader; kept beside it for transparency" % (c_threads, c_dt * 1000.0)}
@@ -488,6 +497,7 @@ def run_ours(args):
                        "algorithmic_bytes_per_row": step_bytes / meta["rows"]},
             "roofline": {"bound": "hbm", "kernel": "k_toast_gather", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": (achieved / peak) if achieved else None, "peak_source": peak_src,
+                         "frac_of_nominal_8_tb_s": (achieved / 8000.0) if achieved else None,
                          "algorithmic_bytes_per_launch": gather_bytes, "launch_ms": gather_ms_max,
                          "share_of_step": gather_ms_max / dev_ms_max if dev_ms_max else None,
                          "traffic": (traffic or {}).get("dram_bytes_per_launch")},
