@@ -137,6 +137,37 @@ def GET_RAWSIZE_FROM_COMPRESSED(bytea):
     return struct.unpack('<I', bytes(bytea[4:8]))[0]
 
 
+def SET_VARSIZE(bytea, header):            # ppr:60-61
+    bytea[:4] = header
+
+
+def att_align_nominal(off):                # ppr:64-69 (int alignment)
+    return TYPEALIGN(4, off)
+
+
+def VARSIZE_1B(bytea):                     # ppr:84-86
+    return get_1b_header(bytea) & 0x7F
+
+
+def acc(bytea, i):                         # ppr:188-189
+    return bytea[i:i + 1]
+
+
+def expand_input_dims(input_data):         # ppr:159-162
+    return np.expand_dims(np.array(input_data, dtype=np.float32), axis=0)
+
+
+def read_page_at(f, pos):                  # ppr:358-361
+    f.seek(pos)
+    return f.read(BLOCK_SIZE)
+
+
+# The per-page parse helpers of the reference's CPU loop (deserialize_page_header, deserialize_item,
+# deserialize_item_header, extract_tuple, desirialize_tupdata; ppr:253-351) have no counterpart here: that
+# parse runs inside k_page_index / k_heap_rows / k_toast_walk, and table_page_read / generator_page return
+# its results in the reference's own record layout.
+
+
 def get_num_chunks(ressize):
     return ((ressize - 1) // TOAST_MAX_CHUNK_SIZE) + 1
 
