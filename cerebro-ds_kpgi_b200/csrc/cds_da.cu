@@ -465,13 +465,17 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
     if (s->n_toast_pages) {
         uint32_t grid = (uint32_t)(s->n_toast_pages < (uint64_t)s->num_sms ? s->n_toast_pages : (uint64_t)s->num_sms);
         const bool timed = s->ev && s->ev_used < s->ev_cap;
-        if (timed) CU(cudaEventRecord(s->ev[2 * s->ev_used], st));
+        // (inside a stream capture the timing events become event-record nodes of the graph)
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        if (timed && cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+        const unsigned ev_flags = cap == cudaStreamCaptureStatusActive ? cudaEventRecordExternal : cudaEventRecordDefault;
+        if (timed) CU(cudaEventRecordWithFlags(s->ev[2 * s->ev_used], st, ev_flags));
         k_toast_gather<<<grid, kGatherThreads, kGatherSmemBytes, st>>>(s->d_toast, (uint32_t)s->n_toast_pages,
                                                                        s->toast_base, s->ops, s->state,
                                                                        s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels);
         CU(cudaGetLastError());
         LAUNCHED(1);
-        if (timed) { CU(cudaEventRecord(s->ev[2 * s->ev_used + 1], st)); s->ev_used++; }
+        if (timed) { CU(cudaEventRecordWithFlags(s->ev[2 * s->ev_used + 1], st, ev_flags)); s->ev_used++; }
     }
     if (s->wide_mem && g_wide_threshold && (s->wide_mode == 1 || (s->wide_mode == 2 && s->wide_hint))) {
         WideArea wa = s->wide;
