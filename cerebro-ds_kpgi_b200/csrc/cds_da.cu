@@ -556,19 +556,32 @@ extern "C" int cds_decode_device(cds_segment *s, const void *d_heap, uint64_t n_
         if ((rc = reset_state(s, st))) return rc;
         s->d_heap = static_cast<const uint8_t *>(d_heap); s->n_heap_pages = n_heap_pages;
         s->d_toast = static_cast<const uint8_t *>(d_toast); s->n_toast_pages = n_toast_pages;
-        const uint32_t gx = scan_grid(s, n_heap_pages > n_toast_pages ? n_heap_pages : n_toast_pages, 4);
-        k_page_index2<<<dim3(gx, 2), kScanThreads, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, (uint32_t)s->cap_rows,
-                                                           s->ws[0], s->d_toast, (uint32_t)n_toast_pages, s->toast_base,
-                                                           (uint32_t)s->cap_chunks, s->ws[1], s->state);
-        CU(cudaGetLastError());
-        LAUNCHED(1);
-        if (n_heap_pages) {
-            uint64_t want = n_heap_pages * kHeapSub, cap = (uint64_t)s->num_sms * 16u;
-            k_heap_rows<<<(uint32_t)(want < cap ? want : cap), 64, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, s->rows,
-                                                                          s->state, s->htab, s->hmask, s->vfirst, s->vcount,
-                                                                          s->vbytes, s->vseq0);
+        uint32_t gx = scan_grid(s, n_heap_pages > n_toast_pages ? n_heap_pages : n_toast_pages, 4);
+        if (n_heap_pages && n_heap_pages <= kFrontMaxHeapPages) {
+            // page indexes and the heap row parse in one launch (three independent planes)
+            const uint64_t want = (n_heap_pages * kHeapSub + 3) / 4, cap = (uint64_t)s->num_sms * 4u;
+            const uint32_t gr = (uint32_t)(want < cap ? want : cap);
+            if (gr > gx) gx = gr;
+            k_front<<<dim3(gx, 3), kScanThreads, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, (uint32_t)s->cap_rows, s->ws[0],
+                                                         s->d_toast, (uint32_t)n_toast_pages, s->toast_base, (uint32_t)s->cap_chunks,
+                                                         s->ws[1], s->state, s->rows, s->htab, s->hmask, s->vfirst, s->vcount,
+                                                         s->vbytes, s->vseq0);
             CU(cudaGetLastError());
             LAUNCHED(1);
+        } else {
+            k_page_index2<<<dim3(gx, 2), kScanThreads, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, (uint32_t)s->cap_rows,
+                                                               s->ws[0], s->d_toast, (uint32_t)n_toast_pages, s->toast_base,
+                                                               (uint32_t)s->cap_chunks, s->ws[1], s->state);
+            CU(cudaGetLastError());
+            LAUNCHED(1);
+            if (n_heap_pages) {
+                uint64_t want = n_heap_pages * kHeapSub, cap = (uint64_t)s->num_sms * 16u;
+                k_heap_rows<<<(uint32_t)(want < cap ? want : cap), 64, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, s->rows,
+                                                                              s->state, s->htab, s->hmask, s->vfirst, s->vcount,
+                                                                              s->vbytes, s->vseq0);
+                CU(cudaGetLastError());
+                LAUNCHED(1);
+            }
         }
         if (n_toast_pages) {
             k_toast_walk<<<(uint32_t)((n_toast_pages + 127) / 128), 128, 0, st>>>(

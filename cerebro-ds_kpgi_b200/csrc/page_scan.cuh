@@ -85,17 +85,17 @@ __device__ inline void index_row_values(const uint32_t *row, uint32_t r, unsigne
 // kHeapSub blocks of 64 threads per heap page, one thread per ItemId: parse the MADlib packed row and
 // write its 16-word descriptor in table order.  (A page holds at most 430 such tuples.)
 constexpr uint32_t kHeapSub = 7;
-__global__ void __launch_bounds__(64)
-k_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *__restrict__ base,
-            uint32_t *__restrict__ rows, DevState *st, unsigned long long *htab, uint32_t hmask,
-            uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0)
+// `base` may live in global or in shared memory.  The work is cut into groups of 64 threads: group `vb` of `nvb`, thread `vt`.
+__device__ __forceinline__ void d_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *base,
+                                            uint32_t *__restrict__ rows, DevState *st, unsigned long long *htab, uint32_t hmask,
+                                            uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0,
+                                            uint32_t vb, uint32_t nvb, uint32_t vt)
 {
-    if (st->flags & kFlagRowOverflow) return;
-    for (uint32_t w = blockIdx.x; w < n_pages * kHeapSub; w += gridDim.x) {
+    for (uint32_t w = vb; w < n_pages * kHeapSub; w += nvb) {
         const uint32_t p = w / kHeapSub, sub = w - p * kHeapSub;
         const uint8_t *pg = heap + (size_t)p * kPage;
         const uint32_t r0 = base[p], n = base[p + 1] - r0;
-        for (uint32_t i = sub * 64u + threadIdx.x; i < n; i += kHeapSub * 64u) {
+        for (uint32_t i = sub * 64u + vt; i < n; i += kHeapSub * 64u) {
             uint32_t *row = rows + (size_t)(r0 + i) * kRowWords;
             uint32_t iid = *reinterpret_cast<const uint32_t *>(pg + kPageHdr + 4u * i);
             uint32_t lp_off = iid & 0x7FFFu, lp_len = iid >> 17;            // ppr:287-300
@@ -128,6 +128,65 @@ k_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *
             index_row_values(row, r0 + i, htab, hmask, vfirst, vcount, vbytes, vseq0);
         }
     }
+}
+
+__global__ void __launch_bounds__(64)
+k_heap_rows(const uint8_t *__restrict__ heap, uint32_t n_pages, const uint32_t *__restrict__ base,
+            uint32_t *__restrict__ rows, DevState *st, unsigned long long *htab, uint32_t hmask,
+            uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0)
+{
+    if (st->flags & kFlagRowOverflow) return;
+    d_heap_rows(heap, n_pages, base, rows, st, htab, hmask, vfirst, vcount, vbytes, vseq0, blockIdx.x, gridDim.x, threadIdx.x);
+}
+
+// One launch for the front of the one-call decode: plane 0 indexes the heap pages, plane 1 the TOAST pages, and
+// plane 2 parses the heap rows at the same time.  The row parse needs the heap's item-count prefix; a heap of up to
+// kFrontMaxHeapPages pages (a 1 GiB segment of one-image rows has 32) is small enough for every block of plane 2 to
+// compute that prefix itself in shared memory, which makes the three planes independent.
+constexpr uint32_t kFrontMaxHeapPages = 1020;                     // 4 pages per thread, and one more prefix entry than pages
+__global__ void __launch_bounds__(kScanThreads)
+k_front(const uint8_t *__restrict__ heap, uint32_t n_heap, uint32_t *__restrict__ heap_base, uint32_t cap_rows, ScanWs ws_h,
+        const uint8_t *__restrict__ toast, uint32_t n_toast, uint32_t *__restrict__ toast_base, uint32_t cap_chunks, ScanWs ws_t,
+        DevState *st, uint32_t *__restrict__ rows, unsigned long long *htab, uint32_t hmask,
+        uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0)
+{
+    if (blockIdx.y == 0) { d_page_index(heap, n_heap, heap_base, st, 0, cap_rows, ws_h); return; }
+    if (blockIdx.y == 1) { d_page_index(toast, n_toast, toast_base, st, 1, cap_chunks, ws_t); return; }
+    if (blockIdx.x * 4u >= n_heap * kHeapSub) return;                        // no row work for this block
+    __shared__ uint32_t sh_base[kFrontMaxHeapPages + 4];
+    __shared__ uint32_t sh_warp[kScanThreads / 32];
+    // item counts with the rules of d_page_index (plane 0 reports the errors), 4 pages per thread
+    uint32_t c[4], tsum = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < 4; k++) {
+        const uint32_t p = threadIdx.x * 4u + k;
+        c[k] = 0;
+        if (p < n_heap) {
+            const uint32_t pd_lower = *reinterpret_cast<const uint32_t *>(heap + (size_t)p * kPage + 12) & 0xFFFFu;
+            if (pd_lower >= kPageHdr && !((pd_lower - kPageHdr) & 3u) && pd_lower <= kPage) c[k] = (pd_lower - kPageHdr) >> 2;
+        }
+        tsum += c[k];
+    }
+    const uint32_t winc = warp_inclusive_scan(tsum);
+    if ((threadIdx.x & 31) == 31) sh_warp[threadIdx.x >> 5] = winc;
+    __syncthreads();
+    uint32_t off = 0, total = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < kScanThreads / 32; w++) {
+        if (w < (threadIdx.x >> 5)) off += sh_warp[w];
+        total += sh_warp[w];
+    }
+    uint32_t run = off + winc - tsum;
+#pragma unroll
+    for (uint32_t k = 0; k < 4; k++) {
+        const uint32_t p = threadIdx.x * 4u + k;
+        if (p <= n_heap) sh_base[p] = run;
+        run += c[k];
+    }
+    __syncthreads();
+    if (total > cap_rows) return;                                            // plane 0 refuses the segment (CDS_ERR_CAPACITY)
+    d_heap_rows(heap, n_heap, sh_base, rows, st, htab, hmask, vfirst, vcount, vbytes, vseq0,
+                blockIdx.x * 4u + (threadIdx.x >> 6), gridDim.x * 4u, threadIdx.x & 63u);
 }
 
 // cds_set_rows path: rows arrive from the host; build the hash table from them.
