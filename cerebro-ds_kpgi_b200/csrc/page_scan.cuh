@@ -488,8 +488,8 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
         A.ops[g] = op;
     }
 
-    // pglz jobs are compacted: independent_var jobs (large) grow from slot 0 upward, dependent_var jobs (small)
-    // from the last slot downward; k_pglz_decode hands them out large first.
+    // pglz jobs are compacted: expensive jobs grow from slot 0 upward, cheap ones from the last slot downward;
+    // k_pglz_decode hands out the front list first.
     const uint32_t last_slot = 2u * n_rows - 1u;
     for (uint32_t v = tid; v < 2u * n_rows; v += nth) {
         PglzJob job;
@@ -543,7 +543,10 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
             }
         }
         if (job.slen != kNone) {
-            if (a == 0) A.jobs[atomicAdd(&st->n_jobs_front, 1u)] = job;
+            // front list = the expensive streams (really compressed, not tiny): handed out first, so that the cheap ones
+            // (literal-only streams copy 256 bytes per step; small labels) fill the tail of the launch
+            const bool expensive = (job.slen & ~kFlagBits) < job.rawsize && job.rawsize >= 4096u;
+            if (expensive) A.jobs[atomicAdd(&st->n_jobs_front, 1u)] = job;
             else A.jobs[last_slot - atomicAdd(&st->n_jobs_back, 1u)] = job;
         }
     }
