@@ -5,7 +5,7 @@ pinning gigabytes per call.
 reference).  Measured on a 1 GiB segment, page-locking a 1 GiB staging buffer (0.37 s + 0.09 s to free
 it) and the pageable device-to-host copy (0.22 s) dwarf the decode itself (a few ms).  So:
 
-* a small ring of page-locked slots is allocated once per process and reused by every call;
+* a small ring of page-locked slots (16 x 16 MiB) is allocated once per process and reused by every call;
 * file chunks are read into free slots by a few threads (`readinto` releases the GIL) while earlier
   slots are on their way to the GPU (`cudaMemcpyAsync` on a copy stream);
 * results come back the same way: device -> pinned slot -> the caller-owned numpy array, the last hop
@@ -22,9 +22,12 @@ import numpy as np
 from . import segment as _segment
 
 BLOCK_SIZE = 32768
-SLOT_BYTES = 64 << 20
-N_SLOTS = 4
-IO_THREADS = 4
+# ring geometry (environment overrides are for measurements: tools/dropin_bench.py)
+# 16 slots of 16 MiB and as many threads (up to the cores present) read a 1 GiB relation in 0.05 s; the first
+# version's 4 x 64 MiB with 4 threads needed 0.07-0.28 s (profiles/README.md)
+SLOT_BYTES = int(os.environ.get("CDS_IO_SLOT_MIB", "16")) << 20
+N_SLOTS = int(os.environ.get("CDS_IO_SLOTS", "16"))
+IO_THREADS = int(os.environ.get("CDS_IO_THREADS", str(max(1, min(16, os.cpu_count() or 4)))))
 
 _lock = threading.Lock()
 _rings = {}
