@@ -222,3 +222,33 @@ def test_repeated_chunk_seq_is_refused_not_overlaid(torch_cuda):
     struct.pack_into("<I", toast, off + 28, 1)                     # now chunk_seq 1 appears twice, 2 never
     status, _ = decode(torch_cuda, seg.heap, toast)
     assert status == _lib.CDS_ERR_CHUNK_SIZE
+
+
+def test_one_call_decode_with_a_heap_of_more_than_1020_pages(torch_cuda, coracle):
+    """The one-call decode parses heap rows in the same launch as the page indexes when the heap has at most 1020
+    pages (each block computes the heap's item prefix itself); larger heaps take the separate kernels."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    rng = np.random.default_rng(17)
+    n = 1150
+    ind = [rng.standard_normal((1, 40)).astype(np.float32) for _ in range(n)]
+    dep = [rng.integers(-300, 300, size=(1, 9000)).astype(np.int16) for _ in range(n)]           # ~20 KB inline: one row per page
+    seg = synth.build_segment(ind, dep, ind_storage="ext_raw", dep_storage="inline_literal")
+    assert seg.heap.size // 32768 > 1020
+    want = coracle.decode(seg.heap, seg.toast)
+    ds = segment.DeviceSegment(seg.heap.size // 32768, seg.toast.size // 32768)
+    out_i = torch.zeros(want["out_ind"].size + 16, dtype=torch.uint8, device="cuda")
+    out_d = torch.zeros(want["out_dep"].size + 16, dtype=torch.uint8, device="cuda")
+    s = ds.decode_device(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(seg.toast).cuda(), out_i, out_d)
+    assert s.status == 0 and s.n_rows == n
+    assert out_i[:want["out_ind"].size].cpu().numpy().tobytes() == want["out_ind"].tobytes()
+    assert out_d[:want["out_dep"].size].cpu().numpy().tobytes() == want["out_dep"].tobytes()
+    # and a heap of exactly the limit or just below goes through the fused launch with the same result
+    m = 1000
+    seg2 = synth.build_segment(ind[:m], dep[:m], ind_storage="ext_raw", dep_storage="inline_literal")
+    assert seg2.heap.size // 32768 <= 1020
+    want2 = coracle.decode(seg2.heap, seg2.toast)
+    s2 = ds.decode_device(torch.from_numpy(seg2.heap).cuda(), torch.from_numpy(seg2.toast).cuda(), out_i, out_d)
+    assert s2.status == 0 and s2.n_rows == m
+    assert out_d[:want2["out_dep"].size].cpu().numpy().tobytes() == want2["out_dep"].tobytes()
+    ds.close()
