@@ -144,6 +144,43 @@ def input_fn_device(file_path, overwrite_table_page_path=None, overwrite_toast_p
     return DevicePartition(images, onehot, labels, part.buffer_ids, rows_per)
 
 
+def prefetch_device(file_paths, dtype=None, u8_normalize=None):
+    """input_fn_device over several partitions (e.g. 'train' then 'valid', or the partitions a model hopper visits),
+    one ahead: while the caller works on partition i, the files of partition i+1 are read, copied to HBM and decoded
+    on a worker thread with its own CUDA stream.  Yields (file_path, DevicePartition) in order.  The optional
+    async variant of the per-partition call; the reference reads partitions one after another."""
+    import threading
+    import torch
+    paths = list(file_paths)
+    if not paths:
+        return
+    dev = torch.cuda.current_device()
+    results = {}
+
+    def work(i):
+        try:
+            with torch.cuda.device(dev), torch.cuda.stream(torch.cuda.Stream(device=dev)):
+                part = input_fn_device(paths[i], dtype=dtype, u8_normalize=u8_normalize)
+                torch.cuda.current_stream().synchronize()
+            results[i] = (part, None)
+        except BaseException as e:  # noqa  (re-raised in the caller's thread)
+            results[i] = (None, e)
+
+    th = threading.Thread(target=work, args=(0,))
+    th.start()
+    for i in range(len(paths)):
+        th.join()
+        part, err = results.pop(i)
+        if i + 1 < len(paths):
+            th = threading.Thread(target=work, args=(i + 1,))
+            th.start()
+        if err is not None:
+            if i + 1 < len(paths):
+                th.join()
+            raise err
+        yield paths[i], part
+
+
 def build_catalog(path, df_train, df_valid, df_shape):
     """Write sys_cat.dill as DirectAccessClient.generate_cats does (da.py:174-182), from frames the
     caller already has (columns of da.py:105-108 and da.py:117-125)."""

@@ -30,6 +30,7 @@ N_SLOTS = int(os.environ.get("CDS_IO_SLOTS", "16"))
 IO_THREADS = int(os.environ.get("CDS_IO_THREADS", str(max(1, min(16, os.cpu_count() or 4)))))
 
 _lock = threading.Lock()
+_use = threading.RLock()             # one transfer at a time through a device's ring (da.prefetch_device runs one in a thread)
 _rings = {}
 _pool = None
 
@@ -94,6 +95,12 @@ def _read_chunk(path, off, n, dst):
 def relation_to_device(filename, relation_files):
     """All whole pages of a relation as one uint8 CUDA tensor (16-byte aligned), plus the partial flag."""
     import torch
+    with _use:
+        return _relation_to_device(filename, relation_files)
+
+
+def _relation_to_device(filename, relation_files):
+    import torch
     ring = _ring()
     chunks, total, partial = _plan_files(filename, relation_files)
     out = torch.empty(max(total, 16), dtype=torch.uint8, device="cuda")
@@ -142,6 +149,12 @@ def device_to_numpy(t):
     if n <= (8 << 20):
         torch.from_numpy(host).copy_(t)
         return host
+    with _use:
+        return _device_to_numpy(t, host, n)
+
+
+def _device_to_numpy(t, host, n):
+    import torch
     ring = _ring()
     ex = _executor()
     cur = torch.cuda.current_stream()

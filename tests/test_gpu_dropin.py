@@ -148,3 +148,30 @@ def test_input_fn_device_and_consumers(tmp_path, torch_cuda, coracle):
     first = next(iter(g()))
     k0 = next(iter(out))
     assert first[0].tobytes() == out[k0]["independent_var"][0].tobytes()
+
+
+def test_prefetch_device_yields_the_same_partitions_in_order(tmp_path, torch_cuda, coracle):
+    from cerebro_ds_kpgi_b200 import da, synth
+    segs, dirs, shape_rows, train = [], [], [], []
+    for seg_id in range(3):
+        ind, dep = synth.imagenet_rows(6, seed=40 + seg_id, kind="normal", images_per_row=2)
+        seg = synth.build_segment(ind, dep, ind_storage=["ext_pglz", "ext_raw"] * 3, dep_storage="inline_pglz",
+                                  buffer_ids=list(range(100 * seg_id, 100 * seg_id + 6)), table_name="t_train")
+        d, _ = write_case(tmp_path, seg.heap, seg.toast, seg.expected, seg_id=seg_id)
+        segs.append(seg); dirs.append(d)
+        shape_rows += [{"__dist_key__": seg_id, "buffer_id": k, "independent_var_shape": list(v["independent_var"].shape),
+                        "dependent_var_shape": list(v["dependent_var"].shape), "table_name": "t_train"} for k, v in seg.expected.items()]
+        train.append(dict(gp_segment_id=seg_id, relname="t_train", relfilenode=50000, toast_relfilenode=50001))
+    cat = str(tmp_path / "sys_cat_all.dill")
+    synth.write_catalog(cat, {"train": train, "valid": []}, shape_rows)
+    da.SYS_CAT_PATH = cat
+    paths = [os.path.join(d, "train") for d in dirs]
+    got = list(da.prefetch_device(paths))
+    assert [p for p, _ in got] == paths
+    for (p, part), seg in zip(got, segs):
+        want = coracle.decode(seg.heap, seg.toast)
+        assert part.images.cpu().numpy().tobytes() == want["out_ind"].tobytes()
+        assert part.buffer_ids == [int(want["rows"][r, 1]) for r in want["order"]]
+    # an error in a later partition surfaces when that partition is reached
+    with pytest.raises(Exception):
+        list(da.prefetch_device(paths[:1] + [os.path.join(str(tmp_path), "gpseg9", "base", "16384", "train")]))
