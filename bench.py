@@ -159,6 +159,21 @@ class ClockSampler:
 # CPU arm: the oracle's C restatement on the host cores
 # ------------------------------------------------------------------------------------------------
 
+def python_pglz_rate():
+    """MB/s of decoded output of the reference's as-shipped decoder, pglz_decompress_py (a Python loop per output byte,
+    ppr:191-231; restated in oracle/da_oracle.py), on one ImageNet-shaped value of 150 KB, one process."""
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    import da_oracle
+    from cerebro_ds_kpgi_b200 import synth
+    ind, _ = synth.imagenet_rows(1, seed=2018, kind="norm_u8")
+    datum = synth.pglz_varlena(ind[0], "lz")
+    t0 = time.perf_counter()
+    out = da_oracle.pglz_decompress(datum)
+    dt = time.perf_counter() - t0
+    assert bytes(out) == ind[0].tobytes()
+    return ind[0].nbytes / dt / 1e6
+
+
 def host_threads():
     try:
         return len(os.sched_getaffinity(0))
@@ -510,6 +525,7 @@ def run_ours(args):
                    "sample": pool.describe(1) + " (best of 2, %.0f ms)" % (dt * 1000.0),
                    "one_process_rows_per_s": (pool.rows / threads) / dt_one,
                    "c_port_openmp_rows_per_s": c_rate,
+                   "reference_python_pglz_mb_per_s": python_pglz_rate(),
                    "c_port_note": "oracle/da_oracle.c, whole path in C + OpenMP (%d threads, %.0f ms per segment): much faster "
                                   "than the reference's Python reader; kept beside it for transparency" % (c_threads, c_dt * 1000.0)}
         line = {
