@@ -34,6 +34,7 @@ sys.path.insert(0, REPO)
 IMAGENET_ROW_BYTES = 112 * 112 * 3 * 4
 IMAGES_PER_BUFFER = int(os.environ.get("CDS_BENCH_IMAGES_PER_BUFFER", "3210"))   # imagenet_packed (--images-per-buffer); workers of the reference arm inherit it through the environment
 LABEL_ROW_BYTES = 1000 * 2
+CRITEO_BUFFERS = int(os.environ.get("CDS_BENCH_CRITEO_BUFFERS", "0"))          # --criteo-buffers (0: sized from --toast-mib, at most 1024)
 NVSMI_QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
                "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
                "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -78,9 +79,12 @@ def make_workload(name, seed, toast_mib):
         per_buf = B * 7306 * 4
         n = max(1, (target * 20) // per_buf)       # ~20x compression: size the TOAST file, not the output
         n = min(n, 1024)           # a real partition holds ~6 300 such buffers (1 624 157 rows / 256)
-        ind, dep = synth.criteo_buffers(n, seed=seed, rows_per_buffer=B)
+        if CRITEO_BUFFERS:
+            n = CRITEO_BUFFERS     # --criteo-buffers: a partition-sized segment; distinct buffers repeat after 256
+        ind, dep = synth.criteo_buffers(min(n, 256), seed=seed, rows_per_buffer=B)
+        ind, dep = [ind[i % len(ind)] for i in range(n)], [dep[i % len(dep)] for i in range(n)]
         seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="inline_pglz", dist_key=seed - 2018,
-                                  keep_expected=False, effort=4)
+                                  keep_expected=False, effort=4, toast_cap_pages=n * 16 + 64)
         meta = dict(isb=7306 * 4, dsb=4, samples=n * B, classes=2,
                     desc="Criteo-shaped buffers (256 x 7306 f32 pglz, int16[256,2] inline pglz)")
     elif name == "imagenet_packed":
@@ -593,6 +597,8 @@ def main():
     ap.add_argument("--no-graph", dest="graph", action="store_false")
     ap.add_argument("--wide", default="auto", choices=["off", "auto", "force"],
                     help="intra-value parallel pglz decoder: never / decided per decode by the device-side cost model / always")
+    ap.add_argument("--criteo-buffers", type=int, default=0,
+                    help="criteo: buffers per segment (default: from --toast-mib, at most 1024; a real partition holds ~6300)")
     ap.add_argument("--images-per-buffer", type=int, default=3210, help="imagenet_packed: images per packed buffer (the paper's tables: 3210)")
     ap.add_argument("--toast-mib", type=int, default=1024, help="TOAST file size per segment (config: 1 GiB)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -602,6 +608,9 @@ def main():
     global IMAGES_PER_BUFFER
     IMAGES_PER_BUFFER = args.images_per_buffer
     os.environ["CDS_BENCH_IMAGES_PER_BUFFER"] = str(args.images_per_buffer)
+    global CRITEO_BUFFERS
+    CRITEO_BUFFERS = args.criteo_buffers
+    os.environ["CDS_BENCH_CRITEO_BUFFERS"] = str(args.criteo_buffers)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference_arm(args)

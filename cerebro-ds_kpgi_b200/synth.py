@@ -190,14 +190,19 @@ def build_segment(ind_arrays, dep_arrays, ind_storage="ext_raw", dep_storage="in
     valueid = first_valueid
     pending = []
 
+    encoded = {}                     # (id(array), storage) -> payload: callers may pass the same array for many rows
+
     def store_external(arr, how):
         nonlocal valueid
         raw = _as_u8(arr)
         if how == "ext_raw":
             payload, rawsize = raw, raw.size
         else:
-            stream = pglz_stream(raw, "literal" if how == "ext_literal" else "lz", effort)
-            payload = np.frombuffer(struct.pack("<I", raw.size) + stream, dtype=np.uint8)
+            key = (id(arr), how)
+            if key not in encoded:
+                stream = pglz_stream(raw, "literal" if how == "ext_literal" else "lz", effort)
+                encoded[key] = np.frombuffer(struct.pack("<I", raw.size) + stream, dtype=np.uint8)
+            payload = encoded[key]
             rawsize = raw.size
         vid = valueid
         valueid += 1
