@@ -91,7 +91,8 @@ def make_workload(name, seed, toast_mib):
         # the paper's table layout (load_imagenet.py:27-31): B images per buffer, one huge pglz value each
         B = IMAGES_PER_BUFFER
         n = max(1, int(target // (B * IMAGENET_ROW_BYTES * 0.67)))
-        ind, dep = synth.imagenet_rows(n, seed=seed, kind="norm_u8", images_per_row=B)
+        ind, dep = synth.imagenet_rows(min(n, 4), seed=seed, kind="norm_u8", images_per_row=B)     # distinct buffers repeat after 4
+        ind, dep = [ind[i % len(ind)] for i in range(n)], [dep[i % len(dep)] for i in range(n)]
         seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="ext_pglz", dist_key=seed - 2018,
                                   keep_expected=False, effort=4)
         meta = dict(isb=IMAGENET_ROW_BYTES, dsb=LABEL_ROW_BYTES, samples=n * B, classes=1000,
