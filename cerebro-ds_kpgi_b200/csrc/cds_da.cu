@@ -159,7 +159,7 @@ static int launch_wide(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs
     k_wide_outs<<<sms * 8u, 256, 0, st>>>(wa);
     k_wide_scan<<<sms * 2u, kScanThreads, 0, st>>>(wa);
     k_wide_check<<<8, 256, 0, st>>>(wa);
-    k_wide_fine<<<sms * 8u, 256, 0, st>>>(wa);
+    k_wide_blkmap<<<sms * 2u, 256, 0, st>>>(wa);
     k_wide_blocks<1><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
     k_wide_tails<0><<<sms, 1024, 0, st>>>(wa);
     k_wide_tails<1><<<sms, 1024, 0, st>>>(wa);

@@ -16,9 +16,10 @@
 //     the segment: entry -> exit offset into the next segment.  These 25-entry maps compose
 //     associatively: k_wide_super folds 256 of them, one warp walks the folded maps of a value
 //     (k_wide_chain: the chain must end exactly at srcend), k_wide_entries unfolds them into the true
-//     entry of every segment.  k_wide_outs / k_wide_scan / k_wide_check then count the output bytes of
-//     each segment's groups, prefix-sum them (the total must be rawsize), and k_wide_fine records, per
-//     32-byte sub-segment, where its first group starts and which output byte that group produces.
+//     entry of every segment.  k_wide_outs walks each segment's groups once: their output bytes and, per
+//     32-byte sub-segment, where its first group starts and which output byte that group produces;
+//     k_wide_scan / k_wide_check prefix-sum the segments (the total must be rawsize); k_wide_blkmap finds
+//     the sub-segment each output block starts in.
 //
 //  B. What does a match copy?  Output is cut into blocks of 57344 bytes.  A block is rebuilt in shared
 //     memory as a forest: every output byte points at the byte it copies (a literal points at itself;
@@ -529,8 +530,10 @@ __device__ __forceinline__ uint32_t wide_group_walk(const uint8_t *__restrict__ 
     return q;
 }
 
-// One thread per segment: output bytes of the groups that start in it (padding segments and values already
-// refused count 0, so one flat prefix sum serves all values).
+// One thread per segment walks its chain of groups: output bytes of the groups that start in it (padding segments
+// and values already refused count 0, so one flat prefix sum serves all values), and, for each 32-byte sub-segment,
+// where its first group starts and which output byte (relative to the segment) that group produces first.
+// Sub-segments are the units the block kernels hand to their threads.
 __global__ void __launch_bounds__(256)
 k_wide_outs(WideArea wa)
 {
@@ -543,16 +546,23 @@ k_wide_outs(WideArea wa)
         uint32_t total = 0;
         if (wjp->state == 0u && lseg < wjp->nseg) {
             const uint32_t e = wa.seg_e[seg];
+            uint32_t *fine = wa.sub_entry + (size_t)seg * kWideSubs;
+            const uint32_t end = min((lseg + 1u) * kWideSeg, slen);
+            uint32_t sub = 0;                                                // next sub-segment of this segment without a record
             if (e < 25u) {
                 const uint8_t *src = reinterpret_cast<const uint8_t *>(wjp->src);
-                const uint32_t end = min((lseg + 1u) * kWideSeg, slen);
                 uint32_t a = lseg * kWideSeg + e;
                 while (a < end) {
+                    const uint32_t my_sub = (a - lseg * kWideSeg) / kWideSub;
+                    if (my_sub >= sub) { fine[my_sub] = (total << 5) | (a - (lseg * kWideSeg + my_sub * kWideSub)); sub = my_sub + 1u; }
                     uint32_t out;
                     a = wide_group_walk(src, a, slen, &out);
                     total += out;
                 }
             }
+            // sub-segments of the stream's end in which no group starts
+            const uint32_t nsub_here = (end - lseg * kWideSeg + kWideSub - 1u) / kWideSub;
+            for (; sub < nsub_here; sub++) fine[sub] = 31u;
         }
         wa.seg_out[seg] = total;
     }
@@ -581,43 +591,31 @@ k_wide_check(WideArea wa)
     }
 }
 
-// One thread per segment walks its chain of groups again, now knowing the output position it starts at, and
-// records, for each 32-byte sub-segment, where its first group starts and which output byte that group produces
-// first; also the sub-segment every output block starts in.  Sub-segments are the units the block kernels hand
-// to their threads.
+// One thread per output block: the sub-segment that holds the group producing the block's first byte = the last
+// sub-segment whose first group starts at or before that byte (binary search; positions grow with the sub-segments,
+// and sub-segments without a group exist only at the very end of a stream).
 __global__ void __launch_bounds__(256)
-k_wide_fine(WideArea wa)
+k_wide_blkmap(WideArea wa)
 {
-    const uint32_t n_jobs = wa.state->n_jobs, n_segs = wa.state->n_segs;
+    const uint32_t n_jobs = wa.state->n_jobs, n_blks = wa.state->n_blks;
     if (n_jobs == 0) return;
-    for (uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x; seg < n_segs; seg += gridDim.x * blockDim.x) {
-        const uint32_t jn = wide_find_seg(wa, n_jobs, seg);
+    for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < n_blks; b += gridDim.x * blockDim.x) {
+        const uint32_t jn = wide_find_blk(wa, n_jobs, b);
         const WideJob *wjp = &wa.jobs[jn];
-        const uint32_t lseg = seg - wjp->seg0, nseg = wjp->nseg, slen = wjp->slen;
-        if (wjp->state != 0u || lseg >= nseg) continue;
-        const uint8_t *src = reinterpret_cast<const uint8_t *>(wjp->src);
-        const uint32_t nblk = wjp->nblk, blk0 = wjp->blk0;
-        const uint32_t e = wa.seg_e[seg];
-        uint32_t *fine = wa.sub_entry + (size_t)seg * kWideSubs;
-        const uint32_t end = min((lseg + 1u) * kWideSeg, slen);
-        uint32_t sub = 0;                                                    // next sub-segment of this segment without a record
-        if (e < 25u) {
-            const uint32_t o_seg = (uint32_t)(wa.seg_base[seg] - wa.seg_base[wjp->seg0]);
-            uint32_t a = lseg * kWideSeg + e, o = o_seg;
-            while (a < end) {
-                const uint32_t my_sub = (a - lseg * kWideSeg) / kWideSub;
-                if (my_sub >= sub) { fine[my_sub] = ((o - o_seg) << 5) | (a - (lseg * kWideSeg + my_sub * kWideSub)); sub = my_sub + 1u; }
-                uint32_t out;
-                a = wide_group_walk(src, a, slen, &out);
-                const uint32_t k = (o + kWideBlock - 1u) / kWideBlock;       // first block boundary at or after o
-                if ((unsigned long long)k * kWideBlock < (unsigned long long)o + out && k < nblk)
-                    wa.blk_sub0[blk0 + k] = lseg * kWideSubs + my_sub;
-                o += out;
-            }
+        const uint32_t k = b - wjp->blk0;
+        if (wjp->state != 0u || k >= wjp->nblk) continue;
+        const unsigned long long target = (unsigned long long)k * kWideBlock;
+        const unsigned long long base0 = wa.seg_base[wjp->seg0];
+        const uint32_t *fine = wa.sub_entry + (size_t)wjp->seg0 * kWideSubs;
+        const uint32_t nsub = wjp->slen ? (wjp->slen - 1u) / kWideSub + 1u : 0u;
+        uint32_t lo = 0, hi = nsub;                                          // sub 0 starts at output 0 <= target
+        while (hi - lo > 1u) {
+            const uint32_t mid = (lo + hi) >> 1, ent = fine[mid];
+            const bool le = (ent & 31u) != 31u &&
+                            wa.seg_base[wjp->seg0 + mid / kWideSubs] - base0 + (ent >> 5) <= target;
+            if (le) lo = mid; else hi = mid;
         }
-        // sub-segments of the stream's end in which no group starts
-        const uint32_t nsub_here = (end - lseg * kWideSeg + kWideSub - 1u) / kWideSub;
-        for (; sub < nsub_here; sub++) fine[sub] = 31u;
+        wa.blk_sub0[b] = lo;
     }
 }
 
