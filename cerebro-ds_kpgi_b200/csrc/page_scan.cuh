@@ -227,7 +227,10 @@ k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t
         uint32_t id = 0, seq = 0, loc_off = 0, loc_len = 0, ref = kNone, hdr0 = 0;
         if (!dead) {
             lp = (lp + 7u) & ~7u;                                            // MAX_ALIGN (ppr:394)
-            if (lp + kItemHdr > kPage) dead = true;
+            if (lp + kItemHdr > kPage) {                                     // the header unpack fails on a short slice (ppr:396)
+                dead = true;
+                report(st, 1, p, 1, i, CDS_ERR_TUPLE);
+            }
         }
         if (!dead) {
             uint32_t t_hoff, hdr, chunkword;

@@ -252,3 +252,23 @@ def test_one_call_decode_with_a_heap_of_more_than_1020_pages(torch_cuda, coracle
     assert s2.status == 0 and s2.n_rows == m
     assert out_d[:want2["out_dep"].size].cpu().numpy().tobytes() == want2["out_dep"].tobytes()
     ds.close()
+
+
+def test_toast_page_claiming_more_items_than_it_holds_is_refused(torch_cuda, coracle):
+    """pd_lower of a TOAST page inflated: the physical walk (ppr:391-414) runs off the end of the page after the real
+    tuples and the reference's header unpack fails; found by the seed-shifted corruption soak (a silent pass before)."""
+    import da_oracle
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    ind, dep = synth.imagenet_rows(6, seed=3, shape=(36, 36, 3), classes=12, images_per_row=2)
+    seg = synth.build_segment(ind, dep, ind_storage="ext_raw", dep_storage="inline_pglz")
+    for extra in (4, 52 * 256):
+        toast = seg.toast.copy()
+        page = 32768
+        lower = int(toast[page + 12]) | (int(toast[page + 13]) << 8)
+        lower += extra                                                      # still a multiple of 4 past the header
+        toast[page + 12], toast[page + 13] = lower & 0xFF, lower >> 8
+        with pytest.raises(da_oracle.OracleError) as ei:
+            coracle.decode(seg.heap, toast)
+        st, part = segment.decode_pages(torch.from_numpy(seg.heap).cuda(), torch.from_numpy(toast).cuda())
+        assert st == ei.value.code == 4
