@@ -749,6 +749,12 @@ k_wide_blocks(WideArea wa)
             }
         }
         __syncthreads();
+        if (sh_bad) {
+            // A match with offset 0, or one that reaches before the start of the output (the group chain of such a stream
+            // can still be well-formed).  Its bytes were not entered into the forest, so nothing below may run on it.
+            if (tid == 0) wide_fail(wa, jn);
+            continue;
+        }
 
         // ---- bodies of long matches: point at the byte they copy (always before their own item)
         uint32_t act[2] = {0u, 0u};                                          // my entries that are not yet resolved
@@ -761,6 +767,7 @@ k_wide_blocks(WideArea wa)
             const uint32_t h = wide_head_of(heads, e);
             if (h == kNone) { sh_bad = 1u; ptr[e] = (uint16_t)e; continue; }  // cannot happen on a stream k_wide_chain accepted
             const uint32_t off = (uint32_t)val[h] | ((uint32_t)val[h + 1u] << 8), kk = e - h;
+            if (off == 0u || off > kWideWin || off > h) { sh_bad = 1u; ptr[e] = (uint16_t)e; continue; }   // (same: keeps every pointer backwards)
             uint32_t sidx;
             if (off > kk) sidx = e - off;
             else if (off <= 1u) sidx = h - 1u;                                // runs of one byte value
@@ -788,7 +795,10 @@ k_wide_blocks(WideArea wa)
         }
         // ---- pointer jumping (two hops a round) until every byte points at a literal of the block or into the
         //      previous tail; resolved entries leave the per-thread work mask
-        for (; resolve_all;) {
+        // (pointers only ever point backwards, so the forest has no cycle and log2(61440) rounds suffice; the bound is a
+        // safety net: a kernel must not spin on damaged input)
+        for (uint32_t round = 0; resolve_all; round++) {
+            if (round > 24u) { sh_bad = 1u; break; }
             int changed = 0;
 #pragma unroll
             for (uint32_t half = 0; half < 2; half++) {

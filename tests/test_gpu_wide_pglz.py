@@ -316,3 +316,42 @@ def test_wide_streams_ending_on_segment_and_block_boundaries(torch_cuda, coracle
         with pytest.raises(Exception):
             coracle.pglz_decompress(d)
         assert c == 11
+
+
+@pytest.mark.timeout(120)
+def test_wide_refuses_offset_zero_and_offsets_before_the_start_without_spinning(torch_cuda, coracle, wide_threshold):
+    """Streams whose chain of control groups is well-formed (so they reach the block kernels) but that hold a match with
+    offset 0, or one that reaches before the start of the output.  (An item that is not entered into the block's
+    forest once left stale pointers behind, and the pointer-jumping loop never ended: found by tools/soak_fuzz.py.)"""
+    from cerebro_ds_kpgi_b200 import segment
+    wide_threshold(1024)
+    rng = np.random.default_rng(1 + SEED_SHIFT)
+
+    def literal_groups(n_groups):
+        return b"".join(b"\x00" + bytes(rng.integers(0, 256, 8, dtype=np.uint8)) for _ in range(n_groups))
+
+    def varlena(stream, rawsize):
+        return struct.pack(">I", 0x40000000 | (8 + len(stream))) + struct.pack("<I", rawsize) + stream
+
+    datums = []
+    for n_before, n_after in ((137, 0), (137, 9000), (8000, 300), (0, 200)):
+        for off, length in ((0, 8), (0, 3), (0, 200)):
+            if length <= 17:
+                tag = bytes([(length - 3) | ((off >> 8) << 4), off & 0xFF])
+            else:
+                tag = bytes([0x0F | ((off >> 8) << 4), off & 0xFF, length - 18])
+            stream = literal_groups(n_before) + b"\x01" + tag + bytes(rng.integers(0, 256, 7, dtype=np.uint8)) + literal_groups(n_after)
+            datums.append(varlena(stream, 8 * n_before + length + 7 + 8 * n_after))
+    for off in (1, 100, 4095):                                              # first item of the value: nothing to copy from yet
+        tag = bytes([0x0F | ((off >> 8) << 4), off & 0xFF, 255])
+        stream = b"\x01" + tag + bytes(rng.integers(0, 256, 7, dtype=np.uint8)) + literal_groups(400)
+        datums.append(varlena(stream, 273 + 7 + 3200))
+    good = varlena(literal_groups(500), 4000)
+    before = wide_count()
+    out, codes = segment.pglz_decompress_batch(datums + [good])
+    assert wide_count() - before == len(datums) + 1
+    assert codes == [11] * len(datums) + [0]
+    for d in datums:
+        with pytest.raises(Exception):
+            coracle.pglz_decompress(d)
+    assert out[-1] == bytes(coracle.pglz_decompress(good))

@@ -42,6 +42,7 @@ def main():
                 print("seed shift %d, %s:\n%s" % (k, name, traceback.format_exc().splitlines()[-1]), flush=True)
             finally:
                 set_thr(1 << 20, 0)
+        print("shift %d done" % k, flush=True)
     print("shifts %d..%d: %d failures %s" % (first, last, len(failed), failed))
     sys.exit(1 if failed else 0)
 
