@@ -79,7 +79,9 @@ int cds_host_free(void *ptr);
  * All device memory the decode needs is allocated here, once: capacities are in pages.
  * max_chunks = 0 -> 6 per TOAST page + 4096.  scratch_bytes = ~0 -> as many bytes as the TOAST
  * capacity (always enough); 0 -> none (segments with compressed external values are refused).
- * stage_pages != 0 also allocates device page buffers so that cds_decode_host can be used. */
+ * stage_pages != 0 also allocates device page buffers so that cds_decode_host can be used.
+ * With scratch, the work area of the intra-value parallel pglz decoder is allocated too: about
+ * 0.18 bytes per scratch byte (sub-segment entries, segment tables, block flags). */
 int cds_segment_create(cds_segment **out, int device, uint64_t max_heap_pages, uint64_t max_toast_pages,
                        uint64_t max_chunks, uint64_t scratch_bytes, int stage_pages);
 int cds_segment_destroy(cds_segment *seg);
