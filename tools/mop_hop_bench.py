@@ -22,6 +22,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     import bench
+    bench.REAL_STDOUT = bench.protect_stdout()      # NCCL prints its version banner on fd 1: the JSON line goes to the saved descriptor
     from cerebro_ds_kpgi_b200 import mop, segment
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -68,10 +69,10 @@ def main():
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
         ms = float(t.item())
-        print(json.dumps({"workload": "mop_hop", "n_gpus": world, "state_bytes": 4 * numel, "hop_ms": ms,
+        bench.emit({"workload": "mop_hop", "n_gpus": world, "state_bytes": 4 * numel, "hop_ms": ms,
                           "hop_gb_per_s_per_gpu": (4 * numel / (ms / 1000.0) / 1e9) if world > 1 and ms > 0 else None,
                           "epochs": 5, "rounds_per_epoch": len(hop.schedule), "wall_s": wall,
-                          "ingest_overlapped": True, "backend": "nccl send/recv (batch_isend_irecv)"}))
+                          "ingest_overlapped": True, "backend": "nccl send/recv (batch_isend_irecv)"})
     dist.destroy_process_group()
 
 
