@@ -41,6 +41,7 @@ _vp, _u64, _u32, _int = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctype
 _pu64, _pu32 = ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint32)
 PROTOTYPES = {
     "cds_version": (_int, []),
+    "cds_summary_size": (_u32, []),
     "cds_status_str": (ctypes.c_char_p, [_int]),
     "cds_last_error": (ctypes.c_char_p, []),
     "cds_device_count": (_int, []),
@@ -63,6 +64,7 @@ PROTOTYPES = {
     "cds_launch_count": (ctypes.c_ulonglong, []),
     "cds_timing_enable": (_int, [_vp, _u32]),
     "cds_timing_read": (_int, [_vp, _vp, _u32, _pu32]),
+    "cds_timing_read_stage": (_int, [_vp, _u32, _vp, _u32, _pu32]),
     "cds_export_rows": (_int, [_vp, _vp, _u64, _pu64, _vp]),
     "cds_export_layout": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _vp]),
     "cds_export_chunks": (_int, [_vp, _vp, _vp, _vp, _vp, _u64, _pu64, _vp]),
@@ -70,6 +72,7 @@ PROTOTYPES = {
     "cds_pglz_decompress_batch_static": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "cds_set_wide_pglz_threshold": (_int, [_u32, _int]),
     "cds_set_wide_pglz": (_int, [_vp, _int]),
+    "cds_trim_work_memory": (_int, [_int]),
     "cds_wide_decoded_count": (ctypes.c_ulonglong, []),
     "pglz_decompress": (None, [ctypes.c_char_p, ctypes.c_char_p]),
     "cds_onehot_argmax_i16": (_int, [_vp, _u64, _u32, _vp, _vp]),

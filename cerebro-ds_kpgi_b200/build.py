@@ -26,6 +26,7 @@ NVCC_FLAGS = [
     "-O3", "-lineinfo", "-std=c++17",
     "--shared", "-Xcompiler", "-fPIC,-O3",
     "-Xptxas", "-v",
+    "-rdc=true",            # k_decode_gate launches kernels from the device (needs relocatable device code + cudadevrt)
 ]
 
 
@@ -80,13 +81,13 @@ def nvcc_path():
 
 def build_cuda(force=False):
     """libcds_da.so: the C-ABI library (include/cds_da.h) with every sm_100a kernel."""
-    srcs = _sources(CSRC, (".cu", ".cuh", ".h")) + _sources(os.path.join(REPO_ROOT, "include"), (".h",))
+    srcs = _sources(CSRC, (".cu", ".cuh", ".h", ".inc")) + _sources(os.path.join(REPO_ROOT, "include"), (".h",))
     stamp = _digest(srcs, " ".join(NVCC_FLAGS))
     if not force and _up_to_date(LIB_DA, stamp):
         return LIB_DA
     cmd = [nvcc_path()] + NVCC_FLAGS + [
         "-I", os.path.join(REPO_ROOT, "include"), "-I", CSRC,
-        os.path.join(CSRC, "cds_da.cu"), "-o", LIB_DA, "-lcudart",
+        os.path.join(CSRC, "cds_da.cu"), "-o", LIB_DA, "-lcudadevrt", "-lcudart",
     ]
     _run(cmd, log_name=os.path.join(PKG_DIR, "build_cuda.log"))
     _write_stamp(LIB_DA, stamp)

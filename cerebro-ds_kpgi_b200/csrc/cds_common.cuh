@@ -50,6 +50,17 @@ constexpr uint32_t kOpU8Norm = 0x40000000u;   // CopyOp.len flag: payload is uin
                                               // CopyOp.src_off bits 16.. hold the channel of the chunk's first byte
 constexpr uint32_t kJobU8Norm = 0x40000000u;  // PglzJob.slen flag, same meaning
 constexpr uint32_t kFlagBits = 0xC0000000u;
+// CopyOp.len flag: the chunk holds part of a LITERAL-ONLY pglz stream (groups of one zero control byte + 8 literals;
+// slen == rawsize + ceil(rawsize / 8), so no tag can exist in a well-formed stream): the gather drops the control
+// bytes on the way (9 -> 8 bytes) and checks that they are zero, no staging copy and no pglz job.  len & 0xFFFF =
+// stream bytes of this chunk; src_off bits 16..19 = stream offset of the first byte mod 9, bits 20..22 = items of
+// the value's final group when its control byte lies in this chunk and the group is short (its unused control bits
+// are never looked at by the reference, ppr:203), else 0.
+constexpr uint32_t kOpLiteral = 0x20000000u;
+__host__ __device__ __forceinline__ bool pglz_literal_only(unsigned long long slen, unsigned long long rawsize)
+{
+    return rawsize > 0ull && slen == rawsize + ((rawsize + 7ull) >> 3);
+}
 struct __align__(16) CopyOp {
     unsigned long long dst;   // absolute device address
     uint32_t src_off;         // payload offset inside its page

@@ -38,6 +38,48 @@ static int cuda_fail(cudaError_t e, const char *what)
         if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
     } while (0)
 
+// Every entry point that makes `device` current restores the caller's device when it returns.
+struct DeviceScope {
+    int prev = -1;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceScope(int device)
+    {
+        int cur = -1;
+        err = cudaGetDevice(&cur);
+        if (err == cudaSuccess && cur != device) {
+            err = cudaSetDevice(device);
+            if (err == cudaSuccess) prev = cur;
+        }
+    }
+    ~DeviceScope() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceScope(const DeviceScope &) = delete;
+    DeviceScope &operator=(const DeviceScope &) = delete;
+};
+#define ON_DEVICE(dev)                                                         \
+    DeviceScope device_scope__(dev);                                           \
+    if (device_scope__.err != cudaSuccess) return cuda_fail(device_scope__.err, "cudaSetDevice")
+
+// Multiprocessor count of `device` (queried once per device).
+static int sm_count(int device)
+{
+    static int cached[64] = {0};
+    if (device < 0 || device >= 64) return 148;
+    if (cached[device] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0) { cudaGetLastError(); n = 148; }
+        cached[device] = n;
+    }
+    return cached[device];
+}
+static int current_sm_count()
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return 148; }
+    return sm_count(dev);
+}
+
+constexpr uint32_t kTimedStages = 4;   // 0 gather, 1 pglz stage (classify + wide + warp decoder), 2 / 3 the wide block passes
+
 struct cds_segment {
     int device = 0;
     int num_sms = 148;
@@ -50,9 +92,9 @@ struct cds_segment {
     int coop_blocks = 0;            // co-resident grid for k_plan_fused (0: cooperative launch unavailable)
     int ind_format = 0;             // cds_set_output_format: 0 stored bytes, 1 f32 -> bf16, 2 u8 -> f32 through the table
     float *d_lut = nullptr;         // cds_set_normalize_lut: [channels][256]
-    int wide_mode = 2;              // cds_set_wide_pglz: 0 never, 1 always, 2 when the last summary counted large values
-    bool wide_hint = true;          // until a summary says otherwise: a handle's first decode launches the wide kernels
-    bool wide_launched = false;     // this decode ran the wide decoder: cds_finish reads its counters
+    int wide_mode = 2;              // cds_set_wide_pglz: 0 never, 1 host-launched without the cost model, 2 decided and launched on
+                                    // the device (k_decode_gate), 3 host-launched with the cost model
+    bool wide_launched = false;     // this decode may have run the wide decoder: cds_finish reads its counters
     uint8_t *wide_mem = nullptr;    // work area of the intra-value parallel pglz decoder (pglz_wide.cuh)
     WideArea wide;
     uint32_t lut_channels = 0;
@@ -77,14 +119,17 @@ struct cds_segment {
     ScanWs ws[7];                               // heap index, TOAST index, inline rank, chunk rank, ind, dep, staging
     DevState *state = nullptr;
     DevState *h_state = nullptr;   // pinned
-    // optional CUDA-event timing of the gather kernel (cds_timing_enable)
+    // optional CUDA-event timing (cds_timing_enable): kTimedStages event pairs per sample
     cudaEvent_t *ev = nullptr;
     uint32_t ev_cap = 0, ev_used = 0;
+    uint8_t *ev_mask = nullptr;     // per sample: which stages were recorded
 };
 
 // ---- library -----------------------------------------------------------------------------------
 
-extern "C" int cds_version(void) { return 100; }
+extern "C" int cds_version(void) { return 200; }
+extern "C" uint32_t cds_summary_size(void) { return (uint32_t)sizeof(cds_summary); }
+static_assert(sizeof(cds_summary) == 80, "cds_summary is part of the ABI: INTEGRATION.md and _lib.py mirror its 80 bytes");
 
 extern "C" const char *cds_status_str(int s)
 {
@@ -145,29 +190,74 @@ static cudaError_t wide_prepare()
     return e;
 }
 
-// Classify the job list and decode the large values; the jobs taken are blanked, so the warp decoder that
-// runs afterwards skips them.
-static int launch_wide(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int num_sms, cudaStream_t st)
+// The 13 kernels behind the classification, on `st` (a host stream, or cudaStreamTailLaunch inside the gate kernel).
+#define CDS_WIDE_PIPELINE(wa, sms, st, BEFORE_B1, AFTER_B1, BEFORE_B3, AFTER_B3)            \
+    do {                                                                                    \
+        k_wide_maps<<<(sms) * 8u, 256, 0, st>>>(wa);                                        \
+        k_wide_super<<<(sms) * 4u, 128, 0, st>>>(wa);                                       \
+        k_wide_chain<<<(sms), 32, 0, st>>>(wa);                                             \
+        k_wide_entries<<<(sms) * 4u, 128, 0, st>>>(wa);                                     \
+        k_wide_outs<<<(sms) * 8u, 256, 0, st>>>(wa);                                        \
+        k_wide_scan<<<(sms) * 2u, kScanThreads, 0, st>>>(wa);                               \
+        k_wide_check<<<8, 256, 0, st>>>(wa);                                                \
+        k_wide_blkmap<<<(sms) * 2u, 256, 0, st>>>(wa);                                      \
+        BEFORE_B1;                                                                          \
+        k_wide_blocks<1><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
+        AFTER_B1;                                                                           \
+        k_wide_tails<0><<<(sms), 1024, 0, st>>>(wa);                                        \
+        k_wide_tails<1><<<(sms), 1024, 0, st>>>(wa);                                        \
+        k_wide_tails<2><<<(sms), 1024, 0, st>>>(wa);                                        \
+        BEFORE_B3;                                                                          \
+        k_wide_blocks<3><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
+        AFTER_B3;                                                                           \
+    } while (0)
+
+// Host-launched: classify the job list and decode the large values; the jobs taken are blanked, so the warp
+// decoder that runs afterwards skips them.  `ev4`: optional event pairs around the two block passes.
+static int launch_wide(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int num_sms, cudaStream_t st,
+                       cudaEvent_t *ev4 = nullptr, unsigned ev_flags = cudaEventRecordDefault)
 {
     const uint32_t sms = (uint32_t)num_sms;
     CU(cudaMemsetAsync(wa.state, 0, wa.zero_bytes, st));
     k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa);
-    k_wide_maps<<<sms * 8u, 256, 0, st>>>(wa);
-    k_wide_super<<<sms * 4u, 128, 0, st>>>(wa);
-    k_wide_chain<<<sms, 32, 0, st>>>(wa);
-    k_wide_entries<<<sms * 4u, 128, 0, st>>>(wa);
-    k_wide_outs<<<sms * 8u, 256, 0, st>>>(wa);
-    k_wide_scan<<<sms * 2u, kScanThreads, 0, st>>>(wa);
-    k_wide_check<<<8, 256, 0, st>>>(wa);
-    k_wide_blkmap<<<sms * 2u, 256, 0, st>>>(wa);
-    k_wide_blocks<1><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
-    k_wide_tails<0><<<sms, 1024, 0, st>>>(wa);
-    k_wide_tails<1><<<sms, 1024, 0, st>>>(wa);
-    k_wide_tails<2><<<sms, 1024, 0, st>>>(wa);
-    k_wide_blocks<3><<<sms, kWideThreads, kWideBlockSmem, st>>>(wa);
+    CDS_WIDE_PIPELINE(wa, sms, st,
+                      if (ev4) cudaEventRecordWithFlags(ev4[0], st, ev_flags), if (ev4) cudaEventRecordWithFlags(ev4[1], st, ev_flags),
+                      if (ev4) cudaEventRecordWithFlags(ev4[2], st, ev_flags), if (ev4) cudaEventRecordWithFlags(ev4[3], st, ev_flags));
     CU(cudaGetLastError());
     LAUNCHED(14);
     return CDS_OK;
+}
+
+// The pglz stage of the one-call decode, decided where the plan lives: on the device.  One block classifies the
+// job list of THIS decode (same cost model as the host-launched path) and then launches, from the device and
+// into the tail of its own stream position, exactly what the decode needs: the wide pipeline when large values
+// go wide, the warp decoder (sized for the job count) when there are jobs at all.  A segment without
+// compressed values pays for this one small launch and nothing else.
+__global__ void __launch_bounds__(1024)
+k_decode_gate(PglzJob *jobs, DevState *st, WideArea wa, uint32_t sms, int wide_enabled, const float *lut, uint32_t lut_channels)
+{
+    if (wide_enabled) {
+        if (threadIdx.x < sizeof(WideState) / 4u) reinterpret_cast<uint32_t *>(wa.state)[threadIdx.x] = 0u;
+        __syncthreads();
+        d_wide_classify(jobs, st, 0u, wa);
+        __syncthreads();
+    }
+    if (threadIdx.x != 0) return;
+    bool ok = true;
+    if (wide_enabled && wa.state->n_jobs != 0u) {
+        k_wide_zero<<<sms, 256, 0, cudaStreamTailLaunch>>>(wa);
+        CDS_WIDE_PIPELINE(wa, sms, cudaStreamTailLaunch, , , , );
+        ok = cudaGetLastError() == cudaSuccess;
+    }
+    const uint32_t n_jobs = st->n_jobs_front + st->n_jobs_back;
+    if (n_jobs != 0u) {
+        uint32_t grid = (n_jobs + kPglzWarps - 1u) / kPglzWarps;
+        if (grid > sms * 7u) grid = sms * 7u;
+        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, cudaStreamTailLaunch>>>(jobs, st, 0u, nullptr, st, &st->pglz_ticket, lut,
+                                                                                       lut_channels);
+        ok = ok && cudaGetLastError() == cudaSuccess;
+    }
+    if (!ok) report(st, 4, 0, 7, 0, CDS_ERR_CUDA);                          // a device-side launch was refused
 }
 
 extern "C" int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model)
@@ -188,7 +278,7 @@ static cudaError_t dalloc(T **p, uint64_t n)
 extern "C" int cds_segment_destroy(cds_segment *s)
 {
     if (!s) return CDS_OK;
-    cudaSetDevice(s->device);
+    DeviceScope device_scope__(s->device);
     void *bufs[] = {s->stage_heap, s->stage_toast, s->heap_base, s->toast_base, s->rows, s->zero_region, s->scan_vals, s->dir_id, s->dir_loc,
                     s->dir_ref, s->chunk_flag, s->vfirst, s->vcount, s->vseq0, s->vbytes, s->vscr, s->inline_flag,
                     s->row_first, s->pos_of_row, s->row_at_pos, s->ind_len, s->dep_len, s->pos_ind, s->pos_dep,
@@ -197,8 +287,9 @@ extern "C" int cds_segment_destroy(cds_segment *s)
     if (s->h_state) cudaFreeHost(s->h_state);
     if (s->d_lut) cudaFree(s->d_lut);
     if (s->ev) {
-        for (uint32_t i = 0; i < 2 * s->ev_cap; i++) cudaEventDestroy(s->ev[i]);
+        for (uint32_t i = 0; i < 2 * kTimedStages * s->ev_cap; i++) cudaEventDestroy(s->ev[i]);
         free(s->ev);
+        free(s->ev_mask);
     }
     delete s;
     return CDS_OK;
@@ -212,7 +303,7 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
     int ndev = cds_device_count();
     if (ndev == 0) return CDS_ERR_NO_DEVICE;
     if (device < 0 || device >= ndev) return CDS_ERR_ARG;
-    CU(cudaSetDevice(device));
+    ON_DEVICE(device);
     cds_segment *s = new (std::nothrow) cds_segment();
     if (!s) return CDS_ERR_ARG;
     s->device = device;
@@ -297,7 +388,7 @@ extern "C" int cds_set_output_format(cds_segment *s, int independent_var_format)
 
 extern "C" int cds_set_wide_pglz(cds_segment *s, int mode)
 {
-    if (!s || mode < 0 || mode > 2) return CDS_ERR_ARG;
+    if (!s || mode < 0 || mode > 3) return CDS_ERR_ARG;
     s->wide_mode = mode;
     return CDS_OK;
 }
@@ -305,7 +396,7 @@ extern "C" int cds_set_wide_pglz(cds_segment *s, int mode)
 extern "C" int cds_set_normalize_lut(cds_segment *s, const float *h_lut, uint32_t channels)
 {
     if (!s || !h_lut || channels == 0 || channels > kMaxLutChannels) return CDS_ERR_ARG;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     if (!s->d_lut) CU(cudaMalloc(reinterpret_cast<void **>(&s->d_lut), sizeof(float) * 256 * kMaxLutChannels));
     CU(cudaMemcpy(s->d_lut, h_lut, sizeof(float) * 256 * channels, cudaMemcpyHostToDevice));
     s->lut_channels = channels;
@@ -336,7 +427,7 @@ extern "C" int cds_heap_scan(cds_segment *s, const void *d_heap_pages, uint64_t 
     if (n_pages > s->cap_heap_pages) return CDS_ERR_CAPACITY;
     if (reinterpret_cast<uintptr_t>(d_heap_pages) & 15u) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     int rc = reset_state(s, st);
     if (rc) return rc;
     s->d_heap = static_cast<const uint8_t *>(d_heap_pages);
@@ -362,7 +453,7 @@ extern "C" int cds_set_rows(cds_segment *s, const uint32_t *h_rows, uint64_t n_r
     if (!s || (!h_rows && n_rows)) return CDS_ERR_ARG;
     if (n_rows > s->cap_rows) return CDS_ERR_CAPACITY;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     int rc = reset_state(s, st);
     if (rc) return rc;
     k_set_n_rows<<<1, 1, 0, st>>>(s->state, (uint32_t)n_rows);
@@ -384,7 +475,7 @@ extern "C" int cds_toast_scan(cds_segment *s, const void *d_toast_pages, uint64_
     if (n_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
     if (reinterpret_cast<uintptr_t>(d_toast_pages) & 15u) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     s->d_toast = static_cast<const uint8_t *>(d_toast_pages);
     s->n_toast_pages = n_pages;
     k_page_index<<<scan_grid(s, n_pages, 4), kScanThreads, 0, st>>>(s->d_toast, (uint32_t)n_pages, s->toast_base, s->state, 1,
@@ -452,7 +543,7 @@ extern "C" int cds_plan(cds_segment *s, uint32_t ind_sample_bytes, uint32_t dep_
 {
     if (!s || !s->have_rows || !s->have_chunks || s->have_plan) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     PlanArgs A = plan_args(s, ind_sample_bytes, dep_sample_bytes, nullptr, 0, nullptr, 0);
     int rc = launch_plan(s, A, false, st);
     if (rc) return rc;
@@ -462,37 +553,60 @@ extern "C" int cds_plan(cds_segment *s, uint32_t ind_sample_bytes, uint32_t dep_
 
 static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
 {
+    const bool timed = s->ev && s->ev_used < s->ev_cap;
+    // (inside a stream capture the timing events become event-record nodes of the graph)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (timed && cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+    const unsigned ev_flags = cap == cudaStreamCaptureStatusActive ? cudaEventRecordExternal : cudaEventRecordDefault;
+    cudaEvent_t *ev = timed ? s->ev + (size_t)2 * kTimedStages * s->ev_used : nullptr;
+    uint8_t mask = 0;
     if (s->n_toast_pages) {
         uint32_t grid = (uint32_t)(s->n_toast_pages < (uint64_t)s->num_sms ? s->n_toast_pages : (uint64_t)s->num_sms);
-        const bool timed = s->ev && s->ev_used < s->ev_cap;
-        // (inside a stream capture the timing events become event-record nodes of the graph)
-        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-        if (timed && cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
-        const unsigned ev_flags = cap == cudaStreamCaptureStatusActive ? cudaEventRecordExternal : cudaEventRecordDefault;
-        if (timed) CU(cudaEventRecordWithFlags(s->ev[2 * s->ev_used], st, ev_flags));
+        if (timed) CU(cudaEventRecordWithFlags(ev[0], st, ev_flags));
         k_toast_gather<<<grid, kGatherThreads, kGatherSmemBytes, st>>>(s->d_toast, (uint32_t)s->n_toast_pages,
                                                                        s->toast_base, s->ops, s->state,
-                                                                       s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels);
+                                                                       s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels,
+                                                                       s->dir_ref, s->vfirst);
         CU(cudaGetLastError());
         LAUNCHED(1);
-        if (timed) { CU(cudaEventRecordWithFlags(s->ev[2 * s->ev_used + 1], st, ev_flags)); s->ev_used++; }
+        if (timed) { CU(cudaEventRecordWithFlags(ev[1], st, ev_flags)); mask |= 1u; }
     }
-    if (s->wide_mem && g_wide_threshold && (s->wide_mode == 1 || (s->wide_mode == 2 && s->wide_hint))) {
-        WideArea wa = s->wide;
+    const float *lut = s->ind_format == 2 ? s->d_lut : nullptr;
+    const bool wide_possible = s->wide_mem && g_wide_threshold && s->wide_mode != 0;
+    WideArea wa = s->wide;
+    if (wide_possible) {
         wa.threshold = g_wide_threshold;
         wa.force = (s->wide_mode == 1 || g_wide_force) ? 1u : 0u;
         wa.st = s->state;
-        wa.lut = s->ind_format == 2 ? s->d_lut : nullptr;
+        wa.lut = lut;
         wa.lut_channels = s->lut_channels ? s->lut_channels : 1u;
-        int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st);
-        if (rc) return rc;
-        s->wide_launched = true;
     }
-    // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
-    k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
-        s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket, s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels);
-    CU(cudaGetLastError());
-    LAUNCHED(1);
+    if (timed) CU(cudaEventRecordWithFlags(ev[2], st, ev_flags));
+    if (s->wide_mode == 2) {
+        // decided on the device: one launch; the wide pipeline and the warp decoder are launched from there
+        k_decode_gate<<<1, 1024, 0, st>>>(s->jobs, s->state, wa, (uint32_t)s->num_sms, wide_possible ? 1 : 0, lut, s->lut_channels);
+        CU(cudaGetLastError());
+        LAUNCHED(1);
+        s->wide_launched = wide_possible;
+    } else {
+        if (wide_possible) {
+            int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st, timed ? ev + 4 : nullptr, ev_flags);
+            if (rc) return rc;
+            if (timed) mask |= 4u | 8u;
+            s->wide_launched = true;
+        }
+        // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
+        k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
+            s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket, lut, s->lut_channels);
+        CU(cudaGetLastError());
+        LAUNCHED(1);
+    }
+    if (timed) {
+        CU(cudaEventRecordWithFlags(ev[3], st, ev_flags));
+        mask |= 2u;
+        s->ev_mask[s->ev_used] = mask;
+        s->ev_used++;
+    }
     return CDS_OK;
 }
 
@@ -501,7 +615,7 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
 {
     if (!s || !s->have_plan || s->have_ops) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     PlanArgs A = plan_args(s, 0, 0, d_out_ind, ind_cap, d_out_dep, dep_cap);
     k_resolve<<<small_grid(s), 256, 0, st>>>(A);
     CU(cudaGetLastError());
@@ -522,7 +636,7 @@ extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
 {
     if (!s) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
     WideState wide_counts;
     memset(&wide_counts, 0, sizeof(wide_counts));
@@ -535,7 +649,6 @@ extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
     local.n_rows = h.n_rows; local.n_positions = h.n_pos; local.ind_bytes = h.ind_bytes; local.dep_bytes = h.dep_bytes;
     local.n_chunks = h.n_chunks; local.n_inline = h.n_inline; local.scratch_bytes = h.scratch_bytes;
     local.n_wide_values = h.n_wide;
-    s->wide_hint = h.n_wide != 0;
     decode_key(~h.err_inv, &local);
     if (sum) *sum = local;
     return (int)local.status;
@@ -549,10 +662,10 @@ extern "C" int cds_decode_device(cds_segment *s, const void *d_heap, uint64_t n_
     if (n_heap_pages > s->cap_heap_pages || n_toast_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
     if ((reinterpret_cast<uintptr_t>(d_heap) | reinterpret_cast<uintptr_t>(d_toast)) & 15u) return CDS_ERR_ARG;
     int rc;
+    ON_DEVICE(s->device);
     {
         // same steps as cds_heap_scan + cds_toast_scan, with both page indexes in one launch
         cudaStream_t st = (cudaStream_t)stream;
-        CU(cudaSetDevice(s->device));
         if ((rc = reset_state(s, st))) return rc;
         s->d_heap = static_cast<const uint8_t *>(d_heap); s->n_heap_pages = n_heap_pages;
         s->d_toast = static_cast<const uint8_t *>(d_toast); s->n_toast_pages = n_toast_pages;
@@ -609,7 +722,7 @@ extern "C" int cds_decode_host(cds_segment *s, const void *h_heap, uint64_t n_he
     if (!s || !s->stage_heap || !s->stage_toast) return CDS_ERR_ARG;
     if (n_heap_pages > s->cap_heap_pages || n_toast_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     CU(cudaMemcpyAsync(s->stage_heap, h_heap, n_heap_pages * (uint64_t)kPage, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s->stage_toast, h_toast, n_toast_pages * (uint64_t)kPage, cudaMemcpyHostToDevice, st));
     return cds_decode_device(s, s->stage_heap, n_heap_pages, s->stage_toast, n_toast_pages, isb, dsb, d_out_ind, ind_cap,
@@ -624,33 +737,46 @@ extern "C" unsigned long long cds_wide_decoded_count(void) { return g_wide_decod
 extern "C" int cds_timing_enable(cds_segment *s, uint32_t max_samples)
 {
     if (!s) return CDS_ERR_ARG;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     if (s->ev) {
-        for (uint32_t i = 0; i < 2 * s->ev_cap; i++) cudaEventDestroy(s->ev[i]);
+        for (uint32_t i = 0; i < 2 * kTimedStages * s->ev_cap; i++) cudaEventDestroy(s->ev[i]);
         free(s->ev);
+        free(s->ev_mask);
         s->ev = nullptr;
+        s->ev_mask = nullptr;
     }
     s->ev_cap = s->ev_used = 0;
     if (max_samples == 0) return CDS_OK;
-    s->ev = (cudaEvent_t *)calloc(2 * (size_t)max_samples, sizeof(cudaEvent_t));
-    if (!s->ev) return CDS_ERR_ARG;
-    for (uint32_t i = 0; i < 2 * max_samples; i++) CU(cudaEventCreate(&s->ev[i]));
+    s->ev = (cudaEvent_t *)calloc(2 * kTimedStages * (size_t)max_samples, sizeof(cudaEvent_t));
+    s->ev_mask = (uint8_t *)calloc(max_samples, 1);
+    if (!s->ev || !s->ev_mask) return CDS_ERR_ARG;
+    for (uint32_t i = 0; i < 2 * kTimedStages * max_samples; i++) CU(cudaEventCreate(&s->ev[i]));
     s->ev_cap = max_samples;
     return CDS_OK;
 }
 
-extern "C" int cds_timing_read(cds_segment *s, float *h_ms, uint32_t cap, uint32_t *n)
+static int timing_read(cds_segment *s, uint32_t stage, float *h_ms, uint32_t cap, uint32_t *n, bool rearm)
 {
-    if (!s || !n) return CDS_ERR_ARG;
-    CU(cudaSetDevice(s->device));
-    uint32_t k = s->ev_used < cap ? s->ev_used : cap;
-    for (uint32_t i = 0; i < k; i++) {
-        CU(cudaEventSynchronize(s->ev[2 * i + 1]));
-        CU(cudaEventElapsedTime(&h_ms[i], s->ev[2 * i], s->ev[2 * i + 1]));
+    if (!s || !n || stage >= kTimedStages) return CDS_ERR_ARG;
+    ON_DEVICE(s->device);
+    uint32_t k = 0;
+    for (uint32_t i = 0; i < s->ev_used && k < cap; i++) {
+        if (!((s->ev_mask[i] >> stage) & 1u)) continue;
+        cudaEvent_t *ev = s->ev + (size_t)2 * kTimedStages * i + 2 * stage;
+        CU(cudaEventSynchronize(ev[1]));
+        CU(cudaEventElapsedTime(&h_ms[k], ev[0], ev[1]));
+        k++;
     }
     *n = k;
-    s->ev_used = 0;
+    if (rearm) s->ev_used = 0;
     return CDS_OK;
+}
+
+extern "C" int cds_timing_read(cds_segment *s, float *h_ms, uint32_t cap, uint32_t *n) { return timing_read(s, 0, h_ms, cap, n, true); }
+
+extern "C" int cds_timing_read_stage(cds_segment *s, uint32_t stage, float *h_ms, uint32_t cap, uint32_t *n)
+{
+    return timing_read(s, stage, h_ms, cap, n, false);
 }
 
 // ---- exports for the Python mirror -------------------------------------------------------------
@@ -659,7 +785,7 @@ extern "C" int cds_export_rows(cds_segment *s, uint32_t *h_rows, uint64_t cap_ro
 {
     if (!s || !n_rows || !s->have_rows) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     *n_rows = s->h_state->n_rows;
@@ -673,7 +799,7 @@ extern "C" int cds_export_layout(cds_segment *s, uint64_t *h_order, uint64_t *h_
 {
     if (!s || !s->have_plan) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     const uint64_t n_rows = s->h_state->n_rows, n_pos = s->h_state->n_pos;
@@ -700,7 +826,7 @@ extern "C" int cds_export_chunks(cds_segment *s, uint32_t *h_id, uint32_t *h_seq
 {
     if (!s || !n_chunks || !s->have_chunks) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(s->device));
+    ON_DEVICE(s->device);
     CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     const uint64_t n = s->h_state->n_chunks;
@@ -753,43 +879,89 @@ k_build_pglz_jobs(const uint8_t *__restrict__ src, const unsigned long long *__r
     }
 }
 
+// Work memory of the synchronous helper entry points (cds_pglz_decompress_batch, pglz_decompress, cds_text_etl):
+// one grow-only device allocation per (device, purpose), kept for the life of the process (cds_trim_work_memory
+// frees them), so that a steady stream of calls never reaches cudaMalloc / cudaFree.  The calls are synchronous,
+// so one lock per purpose serialises them.
+struct WorkArea {
+    uint8_t *ptr = nullptr;
+    size_t cap = 0;
+};
+enum { kWorkBatch = 0, kWorkText = 1, kWorkDatum = 2, kWorkKinds = 3 };
+static std::mutex g_work_mu[kWorkKinds];
+static WorkArea g_work[64][kWorkKinds];
+
+static cudaError_t work_reserve(int device, int kind, size_t bytes, uint8_t **out)
+{
+    WorkArea &w = g_work[device][kind];
+    if (bytes > w.cap) {
+        if (w.ptr) cudaFree(w.ptr);
+        w.ptr = nullptr;
+        w.cap = 0;
+        size_t want = bytes + bytes / 4 + 4096;                               // headroom: sizes that creep up do not reallocate every call
+        cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&w.ptr), want);
+        if (e != cudaSuccess) { w.ptr = nullptr; return e; }
+        w.cap = want;
+    }
+    *out = w.ptr;
+    return cudaSuccess;
+}
+
+extern "C" int cds_trim_work_memory(int device)
+{
+    if (device < 0 || device >= 64) return CDS_ERR_ARG;
+    if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
+    ON_DEVICE(device);
+    for (int k = 0; k < kWorkKinds; k++) {
+        std::lock_guard<std::mutex> lock(g_work_mu[k]);
+        WorkArea &w = g_work[device][k];
+        if (w.ptr) cudaFree(w.ptr);
+        w.ptr = nullptr;
+        w.cap = 0;
+    }
+    return CDS_OK;
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
 extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_src_off, void *d_dst,
                                          const uint64_t *h_dst_off, uint64_t n, int32_t *h_status, void *stream)
 {
     if (n == 0) return CDS_OK;
     if (!d_src || !h_src_off || !d_dst || !h_dst_off || n > 0x7FFFFFFFull) return CDS_ERR_ARG;
     if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
+    if (device < 0 || device >= 64) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(device));
-    // work arrays of this call: the two offset tables, one job per datum, status words + the ticket counter
-    unsigned long long *d_off = nullptr;
-    PglzJob *d_jobs = nullptr;
-    int32_t *d_stat = nullptr;
-    cudaError_t e = dalloc(&d_off, 2 * (n + 1));
-    if (e == cudaSuccess) e = dalloc(&d_jobs, n);
-    if (e == cudaSuccess) e = dalloc(&d_stat, n + 1);
-    if (e == cudaSuccess) e = cudaMemsetAsync(d_stat + n, 0, sizeof(int32_t), st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, h_src_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off + n + 1, h_dst_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
+    ON_DEVICE(device);
     // values large enough for the intra-value parallel decoder?  (room bounds rawsize from above)
-    uint8_t *d_wide = nullptr;
     bool any_wide = false;
     const uint32_t thr = g_wide_threshold;
     for (uint64_t i = 0; thr && i < n && !any_wide; i++) any_wide = h_dst_off[i + 1] - h_dst_off[i] >= (thr > kWideMinRaw ? thr : kWideMinRaw);
     uint32_t wj = 0, ws_ = 0, wb = 0;
-    if (e == cudaSuccess && any_wide) {
+    if (any_wide) {
         const uint64_t src_bytes = h_src_off[n] - h_src_off[0], dst_bytes = h_dst_off[n] - h_dst_off[0];
         const uint64_t cj = n < 65536 ? n : 65536, cs = src_bytes / kWideSeg + (cj + 1) * kWideSuper, cb = dst_bytes / kWideBlock + cj + 1;
-        if (cs < 0xFFFFFFFFull && cb < 0xFFFFFFFFull) {
-            wj = (uint32_t)cj; ws_ = (uint32_t)cs; wb = (uint32_t)cb;
-            e = dalloc(&d_wide, wide_area_bytes(wj, ws_, wb));
-            if (e == cudaSuccess) e = wide_prepare();
-        } else {
-            any_wide = false;
-        }
+        if (cs < 0xFFFFFFFFull && cb < 0xFFFFFFFFull) { wj = (uint32_t)cj; ws_ = (uint32_t)cs; wb = (uint32_t)cb; }
+        else any_wide = false;
     }
+    // work area of this call: [offset tables | jobs | status words + ticket | wide area]
+    const size_t off_bytes = align256(sizeof(uint64_t) * 2 * (n + 1)), job_bytes = align256(sizeof(PglzJob) * n),
+                 stat_bytes = align256(sizeof(int32_t) * (n + 1));
+    const size_t total = off_bytes + job_bytes + stat_bytes + (any_wide ? wide_area_bytes(wj, ws_, wb) : 0);
+    std::lock_guard<std::mutex> lock(g_work_mu[kWorkBatch]);
+    uint8_t *base = nullptr;
+    cudaError_t e = work_reserve(device, kWorkBatch, total, &base);
+    if (e != cudaSuccess) return cuda_fail(e, "cds_pglz_decompress_batch: work area");
+    unsigned long long *d_off = reinterpret_cast<unsigned long long *>(base);
+    PglzJob *d_jobs = reinterpret_cast<PglzJob *>(base + off_bytes);
+    int32_t *d_stat = reinterpret_cast<int32_t *>(base + off_bytes + job_bytes);
+    uint8_t *d_wide = base + off_bytes + job_bytes + stat_bytes;
+    e = cudaMemsetAsync(d_stat + n, 0, sizeof(int32_t), st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, h_src_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_off + n + 1, h_dst_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && any_wide) e = wide_prepare();
     if (e == cudaSuccess) {
+        const int sms = sm_count(device);
         k_build_pglz_jobs<<<(uint32_t)((n + 255) / 256), 256, 0, st>>>(static_cast<const uint8_t *>(d_src), d_off,
                                                                        static_cast<uint8_t *>(d_dst), d_off + n + 1, (uint32_t)n,
                                                                        d_jobs, d_stat, nullptr);
@@ -798,29 +970,22 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
             wa.threshold = thr;
             wa.force = g_wide_force ? 1u : 0u;
             wa.status = d_stat;
-            int sms = 148;
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
             if (launch_wide(d_jobs, nullptr, (uint32_t)n, wa, sms, st) != CDS_OK) e = cudaErrorUnknown;
         }
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
-        if (grid > 148u * 7u) grid = 148u * 7u;
+        if (grid > (uint32_t)sms * 7u) grid = (uint32_t)sms * 7u;
         k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, (uint32_t)n, d_stat, nullptr,
                                                                      reinterpret_cast<uint32_t *>(d_stat + n), nullptr, 0u);
-        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaGetLastError();
         LAUNCHED(2);
     }
     if (e == cudaSuccess && h_status) e = cudaMemcpyAsync(h_status, d_stat, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
+    WideState wc;
+    memset(&wc, 0, sizeof(wc));
+    if (e == cudaSuccess && any_wide) e = cudaMemcpyAsync(&wc, d_wide, sizeof(wc), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    if (e == cudaSuccess && any_wide) {
-        WideState wc;
-        e = cudaMemcpy(&wc, d_wide, sizeof(wc), cudaMemcpyDeviceToHost);
-        if (e == cudaSuccess) g_wide_decoded += wc.n_taken;
-    }
-    if (d_off) cudaFree(d_off);
-    if (d_jobs) cudaFree(d_jobs);
-    if (d_stat) cudaFree(d_stat);
-    if (d_wide) cudaFree(d_wide);
     if (e != cudaSuccess) return cuda_fail(e, "cds_pglz_decompress_batch");
+    g_wide_decoded += wc.n_taken;
     return CDS_OK;
 }
 
@@ -883,7 +1048,7 @@ extern "C" int cds_pglz_decompress_batch_static(int device, const void *d_src, c
     }
     if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(device));
+    ON_DEVICE(device);
     StaticScratch *sc = nullptr;
     int rc = static_scratch_for(device, &sc);
     if (rc != CDS_OK) return rc;
@@ -897,7 +1062,8 @@ extern "C" int cds_pglz_decompress_batch_static(int device, const void *d_src, c
             d_status, &sc->state);
         CU(cudaGetLastError());
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
-        if (grid > 148u * 7u) grid = 148u * 7u;
+        const uint32_t max_grid = (uint32_t)sm_count(device) * 7u;
+        if (grid > max_grid) grid = max_grid;
         k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(sc->jobs, nullptr, (uint32_t)n, d_status, &sc->state,
                                                                      &sc->state.pglz_ticket, nullptr, 0u);
         CU(cudaGetLastError());
@@ -918,14 +1084,17 @@ extern "C" void pglz_decompress(const void *source, char *dest)
     const uint32_t varsize = (((uint32_t)h[0] << 24) | ((uint32_t)h[1] << 16) | ((uint32_t)h[2] << 8) | h[3]) & 0x3FFFFFFFu;
     const uint32_t rawsize = (uint32_t)h[4] | ((uint32_t)h[5] << 8) | ((uint32_t)h[6] << 16) | ((uint32_t)h[7] << 24);
     int dev = 0;
-    if (cds_device_count() == 0 || cudaGetDevice(&dev) != cudaSuccess) {
+    if (cds_device_count() == 0 || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
         fprintf(stderr, "pglz_decompress: no CUDA device (libcds_da has no CPU path)\n");
         abort();
     }
-    uint8_t *d_src = nullptr, *d_dst = nullptr;
+    // staging buffers of this entry point: grow-only, shared by all callers (the reference calls it from one thread)
+    const size_t src_bytes = align256((size_t)(varsize < 8 ? 8 : varsize) + 16), dst_bytes = align256((size_t)rawsize + 16);
     int32_t status = CDS_ERR_CUDA;
-    cudaError_t e = dalloc(&d_src, (uint64_t)varsize + 16);
-    if (e == cudaSuccess) e = dalloc(&d_dst, (uint64_t)rawsize + 16);
+    std::lock_guard<std::mutex> lock(g_work_mu[kWorkDatum]);
+    uint8_t *base = nullptr;
+    cudaError_t e = work_reserve(dev, kWorkDatum, src_bytes + dst_bytes, &base);
+    uint8_t *d_src = base, *d_dst = base + src_bytes;
     if (e == cudaSuccess) e = cudaMemcpy(d_src, h, varsize < 8 ? 8 : varsize, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
         uint64_t so[2] = {0, varsize < 8 ? 8u : varsize}, dof[2] = {0, rawsize};
@@ -933,13 +1102,11 @@ extern "C" void pglz_decompress(const void *source, char *dest)
         if (rc != CDS_OK) status = rc;
     }
     if (e == cudaSuccess && rawsize) e = cudaMemcpy(dest, d_dst, rawsize, cudaMemcpyDeviceToHost);
-    if (d_src) cudaFree(d_src);
-    if (d_dst) cudaFree(d_dst);
     if (e != cudaSuccess) {
         fprintf(stderr, "pglz_decompress: %s\n", cudaGetErrorString(e));
         abort();
     }
-    if (status != CDS_OK) printf("compressed data is corrupt");   // pg_lzcompress.c:138-139
+    if (status != CDS_OK) { printf("compressed data is corrupt"); fflush(stdout); }   // pg_lzcompress.c:138-139
 }
 
 // ---- consumer casts ----------------------------------------------------------------------------
@@ -949,7 +1116,8 @@ extern "C" int cds_onehot_argmax_i16(const void *d_onehot, uint64_t n_rows, uint
     if (n_rows == 0) return CDS_OK;
     if (!d_onehot || !d_labels || classes == 0) return CDS_ERR_ARG;
     uint64_t blocks = (n_rows + 7) / 8;
-    if (blocks > 148ull * 16) blocks = 148ull * 16;
+    const uint64_t max_blocks = (uint64_t)current_sm_count() * 16;
+    if (blocks > max_blocks) blocks = max_blocks;
     k_onehot_argmax_i16<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const int16_t *>(d_onehot), n_rows, classes,
                                                                            static_cast<long long *>(d_labels));
     CU(cudaGetLastError());
@@ -980,9 +1148,7 @@ static int launch_assemble_tma(const void *d_images, uint64_t n_samples, uint32_
 {
     const size_t smem = (size_t)kAsmStages * tp * ch * 4u + 2 * kAsmStages * sizeof(unsigned long long) + 16;
     CU(cudaFuncSetAttribute(k_assemble_tma<TOut>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int sms = current_sm_count();
     const uint64_t total = (uint64_t)batch * (hw / tp);
     const uint32_t grid = (uint32_t)(total < (uint64_t)sms ? total : (uint64_t)sms);
     k_assemble_tma<TOut><<<grid, kAsmThreads, smem, st>>>(
@@ -1002,7 +1168,8 @@ extern "C" int cds_nhwc_to_nchw_f32(const void *d_src, uint64_t n, uint32_t hw, 
         if (tp) return launch_assemble_tma<float>(d_src, n, hw, ch, tp, nullptr, nullptr, (uint32_t)n, d_dst, nullptr, (cudaStream_t)stream);
     }
     uint64_t total = n * hw * ch, blocks = (total + 255) / 256;
-    if (blocks > 148ull * 32) blocks = 148ull * 32;
+    const uint64_t max_blocks = (uint64_t)current_sm_count() * 32;
+    if (blocks > max_blocks) blocks = max_blocks;
     k_nhwc_to_nchw_f32<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const float *>(d_src), n, hw, ch,
                                                                           static_cast<float *>(d_dst));
     CU(cudaGetLastError());
@@ -1015,7 +1182,8 @@ extern "C" int cds_f32_to_bf16(const void *d_src, uint64_t n_elems, void *d_dst,
     if (n_elems == 0) return CDS_OK;
     if (!d_src || !d_dst) return CDS_ERR_ARG;
     uint64_t blocks = (n_elems / 4 + 255) / 256 + 1;
-    if (blocks > 148ull * 32) blocks = 148ull * 32;
+    const uint64_t max_blocks = (uint64_t)current_sm_count() * 32;
+    if (blocks > max_blocks) blocks = max_blocks;
     k_f32_to_bf16<<<(uint32_t)blocks, 256, 0, (cudaStream_t)stream>>>(static_cast<const float *>(d_src), n_elems,
                                                                      static_cast<__nv_bfloat16 *>(d_dst));
     CU(cudaGetLastError());
@@ -1039,7 +1207,8 @@ extern "C" int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint
         }
     }
     uint64_t total = (uint64_t)batch * hw * ch, blocks = (total + 255) / 256;
-    if (blocks > 148ull * 32) blocks = 148ull * 32;
+    const uint64_t max_blocks = (uint64_t)current_sm_count() * 32;
+    if (blocks > max_blocks) blocks = max_blocks;
     if (out_bf16)
         k_batch_assemble<__nv_bfloat16><<<(uint32_t)blocks, 256, 0, st>>>(
             static_cast<const float *>(d_images), n_samples, hw, ch, static_cast<const long long *>(d_labels),
@@ -1067,19 +1236,20 @@ extern "C" int cds_text_etl(int device, const void *d_text, uint64_t n_bytes, ui
     if (n_bytes == 0) return CDS_OK;
     if (cds_device_count() == 0) return CDS_ERR_NO_DEVICE;
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaSetDevice(device));
+    ON_DEVICE(device);
     const uint64_t n_tiles64 = (n_bytes + kTextTile - 1) / kTextTile;
     if (n_tiles64 > 0x7FFFFFFFull) return CDS_ERR_CAPACITY;
     const uint32_t n_tiles = (uint32_t)n_tiles64, scan_tiles = n_tiles / kScanMinTile + 2;
     const uint32_t per_row = values_per_row + 2u;
-    // one allocation: [TextState | 2 tickets | 2 x status] zeroed, then counts, then scan values
-    const size_t zero_bytes = 256 + 4 * (8 + 2 * (size_t)scan_tiles);
+    // work area: [TextState | 2 tickets | 2 x status] zeroed, then counts, then scan values (grow-only, see WorkArea)
+    if (device < 0 || device >= 64) return CDS_ERR_ARG;
+    const size_t zero_bytes = align256(256 + 4 * (8 + 2 * (size_t)scan_tiles));
+    const size_t count_bytes = align256(sizeof(uint32_t) * 2 * ((size_t)n_tiles + 1)), val_bytes = align256(sizeof(unsigned long long) * 4 * (size_t)scan_tiles);
+    std::lock_guard<std::mutex> lock(g_work_mu[kWorkText]);
     uint8_t *zero = nullptr;
-    uint32_t *counts = nullptr;
-    unsigned long long *vals = nullptr;
-    cudaError_t e = dalloc(&zero, zero_bytes);
-    if (e == cudaSuccess) e = dalloc(&counts, 2 * ((size_t)n_tiles + 1));
-    if (e == cudaSuccess) e = dalloc(&vals, 4 * (size_t)scan_tiles);
+    cudaError_t e = work_reserve(device, kWorkText, zero_bytes + count_bytes + val_bytes, &zero);
+    uint32_t *counts = reinterpret_cast<uint32_t *>(zero + zero_bytes);
+    unsigned long long *vals = reinterpret_cast<unsigned long long *>(zero + zero_bytes + count_bytes);
     TextState h;
     memset(&h, 0, sizeof(h));
     if (e == cudaSuccess) e = cudaMemsetAsync(zero, 0, zero_bytes, st);
@@ -1091,7 +1261,8 @@ extern "C" int cds_text_etl(int device, const void *d_text, uint64_t n_bytes, ui
         const uint8_t *text = static_cast<const uint8_t *>(d_text);
         k_text_count<<<n_tiles, kTextThreads, 0, st>>>(text, n_bytes, tile_tokens, tile_lines);
         uint32_t sg = n_tiles / (kScanThreads * 4) + 1;
-        if (sg > 592) sg = 592;
+        const uint32_t sg_max = (uint32_t)sm_count(device) * 4u;
+        if (sg > sg_max) sg = sg_max;
         k_text_scan<<<dim3(sg, 2), kScanThreads, 0, st>>>(tile_tokens, tile_lines, n_tiles, ws0, ws1, state, n_bytes, text);
         k_text_parse<<<n_tiles, kTextThreads, 0, st>>>(text, n_bytes, tile_tokens, tile_lines, per_row, label_digits,
                                                        static_cast<float *>(d_features), static_cast<long long *>(d_labels),
@@ -1101,9 +1272,6 @@ extern "C" int cds_text_etl(int device, const void *d_text, uint64_t n_bytes, ui
         if (e == cudaSuccess) e = cudaMemcpyAsync(&h, state, sizeof(h), cudaMemcpyDeviceToHost, st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     }
-    if (zero) cudaFree(zero);
-    if (counts) cudaFree(counts);
-    if (vals) cudaFree(vals);
     if (e != cudaSuccess) return cuda_fail(e, "cds_text_etl");
     *n_rows = h.n_lines;
     if (h.err_inv) {

@@ -343,6 +343,8 @@ __device__ __forceinline__ void d_plan_rows(const PlanArgs &A)
                     if ((loc.y >> 16) >= 4u)
                         len[a] = ld_u32(A.toast + (size_t)loc.x * kPage + (loc.y & 0xFFFFu));
                 }
+                if (va_extsize >= 4u && (a == 1u || !(A.ind_bf16 | A.ind_u8norm)) && pglz_literal_only(va_extsize - 4u, len[a]))
+                    continue;                                                // literal-only stream: unpacked by the gather itself
                 A.vscr[v] = ((unsigned long long)va_extsize + 15ull) & ~15ull;
                 if (A.wide_threshold && len[a] >= A.wide_threshold) atomicAdd(&st->n_wide, 1u);
             }
@@ -465,10 +467,22 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
             const uint32_t pos = A.pos_of_row[r];
             if (ok && vb == va_extsize && fits && pos != kNone) {
                 const bool compressed = va_extsize != va_rawsize - 4u;
-                unsigned long long dst;
+                const unsigned long long rawlen = a ? A.dep_len[r] : A.ind_len[r];
                 op.src_off = loc.y & 0xFFFFu;
                 op.len = size;
-                if (compressed) {
+                if (compressed && va_extsize >= 4u && (a == 1u || !(half | quad)) && pglz_literal_only(va_extsize - 4u, rawlen)) {
+                    // literal-only pglz stream: stream bytes [s_lo, s_hi) of the value live in this chunk
+                    const unsigned long long s_lo = idx ? (unsigned long long)idx * kChunkMax - 4ull : 0ull;
+                    const uint32_t skip = idx ? 0u : 4u;                     // chunk 0 starts with the rawsize word
+                    const uint32_t n_stream = size - skip;
+                    const unsigned long long s_hi = s_lo + n_stream;
+                    const unsigned long long o_lo = s_lo - (s_lo + 8ull) / 9ull;
+                    const unsigned long long s_fin = 9ull * (((rawlen + 7ull) >> 3) - 1ull);   // control byte of the final group
+                    const uint32_t fin = (s_fin >= s_lo && s_fin < s_hi) ? (uint32_t)(rawlen & 7ull) : 0u;
+                    op.dst = (unsigned long long)((a ? A.out_dep + A.pos_dep[pos] : A.out_ind + A.pos_ind[pos]) + o_lo);
+                    op.src_off = ((loc.y & 0xFFFFu) + skip) | ((uint32_t)(s_lo % 9ull) << 16) | (fin << 20);
+                    op.len = n_stream | kOpLiteral;
+                } else if (compressed) {
                     op.dst = (unsigned long long)(A.scratch + A.vscr[v]) + (unsigned long long)idx * kChunkMax;
                 } else if (a) {
                     op.dst = (unsigned long long)(A.out_dep + A.pos_dep[pos]) + (unsigned long long)idx * kChunkMax;
@@ -521,8 +535,9 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
             } else if (A.vcount[v] != 0) {
                 const uint32_t *ptr = row + (a ? RW_DEP : RW_IND);
                 const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
-                if (va_extsize != va_rawsize - 4u) {
-                    const unsigned long long len = a ? A.dep_len[r] : A.ind_len[r];
+                const unsigned long long len = a ? A.dep_len[r] : A.ind_len[r];
+                const bool literal = va_extsize >= 4u && (a == 1u || !(half | quad)) && pglz_literal_only(va_extsize - 4u, len);
+                if (va_extsize != va_rawsize - 4u && !literal) {
                     job.err_key = make_err_key(3, A.vfirst[v], 3, 0, CDS_ERR_PGLZ_CORRUPT);
                     if (va_extsize < 4u) {
                         report_key(st, job.err_key);

@@ -481,7 +481,7 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
 // Jobs are taken through *ticket (zero at launch).  With `st_counts` the job array is the compacted
 // two-ended list k_resolve builds (n_jobs_front slots from the start, n_jobs_back from slot 2*n_rows-1
 // down): front jobs (large values) are handed out first, the small ones fill the tail.
-__global__ void __launch_bounds__(32 * kPglzWarps)
+__global__ void __launch_bounds__(32 * kPglzWarps, 7)
 k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint32_t n_jobs_host,
               int32_t *status, DevState *st, uint32_t *ticket, const float *__restrict__ lut, uint32_t lut_channels)
 {

@@ -192,8 +192,8 @@ __device__ __forceinline__ bool wide_candidate(const PglzJob &job, uint32_t thre
            (unsigned long long)(job.slen & ~kFlagBits) <= (unsigned long long)job.rawsize * 9ull / 8ull + 9ull;
 }
 
-__global__ void __launch_bounds__(1024)
-k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa)
+// (A block of 1024 threads; every thread of the block must call it.)
+__device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, const WideArea &wa)
 {
     __shared__ uint32_t sh_w[3][32];
     __shared__ uint32_t sh_base[3];
@@ -290,6 +290,22 @@ k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, 
         wa.state->n_segs = min(sh_base[1], wa.cap_segs);                     // values that fit form a prefix of the list
         wa.state->n_blks = min(sh_base[2], wa.cap_blks);
     }
+}
+
+__global__ void __launch_bounds__(1024)
+k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa)
+{
+    d_wide_classify(jobs, st_counts, n_jobs_host, wa);
+}
+
+// Clears the scan status words and the block flags behind the WideState header (the device-launched pipeline:
+// the header itself is cleared by the gate kernel before it classifies).
+__global__ void __launch_bounds__(256)
+k_wide_zero(WideArea wa)
+{
+    uint4 *p = reinterpret_cast<uint4 *>(reinterpret_cast<uint8_t *>(wa.state) + 256);
+    const uint32_t n = (wa.zero_bytes - 256u) >> 4;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 // ---- A: group starts ---------------------------------------------------------------------------------

@@ -140,9 +140,67 @@ __device__ __forceinline__ void copy_payload_u8norm(const uint8_t *src, float *d
     if (tid < len - done) dst[done + tid] = lut[((phase + done + tid) % ch) * 256u + src[done + tid]];
 }
 
+// Part of a literal-only pglz stream (see kOpLiteral): `n` stream bytes at shared `src`, the first one at stream
+// offset = phase (mod 9).  Stream byte s is a control byte when s % 9 == 0 (must be zero: a set bit would announce a
+// tag, which a stream of this length cannot hold, ppr:203-230) and literal number (s / 9) * 8 + s % 9 - 1 otherwise.
+// Writes the literals to `dst` (the address of the first literal in this part); returns false when a control byte is
+// not zero.  `fin`: 1..7 = only that many low bits of the LAST control byte of this part count.
+__device__ __forceinline__ bool copy_payload_literal(const uint8_t *src, uint8_t *dst, uint32_t n, uint32_t phase, uint32_t fin,
+                                                     uint32_t tid, uint32_t nth)
+{
+    bool good = true;
+    const uint32_t c0 = phase ? 9u - phase : 0u;                             // first control byte inside the part
+    const uint32_t n_ctrl = n > c0 ? (n - c0 + 8u) / 9u : 0u;
+    for (uint32_t i = tid; i < n_ctrl; i += nth) {
+        uint32_t b = src[c0 + 9u * i];
+        if (fin && i + 1u == n_ctrl) b &= (1u << fin) - 1u;
+        good = good && b == 0u;
+    }
+    const uint32_t n_out = n - n_ctrl;
+    const uint32_t q = phase ? phase - 1u : 0u;                              // literal index of the first output byte inside its group
+    // output byte j of this part = literal O = q + j counted from the group's first literal -> src[(O / 8) * 9 + O % 8 + 1 - phase]
+    const uintptr_t da = reinterpret_cast<uintptr_t>(dst);
+    if (((da - q) & 7u) != 0u) {                                             // groups do not line up with 8-byte words of the output
+        for (uint32_t j = tid; j < n_out; j += nth) {
+            const uint32_t O = q + j;
+            dst[j] = src[(O >> 3) * 9u + (O & 7u) + 1u - phase];
+        }
+        return good;
+    }
+    uint32_t head = (16u - (uint32_t)(da & 15u)) & 15u;
+    if (head > n_out) head = n_out;
+    if (tid < head) {
+        const uint32_t O = q + tid;
+        dst[tid] = src[(O >> 3) * 9u + (O & 7u) + 1u - phase];
+    }
+    const uint32_t nvec = (n_out - head) >> 4, m0 = (q + head) >> 3;         // q + head is a multiple of 8 here
+    uint4 *d16 = reinterpret_cast<uint4 *>(dst + head);
+    for (uint32_t v = tid; v < nvec; v += nth) {
+        // two groups: literals at src[a .. a+8) and src[a+9 .. a+17)
+        const uint32_t a = smem_u32(src) + (m0 + 2u * v) * 9u + 1u - phase, b = a + 9u;
+        const uint32_t a4 = a & ~3u, b4 = b & ~3u, sa = (a & 3u) * 8u, sb = (b & 3u) * 8u;
+        uint32_t x0, x1, x2, y0, y1, y2;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(x0) : "r"(a4));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(x1) : "r"(a4 + 4u));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(x2) : "r"(a4 + 8u));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(y0) : "r"(b4));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(y1) : "r"(b4 + 4u));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(y2) : "r"(b4 + 8u));
+        st_stream_v4(d16 + v, make_uint4(__funnelshift_r(x0, x1, sa), __funnelshift_r(x1, x2, sa),
+                                         __funnelshift_r(y0, y1, sb), __funnelshift_r(y1, y2, sb)));
+    }
+    const uint32_t done = head + (nvec << 4);
+    if (tid < n_out - done) {
+        const uint32_t O = q + done + tid;
+        dst[done + tid] = src[(O >> 3) * 9u + (O & 7u) + 1u - phase];
+    }
+    return good;
+}
+
 __global__ void __launch_bounds__(kGatherThreads, 1)
 k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32_t *__restrict__ base,
-               const CopyOp *__restrict__ ops, const DevState *__restrict__ st, const float *__restrict__ lut, uint32_t lut_channels)
+               const CopyOp *__restrict__ ops, DevState *st, const float *__restrict__ lut, uint32_t lut_channels,
+               const uint32_t *__restrict__ dir_ref, const uint32_t *__restrict__ vfirst)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *stage_buf = smem;
@@ -194,7 +252,15 @@ k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32
             for (uint32_t j = 0; j < n; j++) {
                 const CopyOp op = j < (uint32_t)kGatherMaxStageOps ? stage_ops[s * kGatherMaxStageOps + j] : ops[g0 + j];
                 if (op.dst == 0 || op.len == 0) continue;
-                if (op.len & kOpToBf16) copy_payload_bf16(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len & ~kFlagBits, ctid, cnth);
+                if (op.len & kOpLiteral) {
+                    if (!copy_payload_literal(pg + (op.src_off & 0xFFFFu), reinterpret_cast<uint8_t *>(op.dst), op.len & 0xFFFFu,
+                                              (op.src_off >> 16) & 15u, (op.src_off >> 20) & 7u, ctid, cnth)) {
+                        // "compressed data is corrupt" for this value (ppr:229-230), the key the pglz decoder would publish
+                        const uint32_t v = dir_ref[g0 + j] & 0x3FFFFFFFu;
+                        report(st, 3, vfirst[v], 3, 0, CDS_ERR_PGLZ_CORRUPT);
+                    }
+                }
+                else if (op.len & kOpToBf16) copy_payload_bf16(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len & ~kFlagBits, ctid, cnth);
                 else if (op.len & kOpU8Norm) copy_payload_u8norm(pg + (op.src_off & 0xFFFFu), reinterpret_cast<float *>(op.dst), op.len & ~kFlagBits,
                                                                 op.src_off >> 16, lut_channels, lut_s, ctid, cnth);
                 else copy_payload(pg + op.src_off, reinterpret_cast<uint8_t *>(op.dst), op.len, ctid, cnth);

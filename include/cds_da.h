@@ -67,6 +67,7 @@ typedef struct cds_summary {
 
 /* ---- library ------------------------------------------------------------------------------ */
 int cds_version(void);
+uint32_t cds_summary_size(void);                /* sizeof(cds_summary) as the library was built: bindings check their mirror */
 const char *cds_status_str(int status);
 const char *cds_last_error(void);               /* text of the last CUDA failure in this thread */
 int cds_device_count(void);
@@ -152,13 +153,18 @@ int cds_decode_host(cds_segment *seg, const void *h_heap_pages, uint64_t n_heap_
 
 /* ---- measurement hooks (bench.py) ------------------------------------------------------------ */
 
-/* Kernels launched by this library in this process so far. */
+/* Kernels launched from the host by this library in this process so far (kernels that k_decode_gate launches
+ * from the device are not counted). */
 unsigned long long cds_launch_count(void);
-/* Record a CUDA-event pair on the launching stream around the gather kernel of the next
- * `max_samples` cds_materialize calls (0 disables); cds_timing_read waits for them and returns the
- * durations in milliseconds, then rearms. */
+/* Record CUDA-event pairs on the launching stream inside the next `max_samples` cds_materialize / cds_decode_*
+ * calls (0 disables).  Stages: 0 = the gather kernel; 1 = the pglz stage (classification, wide decoder, warp
+ * decoder: with device-side launches the pair brackets the parent launch, whose completion includes its children);
+ * 2, 3 = the two block passes of the wide decoder (host-launched modes of cds_set_wide_pglz only).
+ * cds_timing_read_stage waits for the samples of one stage and returns their durations in milliseconds;
+ * cds_timing_read does the same for stage 0 and then rearms (call it last). */
 int cds_timing_enable(cds_segment *seg, uint32_t max_samples);
 int cds_timing_read(cds_segment *seg, float *h_ms, uint32_t cap, uint32_t *n);
+int cds_timing_read_stage(cds_segment *seg, uint32_t stage, float *h_ms, uint32_t cap, uint32_t *n);
 
 /* ---- results for the Python mirror of the reader interface (synchronous, small) ------------ */
 
@@ -183,7 +189,10 @@ int cds_export_chunks(cds_segment *seg, uint32_t *h_chunk_id, uint32_t *h_chunk_
 /* Batch pglz_decompress (ppr:191-231, pg_lzcompress.c:49-143) on device buffers: datum i is the
  * varlena (8-byte header + stream) at d_src + src_off[i], src_off[i+1]-src_off[i] bytes long,
  * decoded to d_dst + dst_off[i] (dst_off[i+1]-dst_off[i] bytes of room).  h_status[i] receives
- * CDS_OK or CDS_ERR_PGLZ_CORRUPT.  Offsets are host arrays of n+1 entries.  Synchronous. */
+ * CDS_OK or CDS_ERR_PGLZ_CORRUPT.  Offsets are host arrays of n+1 entries.  Synchronous.
+ * Its work memory (and that of pglz_decompress and cds_text_etl) is one grow-only device allocation per
+ * device, kept between calls: repeated calls of the same size never reach cudaMalloc.  Calls are
+ * serialised by a lock. */
 int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_src_off, void *d_dst,
                               const uint64_t *h_dst_off, uint64_t n, int32_t *h_status, void *stream);
 
@@ -196,12 +205,17 @@ int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_s
  * (default 1 MiB; 0 switches the wide decoder off; values under 1024 bytes never take it);
  * skip_cost_model != 0 sends every value at or above the threshold through it (tests, measurements). */
 int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model);
-/* Per handle: 0 = never launch the wide decoder, 1 = always launch it and skip the cost model, 2 = automatic
- * (default): launch it (14 small kernels that find no work when nothing qualifies) when the plan counted large
- * values.  In the step-by-step flow that is this decode's own plan (cds_plan + cds_finish before
- * cds_materialize); the one-call entry points have no host sync before the decode and go by the last summary
- * read on the handle (a handle that has not produced a summary yet launches them). */
+/* Per handle: how the pglz stage of a decode is launched.
+ *   2 (default) = decided on the device for THIS decode: one small kernel after the gather classifies the job
+ *       list and launches from the device what the decode needs — the wide pipeline if values go wide, the warp
+ *       decoder if there are compressed values at all.  No state is carried from one decode to the next.
+ *   0 = warp decoder only, host-launched.
+ *   1 = wide pipeline + warp decoder host-launched (14 + 1 kernels), every value at or above the threshold goes
+ *       wide (tests, measurements).
+ *   3 = as 1 but with the cost model (profilers that do not follow device-side launches). */
 int cds_set_wide_pglz(cds_segment *seg, int mode);
+/* Frees the cached work memory of cds_pglz_decompress_batch / pglz_decompress / cds_text_etl on `device`. */
+int cds_trim_work_memory(int device);
 /* Measurement hook: values decoded by the wide decoder so far in this process (counted when a decode's
  * summary is read / a batch call returns). */
 unsigned long long cds_wide_decoded_count(void);
@@ -209,16 +223,21 @@ unsigned long long cds_wide_decoded_count(void);
 /* No counterpart in the reference.  cds_pglz_decompress_batch for callers that are not allowed to
  * allocate device memory while they decode — a loader thread beside a framework that has claimed the
  * whole GPU memory pool, a latency-sensitive ingest loop in which an allocation could stall the device,
- * a process with a hard memory budget.  Same decoding, same per-datum status, but every pointer is a DEVICE pointer the
+ * a process with a hard memory budget.  Same bytes, same per-datum status, always one warp per datum (the
+ * intra-value parallel decoder needs a work area that grows with the data, so it is never used here: a value of
+ * hundreds of megabytes takes seconds on its warp — send those through a segment handle).  Every pointer is a DEVICE pointer the
  * caller already owns (offsets are uint64[n+1] on the device; d_status int32[n]; d_first_corrupt, if
  * not NULL, receives the index of the first corrupt datum or -1) and the work area is an array built
  * into the library (one copy, ~128 KB, on every GPU that loads it, held until the process exits).
  * Limits and rules:
  *   - at most CDS_STATIC_MAX_DATUMS datums per call; more is refused with CDS_ERR_CAPACITY and a
  *     message in cds_last_error();
- *   - the call only enqueues work on `stream` (memset + kernels) and never calls cudaMalloc/cudaFree;
+ *   - the call only enqueues work on `stream` (memset + kernels) and never calls cudaMalloc/cudaFree (the
+ *     CUDA runtime itself may allocate when a device is first used or the module is first loaded: make the
+ *     first call per device at start-up);
  *   - the first call on a device looks up the work area's address (cudaGetSymbolAddress, with that
- *     device current): make that first call outside any stream capture;
+ *     device current): make that first call outside any stream capture.  The address is cached for the life
+ *     of the process: do not call again after cudaDeviceReset;
  *   - all calls on a device share the one work area: two calls whose kernels can overlap on the GPU
  *     (different streams, no dependency) race with each other — serialise them. */
 #define CDS_STATIC_MAX_DATUMS 4096u
