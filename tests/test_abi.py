@@ -39,6 +39,21 @@ def test_ctypes_prototypes_cover_header(lib_path):
     assert L.cds_status_str(1) == b"FATAL"
 
 
+def test_documented_summary_binding_matches_the_library(lib_path):
+    """The Summary struct printed in INTEGRATION.md §2 is what a maintainer pastes: it must have the size the
+    library writes (cds_finish fills the whole cds_summary)."""
+    import ctypes
+    from cerebro_ds_kpgi_b200 import _lib
+    L = _lib.load()
+    text = open(os.path.join(REPO, "INTEGRATION.md")).read()
+    m = re.search(r"class Summary\(ctypes\.Structure\):\n(?:    .*\n|\s*\[.*\n)+", text)
+    assert m, "INTEGRATION.md no longer shows the Summary binding"
+    ns = {"ctypes": ctypes}
+    exec(m.group(0), ns)
+    assert ctypes.sizeof(ns["Summary"]) == L.cds_summary_size() == ctypes.sizeof(_lib.Summary) == 80
+    assert [f[0] for f in ns["Summary"]._fields_] == [f[0] for f in _lib.Summary._fields_]
+
+
 def test_no_cpu_fallback(lib_path):
     """Without a CUDA device every compute entry point must fail loudly."""
     import ctypes

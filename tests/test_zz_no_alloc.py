@@ -99,6 +99,16 @@ def test_static_entry_point_matches_regular_one_on_two_calls_in_a_row():
     assert out_a.tobytes() == out_b.tobytes()
     assert first_bad == -1
 
+    # ---- call 3: the known-answer vectors alone, against the bytes BOTH reference decoders produced for them
+    # (tests/golden/pglz_kat.npz `raw`), not only against the other entry point
+    st_a, out_a, st_b, out_b, first_bad, dst_off = _run_both(torch, L, kat)
+    assert not st_b.any() and first_bad == -1
+    ro = z["raw_off"]
+    for i in range(len(kat)):
+        want = z["raw"][ro[i]:ro[i + 1]].tobytes()
+        o = int(dst_off[i])
+        assert out_b[o:o + len(want)].tobytes() == want, i
+
     # ---- size limit: refused before anything is enqueued, with a message that names the limit
     dummy = torch.zeros(64, dtype=torch.uint8, device="cuda")
     offs = torch.zeros(MAX_DATUMS + 2, dtype=torch.int64, device="cuda")
