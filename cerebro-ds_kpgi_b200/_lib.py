@@ -78,6 +78,8 @@ PROTOTYPES = {
     "cds_onehot_argmax_i16": (_int, [_vp, _u64, _u32, _vp, _vp]),
     "cds_nhwc_to_nchw_f32": (_int, [_vp, _u64, _u32, _u32, _vp, _vp]),
     "cds_f32_to_bf16": (_int, [_vp, _u64, _vp, _vp]),
+    "cds_checksum64": (_int, [_vp, _u64, _vp, _vp]),
+    "cds_peer_copy": (_int, [_vp, _vp, _u64, _vp]),
     "cds_text_etl": (_int, [_int, _vp, _u64, _u32, _u32, _vp, _vp, _vp, _u64, _pu64, _pu64, _vp]),
     "cds_batch_assemble": (_int, [_vp, _u64, _u32, _u32, _vp, _vp, _u32, _vp, _int, _vp, _vp]),
 }

@@ -17,6 +17,7 @@
 #include "pglz_wide.cuh"
 #include "text_etl.cuh"
 #include "toast_gather.cuh"
+#include "util_kernels.cuh"
 
 using namespace cds;
 
@@ -1219,6 +1220,36 @@ extern "C" int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint
             static_cast<const float *>(d_images), n_samples, hw, ch, static_cast<const long long *>(d_labels),
             static_cast<const long long *>(d_indices), batch, static_cast<float *>(d_out),
             static_cast<long long *>(d_out_labels));
+    CU(cudaGetLastError());
+    LAUNCHED(1);
+    return CDS_OK;
+}
+
+// ---- checksum (bench.py's correctness gate) and the model hopper's state copy ------------------------
+
+extern "C" int cds_checksum64(const void *d_buf, uint64_t n_bytes, uint64_t *d_out, void *stream)
+{
+    if (!d_out || (!d_buf && n_bytes)) return CDS_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaMemsetAsync(d_out, 0, sizeof(uint64_t), st));
+    if (n_bytes == 0) return CDS_OK;
+    uint64_t blocks = (n_bytes / 8 + 255) / 256 + 1;
+    const uint64_t max_blocks = (uint64_t)current_sm_count() * 8;
+    if (blocks > max_blocks) blocks = max_blocks;
+    k_checksum64<<<(uint32_t)blocks, 256, 0, st>>>(static_cast<const uint8_t *>(d_buf), n_bytes, reinterpret_cast<unsigned long long *>(d_out));
+    CU(cudaGetLastError());
+    LAUNCHED(1);
+    return CDS_OK;
+}
+
+extern "C" int cds_peer_copy(const void *d_src, void *d_dst, uint64_t n_bytes, void *stream)
+{
+    if (n_bytes == 0) return CDS_OK;
+    if (!d_src || !d_dst) return CDS_ERR_ARG;
+    uint64_t blocks = (n_bytes / 16 + 511) / 512 + 1;
+    const uint64_t max_blocks = (uint64_t)current_sm_count() * 4;
+    if (blocks > max_blocks) blocks = max_blocks;
+    k_peer_copy<<<(uint32_t)blocks, 512, 0, (cudaStream_t)stream>>>(static_cast<const uint8_t *>(d_src), static_cast<uint8_t *>(d_dst), n_bytes);
     CU(cudaGetLastError());
     LAUNCHED(1);
     return CDS_OK;

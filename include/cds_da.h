@@ -270,6 +270,20 @@ int cds_batch_assemble(const void *d_images, uint64_t n_samples, uint32_t hw, ui
                        const void *d_labels, const void *d_indices, uint32_t batch, void *d_out, int out_bf16,
                        void *d_out_labels, void *stream);
 
+/* ---- checksum and model-state copy ------------------------------------------------------------ */
+
+/* Order-sensitive 64-bit checksum of a device buffer into *d_out (device memory): the sum over its 64-bit
+ * little-endian words w_i (tail zero-padded) of w_i * (2 i + 1) * 0x9E3779B97F4A7C15 modulo 2^64.  bench.py compares it
+ * with the same sum over the arrays the segment generator packed (the reference's result compared as a whole,
+ * run_da_cerebro_standalone.py:38-56 consumes exactly these bytes). */
+int cds_checksum64(const void *d_buf, uint64_t n_bytes, uint64_t *d_out, void *stream);
+
+/* The model hopper's transfer (the reference moves the flat float32 state of
+ * madlib_keras_wrapper.py:119-131 between workers as files, ctq.py:330-333,404-405): copies n_bytes from a buffer
+ * on the current device to d_dst, which may be another GPU's buffer mapped into this process (symmetric memory /
+ * CUDA IPC).  One kernel of plain 16-byte loads and stores over NVLink; enqueues on `stream`. */
+int cds_peer_copy(const void *d_src, void *d_dst, uint64_t n_bytes, void *stream);
+
 /* ---- text ETL ("next" row f-4) ---------------------------------------------------------------- */
 
 /* The parser of the filesystem ETL (etl_imagenet.py:30-37 `parser`, etl_criteo.py:28-37) for gpfdist
