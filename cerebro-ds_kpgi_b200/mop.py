@@ -14,6 +14,7 @@ moves instead: `torch.distributed` point-to-point send/recv of the flat buffer â
 NVLink/NVSwitch on the GPU box, gloo in the CPU tests.  The decode path itself has no
 collective; this module is the only place ranks talk to each other.
 """
+import ctypes
 import random
 
 import numpy as np
@@ -99,12 +100,21 @@ def moves_between(prev_round, next_round):
 class ModelHopper:
     """Moves flat model states between ranks according to a schedule.
 
-    One rank = one GPU = one resident partition.  `home[m]` is the rank that holds model m before the
-    first round (rank m by default).  `states` maps model -> flat float32 tensor for the models this rank
-    currently holds; buffers of arriving models are allocated once per model size and reused.
+    One rank = one GPU = one resident partition.  `location[m]` is the rank that holds model m (rank m % world
+    before the first round).  `states` maps model -> flat float32 tensor for the models this rank currently holds.
+
+    Transports:
+      "p2p"   `torch.distributed` batch_isend_irecv of the flat buffer (NCCL on GPUs, gloo in the CPU tests);
+              receive buffers come from a per-size free list, so a steady run allocates nothing.
+      "symm"  GPUs of one node: every rank owns an inbox of `n_models + 1` state-sized slots in symmetric memory
+              (`torch.distributed._symmetric_memory`), mapped into every peer.  A hop is ONE copy kernel
+              (libcds_da `cds_peer_copy`: plain 16-byte stores over NVLink into the destination's free slot)
+              followed by the symmetric-memory barrier; the model then trains in place in that slot.  Which slot is
+              free is bookkeeping every rank replays identically from the schedule, so no message is needed.
+      "auto"  "symm" on CUDA devices when the rendezvous succeeds, else "p2p" (`transport_note` says why).
     """
 
-    def __init__(self, rank, world_size, state_numel, device=None, schedule=None, group=None):
+    def __init__(self, rank, world_size, state_numel, device=None, schedule=None, group=None, transport="auto", p2p_chunks=1):
         import torch
         self.rank, self.world = rank, world_size
         self.numel = dict(state_numel) if isinstance(state_numel, dict) else {m: int(state_numel) for m in range(world_size)}
@@ -115,44 +125,131 @@ class ModelHopper:
         self.location = {m: m % world_size for m in self.numel}          # model -> rank, before round 0
         self.round = -1
         self.bytes_moved = 0
+        self.p2p_chunks = max(1, int(p2p_chunks))
         self._torch = torch
+        self._free = {}                                                   # p2p: numel -> [spare receive buffers]
+        self.transport, self.transport_note = "p2p", ""
+        is_cuda = str(self.device).startswith("cuda")
+        if transport == "symm" or (transport == "auto" and is_cuda and world_size > 1):
+            try:
+                self._init_symm()
+                self.transport = "symm"
+            except Exception as e:  # noqa
+                if transport == "symm":
+                    raise
+                self.transport_note = "symmetric memory unavailable (%s): torch.distributed send/recv" % str(e).splitlines()[0][:160]
+
+    # ---- symmetric-memory transport ---------------------------------------------------------------
+    def _init_symm(self):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        torch = self._torch
+        self._L = _lib.require_device()
+        self._slot_numel = (max(self.numel.values()) + 63) & ~63          # slots stay 256-byte aligned
+        n_slots = len(self.numel) + 1
+        inbox = symm.empty(n_slots * self._slot_numel, dtype=torch.float32, device=self.device)
+        group = self.group if self.group is not None else dist.group.WORLD
+        try:
+            hdl = symm.rendezvous(inbox, group)
+        except Exception:  # noqa  (older releases want the group enabled first)
+            symm.enable_symm_mem_for_group(group.group_name)
+            hdl = symm.rendezvous(inbox, group)
+        self._inbox, self._hdl = inbox, hdl
+        self._peer_ptr = [int(p) for p in hdl.buffer_ptrs]
+        # slot bookkeeping, replayed identically on every rank
+        self._slot_of = {}
+        self._free_slots = {r: list(range(n_slots)) for r in range(self.world)}
+        for m in sorted(self.numel):
+            self._slot_of[m] = self._free_slots[self.location[m]].pop(0)
+
+    def _slot_view(self, slot, numel):
+        o = slot * self._slot_numel
+        return self._inbox[o:o + numel]
 
     def add_local_model(self, model, flat):
         assert self.location[model] == self.rank and flat.dtype == self._torch.float32
+        if self.transport == "symm":
+            view = self._slot_view(self._slot_of[model], self.numel[model])
+            view.copy_(flat)
+            flat = view
         self.states[model] = flat
 
     def model_for_round(self, r):
         """Model this rank trains in round r (None: idle)."""
         return self.schedule[r].get(self.rank)
 
+    def _moves(self, r):
+        target = {m: p for p, m in self.schedule[r].items()}
+        return target, [(m, self.location[m], target[m]) for m in sorted(target) if self.location[m] != target[m]]
+
     def hop_to(self, r):
         """Bring every model to the rank round r needs it on.  Returns the model this rank now trains."""
+        target, moves = self._moves(r)
+        if moves:
+            if self.transport == "symm":
+                self._hop_symm(moves)
+            else:
+                self._hop_p2p(moves)
+        for m, p in target.items():
+            self.location[m] = p
+        self.round = r
+        return self.schedule[r].get(self.rank)
+
+    def _hop_symm(self, moves):
+        from . import _lib
+        torch = self._torch
+        stream = torch.cuda.current_stream()
+        sp = ctypes.c_void_p(stream.cuda_stream)
+        freed, arrived = [], []
+        for m, src, dst in moves:
+            slot = self._free_slots[dst].pop(0)
+            if src == self.rank:
+                cur = self.states.pop(m)
+                _lib.check(self._L.cds_peer_copy(ctypes.c_void_p(cur.data_ptr()),
+                                                 ctypes.c_void_p(self._peer_ptr[dst] + 4 * slot * self._slot_numel),
+                                                 4 * self.numel[m], sp))
+                self.bytes_moved += 4 * self.numel[m]
+            if dst == self.rank:
+                arrived.append((m, slot))
+            freed.append((src, self._slot_of[m]))
+            self._slot_of[m] = slot
+        self._hdl.barrier(channel=0)                                      # every copy of this hop has landed
+        for src, slot in freed:
+            self._free_slots[src].append(slot)                            # reusable from the next hop on
+        for m, slot in arrived:
+            self.states[m] = self._slot_view(slot, self.numel[m])
+
+    def _hop_p2p(self, moves):
         import torch.distributed as dist
         torch = self._torch
-        target = {m: p for p, m in self.schedule[r].items()}
         ops, arriving, leaving = [], {}, []
-        for m in sorted(target):
-            src, dst = self.location[m], target[m]
-            if src == dst:
-                continue
+        for m, src, dst in moves:
             if src == self.rank:
-                ops.append(dist.P2POp(dist.isend, self.states[m], dst, self.group))
+                buf = self.states[m]
                 leaving.append(m)
+                fn, peer = dist.isend, dst
             elif dst == self.rank:
-                buf = torch.empty(self.numel[m], dtype=torch.float32, device=self.device)
+                spare = self._free.get(self.numel[m])
+                buf = spare.pop() if spare else torch.empty(self.numel[m], dtype=torch.float32, device=self.device)
                 arriving[m] = buf
-                ops.append(dist.P2POp(dist.irecv, buf, src, self.group))
+                fn, peer = dist.irecv, src
+            else:
+                continue
+            k = min(self.p2p_chunks, max(1, buf.numel()))
+            step = -(-buf.numel() // k)
+            for c in range(k):
+                part = buf[c * step:(c + 1) * step]
+                if part.numel():
+                    ops.append(dist.P2POp(fn, part, peer, self.group))
         if ops:
             for req in dist.batch_isend_irecv(ops):
                 req.wait()
         for m in leaving:
             self.bytes_moved += 4 * self.numel[m]
-            del self.states[m]
+            gone = self.states.pop(m)
+            self._free.setdefault(gone.numel(), []).append(gone)          # becomes a receive buffer of a later hop
         self.states.update(arriving)
-        for m, p in target.items():
-            self.location[m] = p
-        self.round = r
-        return self.schedule[r].get(self.rank)
 
     def run_epoch(self, train_fn):
         """`train_fn(model, flat_state, round)` is called once per round on the model resident here;

@@ -158,6 +158,13 @@ class DeviceSegment:
         _lib.check(self.L.cds_timing_read(self._h, _ptr(ms), cap, ctypes.byref(n)))
         return ms[:n.value].copy()
 
+    def timing_read_stage(self, stage, cap=4096):
+        """Durations (ms) of one timed stage (0 gather, 1 pglz stage, 2 / 3 the wide block passes); call before timing_read."""
+        ms = np.zeros(cap, dtype=np.float32)
+        n = ctypes.c_uint32()
+        _lib.check(self.L.cds_timing_read_stage(self._h, int(stage), _ptr(ms), cap, ctypes.byref(n)))
+        return ms[:n.value].copy()
+
     # ---- exports --------------------------------------------------------------------------
     def rows(self, stream=None):
         out = np.zeros((self.cap_rows, ROW_WORDS), dtype=np.uint32)
