@@ -12,6 +12,7 @@
 #include "tma_helpers.cuh"
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 // One warp per row; first maximum wins, as np.argmax.  Rows whose bytes are 16-byte aligned are read
 // eight classes per lane and load.
@@ -205,4 +206,5 @@ k_assemble_tma(const float *__restrict__ images, unsigned long long n_samples, u
     }
 }
 
+}  // namespace
 }  // namespace cds

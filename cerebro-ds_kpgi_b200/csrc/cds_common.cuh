@@ -6,6 +6,7 @@
 #include "cds_da.h"
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 constexpr uint32_t kPage = CDS_BLCKSZ;          // 32 KB Greenplum page           (ppr:34)
 constexpr uint32_t kPageHdr = 24;               // PAGE_HEADER_LEN                (ppr:36)
@@ -272,4 +273,5 @@ __device__ inline T device_exclusive_scan(LoadFn load, T *out, uint32_t n, ScanW
     return grand;
 }
 
+}  // namespace
 }  // namespace cds

@@ -362,6 +362,8 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
     if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&s->h_state), sizeof(DevState), cudaHostAllocPortable);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_toast_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGatherSmemBytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
+    // (launched from the device too: state the shared-memory split instead of leaving it to the launch path)
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) e = wide_prepare();
     if (e == cudaSuccess) {
         int coop = 0, per_sm = 0;

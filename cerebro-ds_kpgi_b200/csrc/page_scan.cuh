@@ -16,6 +16,7 @@
 #include "cds_common.cuh"
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 // Shared by the heap and the TOAST relation: item count per page from pd_lower, device-wide
 // exclusive scan into base[0..n_pages], validation of the header.
@@ -593,4 +594,5 @@ __global__ void __launch_bounds__(256) k_plan_fused(const PlanArgs A, int do_res
     }
 }
 
+}  // namespace
 }  // namespace cds

@@ -30,6 +30,7 @@
 #include "cds_common.cuh"
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 constexpr uint32_t kRing = 8192;              // bytes of output history per warp (power of two)
 constexpr uint32_t kFlushAt = 2048;           // flush to HBM once this many bytes are pending
@@ -515,4 +516,5 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
     }
 }
 
+}  // namespace
 }  // namespace cds

@@ -41,6 +41,7 @@
 #include "cds_common.cuh"
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 constexpr uint32_t kWideSeg = 512;                 // source bytes per segment
 constexpr uint32_t kWideChunkSegs = 8;             // segments per k_wide_maps step (one per warp)
@@ -999,4 +1000,5 @@ k_wide_tails(WideArea wa)
     }
 }
 
+}  // namespace
 }  // namespace cds

@@ -19,6 +19,7 @@
 #include "cds_common.cuh"
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 constexpr uint32_t kTextTile = 4096;          // characters per CTA tile
 constexpr uint32_t kTextThreads = 256;        // 16 characters per thread
@@ -290,4 +291,5 @@ k_text_parse(const uint8_t *__restrict__ text, unsigned long long n, const uint3
     }
 }
 
+}  // namespace
 }  // namespace cds

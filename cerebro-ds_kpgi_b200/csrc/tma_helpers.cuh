@@ -3,6 +3,7 @@
 #include <stdint.h>
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -38,4 +39,5 @@ __device__ __forceinline__ void tma_load_bulk(void *smem_dst, const void *gsrc, 
                  : "memory");
 }
 
+}  // namespace
 }  // namespace cds

@@ -20,6 +20,7 @@
 #include "tma_helpers.cuh"
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 constexpr int kGatherStages = 6;
 constexpr int kGatherConsumerWarps = 16;
@@ -271,4 +272,5 @@ k_toast_gather(const uint8_t *__restrict__ pages, uint32_t n_pages, const uint32
     }
 }
 
+}  // namespace
 }  // namespace cds

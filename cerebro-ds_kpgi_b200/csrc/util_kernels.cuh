@@ -7,6 +7,7 @@
 #include "cds_common.cuh"
 
 namespace cds {
+namespace {   // internal linkage: with relocatable device code (-rdc) the optimiser then treats the file as a whole program
 
 constexpr unsigned long long kSumMul = 0x9E3779B97F4A7C15ull;
 
@@ -68,4 +69,5 @@ k_peer_copy(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, unsigned
     if (tid < n_bytes - done) dst[done + tid] = src[done + tid];
 }
 
+}  // namespace
 }  // namespace cds

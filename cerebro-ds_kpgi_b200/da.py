@@ -55,8 +55,11 @@ def _decode_files(table_page_path, toast_page_path, ind_sample_bytes=0, dep_samp
     logs("END READING TOAST: {}".format(toast_page_path))
     logs("START DETOASTING")
     status, part = _segment.decode_pages(d_heap, d_toast, ind_sample_bytes=ind_sample_bytes,
-                                         dep_sample_bytes=dep_sample_bytes, ind_bf16=ind_bf16, u8_normalize=u8_normalize)
+                                         dep_sample_bytes=dep_sample_bytes, ind_bf16=ind_bf16, u8_normalize=u8_normalize,
+                                         want_chunk_ids=pg_page_reader.LOG_VALUE_IDS)
     torch.cuda.synchronize()
+    if pg_page_reader.LOG_VALUE_IDS and status == 0:
+        pg_page_reader._log_value_markers(part, part.rows)          # ppr:554, 600-603
     # reference order of failures: heap scan, short heap page, TOAST walk, short TOAST page, detoast
     stage = part.summary.err_stage if status else 99
     if status and stage == 0:

@@ -56,7 +56,12 @@ ItemIdentifier = namedtuple('ItemIdentifier', ['lp_off', 'lp_flags', 'lp_len'])
 Tuple = namedtuple('Tuple', ['header', 'length', 'dummy1', 'dummy2', 'va_rawsize', 'va_extsize', 'va_valueid',
                              'va_toastrelid', 'external', 'bytea'])
 
-LOG_VALUE_IDS = False                 # the reference prints "ID:<valueid>" per value (ppr:554); off by default
+# The reference prints three markers per external value while it detoasts (ppr:554, 600-603; parsed by
+# plots/data_analytics.py): "ID:<valueid>", "START DECOMPRESSING", "END DECOMPRESSING".  Here all values of a
+# segment are decoded by one batch of kernels, so there is no per-value moment to stamp; with LOG_VALUE_IDS = True
+# the same lines are printed after the decode, in the reference's order (first-seen physical TOAST order), so that
+# log parsers keep working (every value then shows the same second).  Off by default: it is one line per value.
+LOG_VALUE_IDS = False
 
 
 def logs(message):
@@ -333,17 +338,60 @@ def table_page_read(page_dir):
     return df_data, df_toast
 
 
+def _file_of_page(filename):
+    """[(first page, pages)] per file of the relation, for the per-file positions debug=True prints (ppr:380-381)."""
+    import os
+    out, first = [], 0
+    for f in relation_files(filename):
+        n = os.path.getsize(f) // BLOCK_SIZE
+        out.append((first, n))
+        first += n
+    return out
+
+
+def _debug_page(host, page, spans):
+    """What the reference holds per page when debug=True: prints "PAGE: <position in its file>" (ppr:380-381) and
+    returns (page_bytes, PageHeader, item_identifiers_bytes, item_num) as deserialize_page_header does (ppr:253-269)."""
+    pos = next((page - first) * BLOCK_SIZE for first, n in spans if first <= page < first + n)
+    print("PAGE: {}".format(pos))
+    page_bytes = bytes(host[page * BLOCK_SIZE:(page + 1) * BLOCK_SIZE])
+    hdr = list(struct.unpack('@qHHHHHHI', page_bytes[:PAGE_HEADER_LEN]))
+    hdr[-2] &= 0x00FF
+    header = PageHeader(*hdr)
+    ids = page_bytes[PAGE_HEADER_LEN:header.pd_lower]
+    return page_bytes, header, ids, len(ids) // ITEM_IDENTIFIER_LEN
+
+
 def generator_page(filename, toast=False, debug=False):
     """ppr:364-448.  Yields (dist_key, independent_var_tuple, dependent_var_tuple, buffer_id, None) for a
     heap relation or (chunk_id, chunk_seq, chunk_data, None) for a TOAST relation, in the reference's
-    order; the walk itself runs on the GPU.  `debug=True` (raw page dumps) is not offered."""
-    if debug:
-        raise NotImplementedError("debug=True yields host-side page dumps in the reference; use debug=False")
+    order; the walk itself runs on the GPU.  With debug=True the last element is the reference's tuple
+    (page_bytes, page_header, item_identifiers_bytes, lp_off | None, item_num, item_identifier, item_header, tupdata)
+    (ppr:415-420, 433-445) and "PAGE: <pos>" is printed as each page is entered: positions come from the GPU's row
+    table / chunk directory, the headers shown are unpacked from the page bytes for display."""
     if not toast:
         rows, heap_host, holder = _scan_heap(filename)
         df_data, _ = _rows_to_frames(rows, heap_host)
-        for rec in df_data.itertuples(index=False):
-            yield rec[0], rec[1], rec[2], rec[3], None
+        if not debug:
+            for rec in df_data.itertuples(index=False):
+                yield rec[0], rec[1], rec[2], rec[3], None
+            return
+        spans = _file_of_page(filename)
+        inline_off = rows[:, 13].astype(np.uint64) | (rows[:, 14].astype(np.uint64) << np.uint64(32))
+        r = 0
+        recs = list(df_data.itertuples(index=False))
+        for page in range(heap_host.size // BLOCK_SIZE):
+            page_bytes, header, ids, item_num = _debug_page(heap_host, page, spans)
+            for i in range(item_num):
+                word = struct.unpack('<I', ids[4 * i:4 * i + 4])[0]
+                ident = ItemIdentifier(word & 0x7FFF, (word >> 15) & 3, word >> 17)       # ppr:285-300
+                item = page_bytes[ident.lp_off:ident.lp_off + ident.lp_len]
+                item_header = HeapTupleHeader(*struct.unpack('@IIIHHHHHB', item[:ITEM_HEADER_LEN]))
+                tupdata = item[item_header.t_hoff:]
+                rec = recs[r]
+                assert int(inline_off[r]) == page * BLOCK_SIZE + ident.lp_off + item_header.t_hoff + 24
+                r += 1
+                yield rec[0], rec[1], rec[2], rec[3], (page_bytes, header, ids, None, item_num, ident, item_header, tupdata)
         return
     _lib.require_device()
     holder, toast_host, partial = read_relation(filename)
@@ -360,11 +408,34 @@ def generator_page(filename, toast=False, debug=False):
         stop_at = int(s.err_where) if err and s.err_stage == 1 else None
     finally:
         seg.close()
-    for i in range(cid.size):
-        o, n = int(off[i]), int(ln[i])
-        if stop_at is not None and o // BLOCK_SIZE >= stop_at:
-            break
-        yield int(cid[i]), int(seq[i]), bytes(toast_host[o - 4:o + n]), None
+    if not debug:
+        for i in range(cid.size):
+            o, n = int(off[i]), int(ln[i])
+            if stop_at is not None and o // BLOCK_SIZE >= stop_at:
+                break
+            yield int(cid[i]), int(seq[i]), bytes(toast_host[o - 4:o + n]), None
+    else:
+        spans = _file_of_page(filename)
+        i = 0
+        last_page = n_pages if stop_at is None else min(n_pages, stop_at + 1)
+        for page in range(last_page):
+            page_bytes, header, ids, item_num = _debug_page(toast_host, page, spans)
+            if stop_at is not None and page >= stop_at:
+                break                                                 # the reference fails inside this page
+            lp_off = header.pd_upper
+            while i < cid.size and int(off[i]) // BLOCK_SIZE == page:
+                o, n = int(off[i]) - page * BLOCK_SIZE, int(ln[i])
+                lp_off = MAX_ALIGN(lp_off)                                # ppr:394
+                t_hoff = o - 12 - lp_off                                  # payload = item + t_hoff + 8 (ids) + 4 (length word)
+                lp_len = t_hoff + 8 + 4 + n
+                ident = ItemIdentifier(lp_off, 1, lp_len)                 # ppr:391,407-408
+                item = page_bytes[lp_off:lp_off + lp_len]
+                item_header = HeapTupleHeader(*struct.unpack('@IIIHHHHHB', item[:ITEM_HEADER_LEN]))
+                assert item_header.t_hoff == t_hoff
+                lp_off += lp_len
+                yield int(cid[i]), int(seq[i]), page_bytes[o - 4:o + n], (page_bytes, header, ids, lp_off, item_num, ident,
+                                                                         item_header, item[t_hoff:])
+                i += 1
     raise_for_status(err)
     if partial:
         raise_for_status(_lib.CDS_ERR_PARTIAL_PAGE)
@@ -439,9 +510,23 @@ def _assemble(part, ind_host, dep_host, df_shape, table_name):
     return out
 
 
+def _log_value_markers(part, rows):
+    wanted = set(int(x) for x in rows[:, 5]) | set(int(rows[r, 10]) for r in range(rows.shape[0]) if rows[r, 12])
+    seen = set()
+    for cid in part.chunk_ids:
+        cid = int(cid)
+        if cid in wanted and cid not in seen:
+            seen.add(cid)
+            logs("ID:{}".format(cid))
+            logs("START DECOMPRESSING")
+            logs("END DECOMPRESSING")
+
+
 def _detoast_on_device(d_heap, d_toast, rows, inline_blob, df_shape, table_name, partial):
     import torch
-    status, part = _segment.decode_pages(d_heap, d_toast, rows=rows, inline_blob=inline_blob)
+    status, part = _segment.decode_pages(d_heap, d_toast, rows=rows, inline_blob=inline_blob, want_chunk_ids=LOG_VALUE_IDS)
+    if LOG_VALUE_IDS and status == 0:
+        _log_value_markers(part, part.rows)
     # errors of the TOAST walk surface in read_toast_all_bytes, before detoast; a trailing short page
     # is met by the walk only after every whole page was read (ppr:375-377)
     if status and part.summary.err_stage <= 1:
@@ -486,6 +571,8 @@ def detoast(grand_bytes, df_toast, df_shape, table_name):
     for k, v in grand_bytes.items():
         if LOG_VALUE_IDS:
             logs("ID:{}".format(k))
+            logs("START DECOMPRESSING")
+            logs("END DECOMPRESSING")
         hit = external.loc[external['va_valueid'] == k].iloc[0]
         va_extsize, buffer_id, attname = hit['va_extsize'], hit['buffer_id'], hit['attname']
         numchunks = get_num_chunks(va_extsize)

@@ -289,7 +289,7 @@ class DecodedPartition:
 
 
 def decode_pages(heap, toast, device=None, ind_sample_bytes=0, dep_sample_bytes=0, rows=None, inline_blob=None,
-                 segment=None, ind_bf16=False, u8_normalize=None):
+                 segment=None, ind_bf16=False, u8_normalize=None, want_chunk_ids=False):
     """Two-phase decode of page buffers already on the GPU (uint8 CUDA tensors): scan + plan, one
     host sync to size the outputs, then materialize.  With `rows` (exported-row layout) the heap scan
     is replaced by an upload of those rows (`toast_page_read` path).  Returns (status, DecodedPartition)."""
@@ -316,7 +316,10 @@ def decode_pages(heap, toast, device=None, ind_sample_bytes=0, dep_sample_bytes=
             s2 = seg.finish()
             out_rows = seg.rows()
             lay = seg.layout(int(s2.n_rows), int(s2.n_positions))
-            return int(s2.status), DecodedPartition(s2, out_rows, lay, ind[:ind_out_bytes], dep[:int(s1.dep_bytes)])
+            part = DecodedPartition(s2, out_rows, lay, ind[:ind_out_bytes], dep[:int(s1.dep_bytes)])
+            if want_chunk_ids:                                   # chunk ids in the reference's yield order (ppr:412-422)
+                part.chunk_ids = seg.chunks(max(1, int(s2.n_chunks)))[0]
+            return int(s2.status), part
         finally:
             if segment is None:
                 seg.close()

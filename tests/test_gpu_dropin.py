@@ -175,3 +175,52 @@ def test_prefetch_device_yields_the_same_partitions_in_order(tmp_path, torch_cud
     # an error in a later partition surfaces when that partition is reached
     with pytest.raises(Exception):
         list(da.prefetch_device(paths[:1] + [os.path.join(str(tmp_path), "gpseg9", "base", "16384", "train")]))
+
+
+def test_generator_page_debug_and_value_markers_match_the_reference(tmp_path, torch_cuda, capsys):
+    """generator_page(debug=True) (ppr:380-381, 415-420, 433-445) and the per-value log markers (ppr:554, 600-603)
+    against what the unmodified reference printed and yielded (tests/golden/frames_debug.npz)."""
+    import re
+    from cerebro_ds_kpgi_b200 import da
+    from cerebro_ds_kpgi_b200 import pg_page_reader as ppr
+    heap, toast, order, expected = load_golden_segment("seg_small_mixed")
+    z = np.load(os.path.join(GOLDEN, "frames_debug.npz"))
+    d, cat = write_case(tmp_path, heap, toast, expected)
+    # same two-file TOAST relation the golden run used
+    cut = int(z["toast_cut_pages"][0]) * 32768
+    tp = os.path.join(d, "50001")
+    open(tp, "wb").write(toast.tobytes()[:cut])
+    open(tp + ".1", "wb").write(toast.tobytes()[cut:])
+    capsys.readouterr()
+    for name, path, is_toast in (("heap", os.path.join(d, "50000"), False), ("toast", tp, True)):
+        recs = list(ppr.generator_page(path, toast=is_toast, debug=True))
+        printed = capsys.readouterr().out.splitlines()
+        assert printed == [str(x) for x in z[name + "_printed"]], name
+        assert len(recs) == len(z[name + "_lp_off"])
+        off = 0
+        for i, rec in enumerate(recs):
+            page_bytes, header, ids, lp_off, item_num, ident, item_header, tupdata = rec[-1]
+            assert len(page_bytes) == 32768
+            assert list(header) == list(z[name + "_page_header"][i]), (name, i)
+            assert len(ids) == z[name + "_ids_len"][i] and item_num == z[name + "_item_num"][i]
+            assert (-1 if lp_off is None else lp_off) == z[name + "_lp_off"][i], (name, i)
+            assert list(ident) == list(z[name + "_ident"][i]), (name, i)
+            assert list(item_header) == list(z[name + "_item_header"][i]), (name, i)
+            n = int(z[name + "_tupdata_len"][i])
+            assert bytes(tupdata) == z[name + "_tupdata"][off:off + n].tobytes(), (name, i)
+            off += n
+    # the reader's log, line for line (timestamps stripped), with the per-value markers switched on
+    os.remove(tp + ".1")
+    open(tp, "wb").write(toast.tobytes())
+    da.SYS_CAT_PATH = cat
+    ppr.LOG_VALUE_IDS = True
+    try:
+        out = da.input_fn(os.path.join(d, "train"))
+    finally:
+        ppr.LOG_VALUE_IDS = False
+    assert_dict_equal(out, expected, order)
+    stamp = re.compile(r": \d{4}-\d\d-\d\d \d\d:\d\d:\d\d$")
+    got = [stamp.sub("", l).replace(str(tmp_path), "<root>") for l in capsys.readouterr().out.splitlines()]
+    want = [str(x) for x in z["input_fn_markers"]]
+    assert got[:-1] == want[:-1]
+    assert got[-1].startswith("ITEM NUM:6, BUFFER_IDs:")
