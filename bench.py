@@ -556,6 +556,7 @@ def gpu_leg(ctx, name, steps, warmup, graph_wanted, with_cpu, sampler=None):
     for _ in range(warmup):
         step_device()
     ds.finish()
+    wide0 = int(L.cds_wide_decoded_count())
     poison()
     ds.timing_enable(steps)
     ctx.barrier()
@@ -599,9 +600,11 @@ def gpu_leg(ctx, name, steps, warmup, graph_wanted, with_cpu, sampler=None):
         launches = int(L.cds_launch_count() - launches0)
     s = ds.finish()
     assert s.status == 0
-    n_wide = int(s.n_wide_values)
+    went_wide = int(L.cds_wide_decoded_count()) > wide0
+    blocks_ms = None
     dev_ms = ev0.elapsed_time(ev1) / steps
     stage_ms = ds.timing_read_stage(1, steps)
+    b1_ms, b3_ms = ds.timing_read_stage(2, steps), ds.timing_read_stage(3, steps)
     gather_ms = ds.timing_read(steps)
     ds.timing_enable(0)
     gate("after the timed region")
@@ -676,12 +679,12 @@ def gpu_leg(ctx, name, steps, warmup, graph_wanted, with_cpu, sampler=None):
     stage_bytes = meta["pglz_in_bytes"] + meta["pglz_out_bytes"]
     if meta["pglz_out_bytes"] == 0:
         dom, dom_ms, dom_bytes = "k_toast_gather", gather_ms_max, gather_bytes
-    elif n_wide and args.wide != "off":
+    elif went_wide:
         dom, dom_ms, dom_bytes = ("wide pglz pipeline (k_wide_* : 14 kernels incl. the two k_wide_blocks passes, + k_pglz_decode for the small "
                                   "values; one CUDA-event pair around the stage)"), stage_ms_max, stage_bytes
+        blocks_ms = float(np.mean(b1_ms) + np.mean(b3_ms)) if len(b1_ms) and len(b3_ms) else None
     else:
-        dom, dom_ms, dom_bytes = ("k_pglz_decode (launched from the device by k_decode_gate: the CUDA-event pair brackets the parent launch, "
-                                  "i.e. classification + decoder)" if args.wide == "auto" else "k_pglz_decode"), stage_ms_max, stage_bytes
+        dom, dom_ms, dom_bytes = "k_pglz_decode (+ the classification kernel in front of it, one CUDA-event pair around both)", stage_ms_max, stage_bytes
     achieved = dom_bytes / (dom_ms / 1000.0) / 1e9 if dom_ms > 0 else None
     res = {
         "value": rows_total / (dev_ms_max / 1000.0), "unit": "rows/s", "ms_per_step": dev_ms_max, "steps": steps, "warmup": warmup,
@@ -695,7 +698,7 @@ def gpu_leg(ctx, name, steps, warmup, graph_wanted, with_cpu, sampler=None):
                      "algorithmic_bytes_per_launch": dom_bytes, "launch_ms": dom_ms,
                      "share_of_step": dom_ms / dev_ms_max if dev_ms_max else None,
                      "traffic": (load_profile_traffic(name) or {}).get("dram_bytes_per_launch"),
-                     "stages_ms": {"gather": gather_ms_max, "pglz_stage": stage_ms_max}},
+                     "stages_ms": {"gather": gather_ms_max, "pglz_stage": stage_ms_max, "k_wide_blocks_1_plus_3 (rank 0)": blocks_ms}},
         "e2e": {"value": rows_total / (e2e_ms_max / 1000.0), "unit": "rows/s", "ms_per_step": e2e_ms_max,
                 "h2d_bytes_per_step": int(seg.heap.size + seg.toast.size),
                 "d2h_bytes_per_step": int(meta["samples"] * 8 + 96), "steps": e2e_steps,
@@ -845,8 +848,8 @@ def main():
                     help="time the K steps as one CUDA graph replay (default; falls back to eager launches if capture fails)")
     ap.add_argument("--no-graph", dest="graph", action="store_false")
     ap.add_argument("--wide", default="auto", choices=["off", "auto", "force", "host"],
-                    help="pglz stage: warp decoder only / decided and launched on the device (default) / wide decoder forced, "
-                         "host-launched / cost model with host launches (profilers)")
+                    help="pglz stage: warp decoder only / automatic (default) / every large value through the wide decoder / "
+                         "wide kernels always enqueued, cost model on")
     ap.add_argument("--criteo-buffers", type=int, default=0,
                     help="criteo: buffers per segment (default: from --toast-mib, at most 1024; a real partition holds ~6300)")
     ap.add_argument("--images-per-buffer", type=int, default=3210, help="imagenet_packed: images per packed buffer (the paper's tables: 3210)")

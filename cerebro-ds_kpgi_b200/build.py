@@ -26,7 +26,6 @@ NVCC_FLAGS = [
     "-O3", "-lineinfo", "-std=c++17",
     "--shared", "-Xcompiler", "-fPIC,-O3",
     "-Xptxas", "-v",
-    "-rdc=true",            # k_decode_gate launches kernels from the device (needs relocatable device code + cudadevrt)
 ]
 
 
@@ -87,7 +86,7 @@ def build_cuda(force=False):
         return LIB_DA
     cmd = [nvcc_path()] + NVCC_FLAGS + [
         "-I", os.path.join(REPO_ROOT, "include"), "-I", CSRC,
-        os.path.join(CSRC, "cds_da.cu"), "-o", LIB_DA, "-lcudadevrt", "-lcudart",
+        os.path.join(CSRC, "cds_da.cu"), "-o", LIB_DA, "-lcudart",
     ]
     _run(cmd, log_name=os.path.join(PKG_DIR, "build_cuda.log"))
     _write_stamp(LIB_DA, stamp)

@@ -16,6 +16,7 @@ constexpr uint32_t kRowWords = CDS_ROW_WORDS;
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr unsigned long long kNoErr = ~0ull;
 constexpr uint32_t kFlagRowOverflow = 1u, kFlagChunkOverflow = 2u;
+constexpr uint32_t kFlagNeedWide = 4u;   // the classification took values for the wide decoder, whose kernels were not enqueued (cds_finish runs them)
 
 // row words (cds_export_rows layout)
 enum RowWord : uint32_t {

@@ -93,9 +93,10 @@ struct cds_segment {
     int coop_blocks = 0;            // co-resident grid for k_plan_fused (0: cooperative launch unavailable)
     int ind_format = 0;             // cds_set_output_format: 0 stored bytes, 1 f32 -> bf16, 2 u8 -> f32 through the table
     float *d_lut = nullptr;         // cds_set_normalize_lut: [channels][256]
-    int wide_mode = 2;              // cds_set_wide_pglz: 0 never, 1 host-launched without the cost model, 2 decided and launched on
-                                    // the device (k_decode_gate), 3 host-launched with the cost model
-    bool wide_launched = false;     // this decode may have run the wide decoder: cds_finish reads its counters
+    int wide_mode = 2;              // cds_set_wide_pglz: 0 never, 1 always and without the cost model, 2 automatic, 3 always
+    bool wide_hint = false;         // mode 2: the last summary saw values go wide -> enqueue the wide kernels with the decode
+    bool wide_launched = false;     // this decode classified its jobs: cds_finish reads the counters (and decodes what is left)
+    WideArea last_wa;               // the work area as this decode's classification used it
     uint8_t *wide_mem = nullptr;    // work area of the intra-value parallel pglz decoder (pglz_wide.cuh)
     WideArea wide;
     uint32_t lut_channels = 0;
@@ -191,7 +192,7 @@ static cudaError_t wide_prepare()
     return e;
 }
 
-// The 13 kernels behind the classification, on `st` (a host stream, or cudaStreamTailLaunch inside the gate kernel).
+// The 13 kernels behind the classification, on stream `st`.
 #define CDS_WIDE_PIPELINE(wa, sms, st, BEFORE_B1, AFTER_B1, BEFORE_B3, AFTER_B3)            \
     do {                                                                                    \
         k_wide_maps<<<(sms) * 8u, 256, 0, st>>>(wa);                                        \
@@ -213,52 +214,29 @@ static cudaError_t wide_prepare()
         AFTER_B3;                                                                           \
     } while (0)
 
-// Host-launched: classify the job list and decode the large values; the jobs taken are blanked, so the warp
-// decoder that runs afterwards skips them.  `ev4`: optional event pairs around the two block passes.
-static int launch_wide(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int num_sms, cudaStream_t st,
-                       cudaEvent_t *ev4 = nullptr, unsigned ev_flags = cudaEventRecordDefault)
+// Classify the job list (cost model on the device); the jobs taken are blanked, so the warp decoder that runs
+// afterwards skips them.  with_pipeline: also decode them (the 13 kernels; `ev4`: optional event pairs around the two
+// block passes).  Without it only the classification runs (one small launch): if it does take values,
+// kFlagNeedWide is raised and cds_finish runs wide_pipeline() for them.
+static int wide_pipeline(WideArea wa, int num_sms, cudaStream_t st, cudaEvent_t *ev4 = nullptr, unsigned ev_flags = cudaEventRecordDefault)
 {
     const uint32_t sms = (uint32_t)num_sms;
-    CU(cudaMemsetAsync(wa.state, 0, wa.zero_bytes, st));
-    k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa);
+    CU(cudaMemsetAsync(reinterpret_cast<uint8_t *>(wa.state) + 256, 0, wa.zero_bytes - 256, st));
     CDS_WIDE_PIPELINE(wa, sms, st,
                       if (ev4) cudaEventRecordWithFlags(ev4[0], st, ev_flags), if (ev4) cudaEventRecordWithFlags(ev4[1], st, ev_flags),
                       if (ev4) cudaEventRecordWithFlags(ev4[2], st, ev_flags), if (ev4) cudaEventRecordWithFlags(ev4[3], st, ev_flags));
     CU(cudaGetLastError());
-    LAUNCHED(14);
+    LAUNCHED(13);
     return CDS_OK;
 }
 
-// The pglz stage of the one-call decode, decided where the plan lives: on the device.  One block classifies the
-// job list of THIS decode (same cost model as the host-launched path) and then launches, from the device and
-// into the tail of its own stream position, exactly what the decode needs: the wide pipeline when large values
-// go wide, the warp decoder (sized for the job count) when there are jobs at all.  A segment without
-// compressed values pays for this one small launch and nothing else.
-__global__ void __launch_bounds__(1024)
-k_decode_gate(PglzJob *jobs, DevState *st, WideArea wa, uint32_t sms, int wide_enabled, const float *lut, uint32_t lut_channels)
+static int launch_wide(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int num_sms, cudaStream_t st,
+                       bool with_pipeline = true, cudaEvent_t *ev4 = nullptr, unsigned ev_flags = cudaEventRecordDefault)
 {
-    if (wide_enabled) {
-        if (threadIdx.x < sizeof(WideState) / 4u) reinterpret_cast<uint32_t *>(wa.state)[threadIdx.x] = 0u;
-        __syncthreads();
-        d_wide_classify(jobs, st, 0u, wa);
-        __syncthreads();
-    }
-    if (threadIdx.x != 0) return;
-    bool ok = true;
-    if (wide_enabled && wa.state->n_jobs != 0u) {
-        k_wide_zero<<<sms, 256, 0, cudaStreamTailLaunch>>>(wa);
-        CDS_WIDE_PIPELINE(wa, sms, cudaStreamTailLaunch, , , , );
-        ok = cudaGetLastError() == cudaSuccess;
-    }
-    const uint32_t n_jobs = st->n_jobs_front + st->n_jobs_back;
-    if (n_jobs != 0u) {
-        uint32_t grid = (n_jobs + kPglzWarps - 1u) / kPglzWarps;
-        if (grid > sms * 7u) grid = sms * 7u;
-        k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, cudaStreamTailLaunch>>>(jobs, st, 0u, nullptr, st, &st->pglz_ticket, lut,
-                                                                                       lut_channels);
-        ok = ok && cudaGetLastError() == cudaSuccess;
-    }
-    if (!ok) report(st, 4, 0, 7, 0, CDS_ERR_CUDA);                          // a device-side launch was refused
+    k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa, with_pipeline ? 0 : 1);
+    CU(cudaGetLastError());
+    LAUNCHED(1);
+    return with_pipeline ? wide_pipeline(wa, num_sms, st, ev4, ev_flags) : CDS_OK;
 }
 
 extern "C" int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model)
@@ -576,34 +554,28 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
     }
     const float *lut = s->ind_format == 2 ? s->d_lut : nullptr;
     const bool wide_possible = s->wide_mem && g_wide_threshold && s->wide_mode != 0;
-    WideArea wa = s->wide;
+    if (timed) CU(cudaEventRecordWithFlags(ev[2], st, ev_flags));
     if (wide_possible) {
+        WideArea wa = s->wide;
         wa.threshold = g_wide_threshold;
         wa.force = (s->wide_mode == 1 || g_wide_force) ? 1u : 0u;
         wa.st = s->state;
         wa.lut = lut;
         wa.lut_channels = s->lut_channels ? s->lut_channels : 1u;
+        s->last_wa = wa;
+        // mode 2: the 13 kernels of the wide decoder are enqueued when the handle's last summary saw values go wide;
+        // the classification always runs, and what it takes without them is decoded by cds_finish (see there)
+        const bool pipeline = s->wide_mode != 2 || s->wide_hint;
+        int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st, pipeline, (timed && pipeline) ? ev + 4 : nullptr, ev_flags);
+        if (rc) return rc;
+        if (timed && pipeline) mask |= 4u | 8u;
+        s->wide_launched = true;
     }
-    if (timed) CU(cudaEventRecordWithFlags(ev[2], st, ev_flags));
-    if (s->wide_mode == 2) {
-        // decided on the device: one launch; the wide pipeline and the warp decoder are launched from there
-        k_decode_gate<<<1, 1024, 0, st>>>(s->jobs, s->state, wa, (uint32_t)s->num_sms, wide_possible ? 1 : 0, lut, s->lut_channels);
-        CU(cudaGetLastError());
-        LAUNCHED(1);
-        s->wide_launched = wide_possible;
-    } else {
-        if (wide_possible) {
-            int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st, timed ? ev + 4 : nullptr, ev_flags);
-            if (rc) return rc;
-            if (timed) mask |= 4u | 8u;
-            s->wide_launched = true;
-        }
-        // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
-        k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
-            s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket, lut, s->lut_channels);
-        CU(cudaGetLastError());
-        LAUNCHED(1);
-    }
+    // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
+    k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
+        s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket, lut, s->lut_channels);
+    CU(cudaGetLastError());
+    LAUNCHED(1);
     if (timed) {
         CU(cudaEventRecordWithFlags(ev[3], st, ev_flags));
         mask |= 2u;
@@ -627,6 +599,8 @@ extern "C" int cds_materialize(cds_segment *s, void *d_out_ind, uint64_t ind_cap
     return launch_gather_and_pglz(s, st);
 }
 
+__global__ void k_clear_flag(DevState *st, uint32_t flag) { st->flags &= ~flag; }
+
 static void decode_key(unsigned long long key, cds_summary *sum)
 {
     if (key == kNoErr) { sum->status = CDS_OK; sum->err_stage = 0; sum->err_where = 0; return; }   // err_inv == 0
@@ -640,12 +614,28 @@ extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
     if (!s) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     ON_DEVICE(s->device);
-    CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
     WideState wide_counts;
     memset(&wide_counts, 0, sizeof(wide_counts));
-    if (s->wide_launched) CU(cudaMemcpyAsync(&wide_counts, s->wide.state, sizeof(WideState), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    if (s->wide_launched) { g_wide_decoded += wide_counts.n_taken; s->wide_launched = false; }
+    for (int pass = 0; pass < 2; pass++) {
+        CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
+        if (s->wide_launched) CU(cudaMemcpyAsync(&wide_counts, s->wide.state, sizeof(WideState), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (pass == 0 && s->wide_launched && (s->h_state->flags & kFlagNeedWide)) {
+            // The classification of this decode took values for the wide decoder, but its kernels were not enqueued with
+            // the decode (the handle had not seen such values before): decode them now.  One extra round trip, once.
+            k_clear_flag<<<1, 1, 0, st>>>(s->state, kFlagNeedWide);
+            LAUNCHED(1);
+            int rc = wide_pipeline(s->last_wa, s->num_sms, st);
+            if (rc) return rc;
+            continue;
+        }
+        break;
+    }
+    if (s->wide_launched) {
+        g_wide_decoded += wide_counts.n_taken;
+        s->wide_hint = wide_counts.n_taken != 0;
+        s->wide_launched = false;
+    }
     cds_summary local;
     memset(&local, 0, sizeof(local));
     const DevState &h = *s->h_state;
@@ -973,7 +963,7 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
             wa.threshold = thr;
             wa.force = g_wide_force ? 1u : 0u;
             wa.status = d_stat;
-            if (launch_wide(d_jobs, nullptr, (uint32_t)n, wa, sms, st) != CDS_OK) e = cudaErrorUnknown;
+            if (cudaMemsetAsync(wa.state, 0, 256, st) != cudaSuccess || launch_wide(d_jobs, nullptr, (uint32_t)n, wa, sms, st) != CDS_OK) e = cudaErrorUnknown;
         }
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
         if (grid > (uint32_t)sms * 7u) grid = (uint32_t)sms * 7u;

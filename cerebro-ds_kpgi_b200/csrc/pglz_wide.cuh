@@ -293,10 +293,17 @@ __device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *s
     }
 }
 
+// The WideState header is cleared here (the rest of the zeroed area only matters to the kernels that follow).
+// deferred != 0: those kernels were not enqueued with this decode; tell cds_finish when they are needed after all.
 __global__ void __launch_bounds__(1024)
-k_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, WideArea wa)
+k_wide_classify(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int deferred)
 {
+    if (st_counts) {                                       // (the batch entry points clear the header with a memset)
+        if (threadIdx.x < sizeof(WideState) / 4u) reinterpret_cast<uint32_t *>(wa.state)[threadIdx.x] = 0u;
+        __syncthreads();
+    }
     d_wide_classify(jobs, st_counts, n_jobs_host, wa);
+    if (deferred && threadIdx.x == 0 && wa.state->n_jobs != 0u && st_counts) atomicOr(&st_counts->flags, kFlagNeedWide);
 }
 
 // Clears the scan status words and the block flags behind the WideState header (the device-launched pipeline:

@@ -153,13 +153,11 @@ int cds_decode_host(cds_segment *seg, const void *h_heap_pages, uint64_t n_heap_
 
 /* ---- measurement hooks (bench.py) ------------------------------------------------------------ */
 
-/* Kernels launched from the host by this library in this process so far (kernels that k_decode_gate launches
- * from the device are not counted). */
+/* Kernels launched by this library in this process so far. */
 unsigned long long cds_launch_count(void);
 /* Record CUDA-event pairs on the launching stream inside the next `max_samples` cds_materialize / cds_decode_*
  * calls (0 disables).  Stages: 0 = the gather kernel; 1 = the pglz stage (classification, wide decoder, warp
- * decoder: with device-side launches the pair brackets the parent launch, whose completion includes its children);
- * 2, 3 = the two block passes of the wide decoder (host-launched modes of cds_set_wide_pglz only).
+ * decoder); 2, 3 = the two block passes of the wide decoder (when its kernels are enqueued with the decode).
  * cds_timing_read_stage waits for the samples of one stage and returns their durations in milliseconds;
  * cds_timing_read does the same for stage 0 and then rearms (call it last). */
 int cds_timing_enable(cds_segment *seg, uint32_t max_samples);
@@ -205,14 +203,16 @@ int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_s
  * (default 1 MiB; 0 switches the wide decoder off; values under 1024 bytes never take it);
  * skip_cost_model != 0 sends every value at or above the threshold through it (tests, measurements). */
 int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model);
-/* Per handle: how the pglz stage of a decode is launched.
- *   2 (default) = decided on the device for THIS decode: one small kernel after the gather classifies the job
- *       list and launches from the device what the decode needs — the wide pipeline if values go wide, the warp
- *       decoder if there are compressed values at all.  No state is carried from one decode to the next.
- *   0 = warp decoder only, host-launched.
- *   1 = wide pipeline + warp decoder host-launched (14 + 1 kernels), every value at or above the threshold goes
- *       wide (tests, measurements).
- *   3 = as 1 but with the cost model (profilers that do not follow device-side launches). */
+/* Per handle: how the pglz stage of a decode is launched.  Which values go wide is always decided on the device
+ * for THIS decode (one small classification kernel after the gather); the modes differ in whether the 13 kernels
+ * of the wide decoder are enqueued along with it.
+ *   2 (default) = they are enqueued when the handle's previous summary saw values go wide (a performance hint
+ *       only).  When they were not enqueued and the classification does take values, cds_finish runs them before it
+ *       returns — one extra round trip on the first such segment, never a slow decode and never a wrong one; the
+ *       outputs of an enqueue-only decode (summary == NULL) are complete once cds_finish has returned.
+ *   0 = warp decoder only.
+ *   1 = always enqueued, and every value at or above the threshold goes wide (tests, measurements).
+ *   3 = always enqueued, cost model on (profiling a steady state). */
 int cds_set_wide_pglz(cds_segment *seg, int mode);
 /* Frees the cached work memory of cds_pglz_decompress_batch / pglz_decompress / cds_text_etl on `device`. */
 int cds_trim_work_memory(int device);
