@@ -546,8 +546,9 @@ def gpu_leg(ctx, name, steps, warmup, graph_wanted, with_cpu, sampler=None):
 
     # ---- correctness gate before timing
     poison()
-    step_device()
-    s = ds.finish()
+    ds.decode_device(d_heap, d_toast, out_ind, out_dep, meta["isb"], meta["dsb"], sync=False)
+    s = ds.finish()                  # (the decode is complete when cds_finish returns; consumers are enqueued after it)
+    _lib.check(L.cds_onehot_argmax_i16(segment._ptr(onehot), meta["samples"], meta["classes"], segment._ptr(labels), sp))
     if s.status != 0 or s.ind_bytes != meta["ind_bytes"] or s.dep_bytes != meta["dep_bytes"]:
         raise SystemExit("%s: decode failed: status %d, %d/%d bytes" % (name, s.status, s.ind_bytes, meta["ind_bytes"]))
     gate("before the warm-up")

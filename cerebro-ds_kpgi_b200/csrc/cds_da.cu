@@ -94,7 +94,7 @@ struct cds_segment {
     int ind_format = 0;             // cds_set_output_format: 0 stored bytes, 1 f32 -> bf16, 2 u8 -> f32 through the table
     float *d_lut = nullptr;         // cds_set_normalize_lut: [channels][256]
     int wide_mode = 2;              // cds_set_wide_pglz: 0 never, 1 always and without the cost model, 2 automatic, 3 always
-    bool wide_hint = false;         // mode 2: the last summary saw values go wide -> enqueue the wide kernels with the decode
+    bool wide_hint = true;          // mode 2: the last summary saw values go wide (or there is none yet) -> enqueue the wide kernels with the decode
     bool wide_launched = false;     // this decode classified its jobs: cds_finish reads the counters (and decodes what is left)
     WideArea last_wa;               // the work area as this decode's classification used it
     uint8_t *wide_mem = nullptr;    // work area of the intra-value parallel pglz decoder (pglz_wide.cuh)
@@ -184,6 +184,19 @@ extern "C" int cds_host_free(void *ptr)
 }
 
 // ---- intra-value parallel pglz (pglz_wide.cuh) -----------------------------------------------------
+
+constexpr uint32_t kPglzCtasPerSm = 2;
+
+// k_pglz_decode needs more dynamic shared memory than the default limit: once per device.
+static cudaError_t pglz_prepare(int device)
+{
+    static bool done[64] = {false};
+    if (device >= 0 && device < 64 && done[device]) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess && device >= 0 && device < 64) done[device] = true;
+    return e;
+}
 
 static cudaError_t wide_prepare()
 {
@@ -339,9 +352,7 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
 #undef A
     if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&s->h_state), sizeof(DevState), cudaHostAllocPortable);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_toast_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGatherSmemBytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPglzSmemBytes);
-    // (launched from the device too: state the shared-memory split instead of leaving it to the launch path)
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pglz_decode, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = pglz_prepare(device);
     if (e == cudaSuccess) e = wide_prepare();
     if (e == cudaSuccess) {
         int coop = 0, per_sm = 0;
@@ -571,8 +582,8 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
         if (timed && pipeline) mask |= 4u | 8u;
         s->wide_launched = true;
     }
-    // one warp per value; the grid is sized for residency (7 CTAs of 4 warps fit one SM's shared memory)
-    k_pglz_decode<<<(uint32_t)s->num_sms * 7u, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
+    // one warp per value; the grid is sized for residency (kPglzCtasPerSm CTAs of kPglzWarps warps fill one SM's shared memory)
+    k_pglz_decode<<<(uint32_t)s->num_sms * kPglzCtasPerSm, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
         s->jobs, s->state, 0u, nullptr, s->state, &s->state->pglz_ticket, lut, s->lut_channels);
     CU(cudaGetLastError());
     LAUNCHED(1);
@@ -953,6 +964,7 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, h_src_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_off + n + 1, h_dst_off, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess && any_wide) e = wide_prepare();
+    if (e == cudaSuccess) e = pglz_prepare(device);
     if (e == cudaSuccess) {
         const int sms = sm_count(device);
         k_build_pglz_jobs<<<(uint32_t)((n + 255) / 256), 256, 0, st>>>(static_cast<const uint8_t *>(d_src), d_off,
@@ -966,7 +978,7 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
             if (cudaMemsetAsync(wa.state, 0, 256, st) != cudaSuccess || launch_wide(d_jobs, nullptr, (uint32_t)n, wa, sms, st) != CDS_OK) e = cudaErrorUnknown;
         }
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
-        if (grid > (uint32_t)sms * 7u) grid = (uint32_t)sms * 7u;
+        if (grid > (uint32_t)sms * kPglzCtasPerSm) grid = (uint32_t)sms * kPglzCtasPerSm;
         k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(d_jobs, nullptr, (uint32_t)n, d_stat, nullptr,
                                                                      reinterpret_cast<uint32_t *>(d_stat + n), nullptr, 0u);
         if (e == cudaSuccess) e = cudaGetLastError();
@@ -1045,6 +1057,7 @@ extern "C" int cds_pglz_decompress_batch_static(int device, const void *d_src, c
     StaticScratch *sc = nullptr;
     int rc = static_scratch_for(device, &sc);
     if (rc != CDS_OK) return rc;
+    CU(pglz_prepare(device));                                   // (a function attribute, set once per device: no allocation)
     // The work area still holds whatever the previous call left: the error word is the only part that is
     // accumulated into (atomicMax), so it is the only part that has to be cleared.
     CU(cudaMemsetAsync(&sc->state, 0, sizeof(DevState), st));
@@ -1055,7 +1068,7 @@ extern "C" int cds_pglz_decompress_batch_static(int device, const void *d_src, c
             d_status, &sc->state);
         CU(cudaGetLastError());
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);
-        const uint32_t max_grid = (uint32_t)sm_count(device) * 7u;
+        const uint32_t max_grid = (uint32_t)sm_count(device) * kPglzCtasPerSm;
         if (grid > max_grid) grid = max_grid;
         k_pglz_decode<<<grid, 32 * kPglzWarps, kPglzSmemBytes, st>>>(sc->jobs, nullptr, (uint32_t)n, d_status, &sc->state,
                                                                      &sc->state.pglz_ticket, nullptr, 0u);

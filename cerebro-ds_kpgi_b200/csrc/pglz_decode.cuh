@@ -34,7 +34,8 @@ namespace {   // internal linkage: with relocatable device code (-rdc) the optim
 
 constexpr uint32_t kRing = 8192;              // bytes of output history per warp (power of two)
 constexpr uint32_t kFlushAt = 2048;           // flush to HBM once this many bytes are pending
-constexpr int kPglzWarps = 4;                 // warps (datums) per CTA
+constexpr int kPglzWarps = 14;                // warps (datums) per CTA: two CTAs of 14 x 8 KB rings fill an SM's shared memory (28 datums per SM)
+constexpr uint32_t kItemCopyMax = 20;         // matches up to this long are copied by one lane each
 constexpr size_t kPglzSmemBytes = (size_t)kPglzWarps * kRing;
 
 // Flush ring bytes for output positions [from, to) to global memory.  `shift` = dst & 15, so that
@@ -205,8 +206,55 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
     const bool bad = is_item && ((dp + my_o + olen > rawsize) || (is_match && (moff == 0u || moff > dp + my_o)));
     if (__ballot_sync(0xffffffffu, bad)) return false;
 
-    if (total <= 128u) {
-        // ---- short items: one lane per output byte, 32 bytes per step
+    constexpr uint32_t M_ = kRing - 1;
+    if (total <= 128u && __ballot_sync(0xffffffffu, is_match && len > kItemCopyMax) == 0u) {
+        // ---- short items, none longer than kItemCopyMax: one lane per ITEM.  A literal lane stores its byte; a match lane
+        //      copies its own bytes in order (so a copy that overlaps itself needs no modulo: it re-reads what it wrote).
+        //      A match whose source lies inside this step's output waits until the items that produce those bytes are
+        //      done: rounds over a "not done" ballot, the items it needs found through a bitmap of item starts.
+        const uint32_t d0 = dp + my_o + shift;                               // ring position of my first byte
+        if (is_item && !is_match) ring[d0 & M_] = (uint8_t)litbyte;
+        const uint32_t ext = min(len, moff);                                 // source bytes that are not my own output
+        const bool dep = is_match && my_o + ext > moff;                      // ... reach into this step's output
+        uint32_t need = 0;                                                   // items (bit = lane) that produce them
+        if (__ballot_sync(0xffffffffu, dep)) {
+            const uint32_t wsel = my_o >> 5, bit = 1u << (my_o & 31u);
+            const uint32_t s0 = __reduce_or_sync(0xffffffffu, (is_item && wsel == 0u) ? bit : 0u);
+            const uint32_t s1 = __reduce_or_sync(0xffffffffu, (is_item && wsel == 1u) ? bit : 0u);
+            const uint32_t s2 = __reduce_or_sync(0xffffffffu, (is_item && wsel == 2u) ? bit : 0u);
+            const uint32_t s3 = __reduce_or_sync(0xffffffffu, (is_item && wsel == 3u) ? bit : 0u);
+            const uint32_t p1 = __popc(s0), p2 = p1 + __popc(s1), p3 = p2 + __popc(s2);
+            auto item_at = [&](uint32_t x) -> uint32_t {                     // index of the item that holds output offset x of the step
+                const uint32_t w = x >> 5, m = 0xFFFFFFFFu >> (31u - (x & 31u));
+                const uint32_t sw = w == 0u ? s0 : w == 1u ? s1 : w == 2u ? s2 : s3;
+                const uint32_t below = w == 0u ? 0u : w == 1u ? p1 : w == 2u ? p2 : p3;
+                return below + __popc(sw & m) - 1u;
+            };
+            if (dep) {
+                const uint32_t lo = my_o > moff ? my_o - moff : 0u, hi = my_o + ext - moff - 1u;     // lo <= hi < my_o
+                const uint32_t ja = item_at(lo), jb = item_at(hi);
+                need = (0xFFFFFFFFu >> (31u - jb)) & (0xFFFFFFFFu << ja);
+            }
+        }
+        bool done = !is_match;
+        __syncwarp();
+        for (;;) {
+            const uint32_t undone = __ballot_sync(0xffffffffu, !done);
+            if (undone == 0u) break;
+            if (!done && (need & undone) == 0u) {
+                const uint32_t sr = d0 - moff;
+                if (((d0 | sr | len) & 3u) == 0u) {                          // whole aligned words (float data: the usual case)
+                    for (uint32_t k = 0; k < len; k += 4u)
+                        *reinterpret_cast<uint32_t *>(ring + ((d0 + k) & M_)) = *reinterpret_cast<const uint32_t *>(ring + ((sr + k) & M_));
+                } else {
+                    for (uint32_t k = 0; k < len; k++) ring[(d0 + k) & M_] = ring[(sr + k) & M_];
+                }
+                done = true;
+            }
+            __syncwarp();
+        }
+    } else if (total <= 128u) {
+        // ---- short items with a long one among them: one lane per output byte, 32 bytes per step
         const uint32_t pack = moff | (len << 12) | ((is_match ? 1u : 0u) << 21);
         for (uint32_t t0 = 0; t0 < total; t0 += 32) {
             const uint32_t c0 = __popc(__ballot_sync(0xffffffffu, is_item && my_o <= t0));
@@ -482,7 +530,7 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
 // Jobs are taken through *ticket (zero at launch).  With `st_counts` the job array is the compacted
 // two-ended list k_resolve builds (n_jobs_front slots from the start, n_jobs_back from slot 2*n_rows-1
 // down): front jobs (large values) are handed out first, the small ones fill the tail.
-__global__ void __launch_bounds__(32 * kPglzWarps, 7)
+__global__ void __launch_bounds__(32 * kPglzWarps, 2)
 k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint32_t n_jobs_host,
               int32_t *status, DevState *st, uint32_t *ticket, const float *__restrict__ lut, uint32_t lut_channels)
 {

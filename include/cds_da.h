@@ -206,8 +206,8 @@ int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model);
 /* Per handle: how the pglz stage of a decode is launched.  Which values go wide is always decided on the device
  * for THIS decode (one small classification kernel after the gather); the modes differ in whether the 13 kernels
  * of the wide decoder are enqueued along with it.
- *   2 (default) = they are enqueued when the handle's previous summary saw values go wide (a performance hint
- *       only).  When they were not enqueued and the classification does take values, cds_finish runs them before it
+ *   2 (default) = they are enqueued when the handle's previous summary saw values go wide, or the handle has not
+ *       produced a summary yet (a performance hint only).  When they were not enqueued and the classification does take values, cds_finish runs them before it
  *       returns — one extra round trip on the first such segment, never a slow decode and never a wrong one; the
  *       outputs of an enqueue-only decode (summary == NULL) are complete once cds_finish has returned.
  *   0 = warp decoder only.
