@@ -318,7 +318,25 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
                     continue;
                 }
                 const uint32_t kmoff = __shfl_sync(0xffffffffu, moff, k);
-                if (kmoff >= klen && klen >= 8u) {
+                if (kmoff >= klen && klen >= 16u) {
+                    // source and destination do not overlap: aligned 16-byte stores (one per lane covers 273 bytes in one
+                    // go), the source re-aligned with funnel shifts of five aligned words.  The last vector may run up to 15
+                    // bytes past the item, like the run fill above.
+                    const uint32_t s0 = a0 - kmoff;
+                    const uint32_t head = (16u - (a0 & 15u)) & 15u;               // < 16 <= klen
+                    if (lane < head) ring[(a0 + lane) & M] = ring[(s0 + lane) & M];
+                    const uint32_t nv = (klen - head + 15u) >> 4, v0 = a0 + head, sv = s0 + head, r8 = (sv & 3u) * 8u;
+                    for (uint32_t i = lane; i < nv; i += 32) {
+                        const uint32_t sa = (sv + 16u * i) & ~3u;
+                        const uint32_t x0 = *reinterpret_cast<const uint32_t *>(ring + (sa & M));
+                        const uint32_t x1 = *reinterpret_cast<const uint32_t *>(ring + ((sa + 4u) & M));
+                        const uint32_t x2 = *reinterpret_cast<const uint32_t *>(ring + ((sa + 8u) & M));
+                        const uint32_t x3 = *reinterpret_cast<const uint32_t *>(ring + ((sa + 12u) & M));
+                        const uint32_t x4 = *reinterpret_cast<const uint32_t *>(ring + ((sa + 16u) & M));
+                        *reinterpret_cast<uint4 *>(ring + ((v0 + 16u * i) & M)) =
+                            make_uint4(__funnelshift_r(x0, x1, r8), __funnelshift_r(x1, x2, r8), __funnelshift_r(x2, x3, r8), __funnelshift_r(x3, x4, r8));
+                    }
+                } else if (kmoff >= klen && klen >= 8u) {
                     // source and destination do not overlap: aligned 32-bit stores, the source re-aligned with a funnel
                     // shift of two aligned words (bytes read beyond the source are shifted out)
                     const uint32_t s0 = a0 - kmoff;
@@ -489,13 +507,20 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
             const uint32_t extmask = __ballot_sync(0xffffffffu, (byte & 0x0Fu) == 0x0Fu);
             const uint32_t n_avail = min(32u, slen - sp);                    // a group is at most 25 bytes
             uint32_t pnext = 1, my_p = 0, nitems = 0;
+            if (ctrl == 0xFFu && n_avail >= 25u && ((extmask >> 1) & 0x249249u) == 0x249249u) {
+                // eight tags with a length-extension byte each (long matches: sparse data): item k starts at 1 + 3k
+                my_p = lane < 8u ? 1u + 3u * lane : 0u;
+                pnext = 25u;
+                nitems = 8u;
+            } else {
 #pragma unroll
-            for (uint32_t k = 0; k < 8; k++) {
-                if (pnext < n_avail) {                                       // `sp < srcend` of the inner loop
-                    const uint32_t sz = ((ctrl >> k) & 1u) ? 2u + ((extmask >> pnext) & 1u) : 1u;
-                    if (lane == k) my_p = pnext;
-                    pnext += sz;
-                    nitems = k + 1;
+                for (uint32_t k = 0; k < 8; k++) {
+                    if (pnext < n_avail) {                                   // `sp < srcend` of the inner loop
+                        const uint32_t sz = ((ctrl >> k) & 1u) ? 2u + ((extmask >> pnext) & 1u) : 1u;
+                        if (lane == k) my_p = pnext;
+                        pnext += sz;
+                        nitems = k + 1;
+                    }
                 }
             }
             if (pnext > n_avail) { corrupt = true; break; }                  // a tag runs past the source
