@@ -217,7 +217,7 @@ static cudaError_t wide_prepare()
         k_wide_check<<<8, 256, 0, st>>>(wa);                                                \
         k_wide_blkmap<<<(sms) * 2u, 256, 0, st>>>(wa);                                      \
         BEFORE_B1;                                                                          \
-        k_wide_tailmap<<<(sms) * 2u, 1024, 0, st>>>(wa);                                    \
+        if (kWideLazyTail) k_wide_tailmap<<<(sms) * 2u, 1024, 0, st>>>(wa);                 \
         k_wide_blocks<1><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
         AFTER_B1;                                                                           \
         k_wide_tails<0><<<(sms), 1024, 0, st>>>(wa);                                        \

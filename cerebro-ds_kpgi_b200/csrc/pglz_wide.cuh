@@ -56,7 +56,8 @@ constexpr uint32_t kWideThreads = 1024;
 constexpr uint32_t kWidePer = kWideIdx / kWideThreads;   // 60 entries per thread
 constexpr uint32_t kWideEnd = 30, kWideBad = 31;   // map states besides the entry offsets 0..24
 constexpr uint32_t kWideChase = 48;                // pass 1 follows a tail byte's chain this many hops before resolving the whole block
-constexpr uint32_t kWideShort = 2;                 // (cut) matches up to this long are written byte by byte by the emitting thread
+constexpr uint32_t kWideShort = 16;                // (cut) matches up to this long are written byte by byte by the emitting thread (the fill
+                                                   // pass below costs ~10x more per byte; only long matches, whose bytes would serialise one thread, go there)
 constexpr uint32_t kWideMinRaw = 1024;             // below this the maps would not fit the output region
 constexpr size_t kWideBlockSmem = (size_t)kWideIdx * 3 + kWideIdx / 8;
 
@@ -659,6 +660,8 @@ k_wide_blkmap(WideArea wa)
 // through each other: sparse data) is handed to k_wide_blocks<1> instead (blk_full).
 constexpr uint32_t kWideMaxSubs = 2304;            // sub-segments one block can span: 57344 * 9/8 / 32 = 2016, + slack
 constexpr uint32_t kWideLazyHops = 48;
+constexpr bool kWideLazyTail = false;              // measured on packed ImageNet buffers: 31.9 ms against 8 ms for k_wide_blocks<1> (chains of
+                                                   // always-matched bytes run 35-40 hops and a warp waits for its longest one): kept for reference
 
 __global__ void __launch_bounds__(1024)
 k_wide_tailmap(WideArea wa)
@@ -815,7 +818,7 @@ k_wide_blocks(WideArea wa)
             if (kMode == 3 && tid == 0) *reinterpret_cast<volatile uint32_t *>(&wa.blk_flag[b]) = 1u;
             continue;
         }
-        if (kMode == 1 && (k + 1u == wj.nblk || !wa.blk_full[b])) continue;  // nobody needs the last block's tail; k_wide_tailmap did the others
+        if (kMode == 1 && (k + 1u == wj.nblk || (kWideLazyTail && !wa.blk_full[b]))) continue;  // nobody needs the last block's tail
         const uint32_t o0 = k * kWideBlock, o1 = min(o0 + kWideBlock, wj.rawsize), n_out = o1 - o0;
         const uint8_t *src = reinterpret_cast<const uint8_t *>(wj.src);
         uint8_t *dst = reinterpret_cast<uint8_t *>(wj.dst);
@@ -848,6 +851,14 @@ k_wide_blocks(WideArea wa)
             uint32_t a = sb * kWideSub + (ent & 31u);
             uint32_t o = (uint32_t)(wa.seg_base[wj.seg0 + sb / kWideSubs] - value_base) + (ent >> 5);
             const uint32_t send = min((sb + 1u) * kWideSub, slen);
+            // item starts are collected per 32-entry word of the bitmap and published with one atomic per word
+            uint32_t hw = kNone, hm = 0;
+            auto mark = [&](uint32_t e0, uint32_t n) {                           // n <= kWideShort < 32
+                const uint32_t w0 = e0 >> 5, sh = e0 & 31u, mask = (1u << n) - 1u;
+                if (w0 != hw) { if (hm) atomicOr(&heads[hw], hm); hw = w0; hm = 0; }
+                hm |= mask << sh;
+                if (sh + n > 32u) { atomicOr(&heads[hw], hm); hw = w0 + 1u; hm = mask >> (32u - sh); }
+            };
             while (a < send && o < o1) {
                 const uint32_t ctrl = __ldg(src + a);
                 uint32_t q = a + 1u;
@@ -863,7 +874,7 @@ k_wide_blocks(WideArea wa)
                         const uint32_t lo = max(o, o0), hi = min(o + len, o1);
                         if (lo < hi) {
                             // (a match cut by the block start is the same match started at the cut: it is periodic in off)
-                            const uint32_t e0 = kWideWin + (lo - o0), n = hi - lo, sh = e0 & 31u;
+                            const uint32_t e0 = kWideWin + (lo - o0), n = hi - lo;
                             if (off == 0u || e0 - off < floor_idx) {             // offset 0, or before the start of the output
                                 sh_bad = 1u;
                             } else if (n <= kWideShort) {
@@ -876,14 +887,12 @@ k_wide_blocks(WideArea wa)
                                         if (++r == off) r = 0;
                                     }
                                 }
-                                const uint32_t mask = (1u << n) - 1u;
-                                atomicOr(&heads[e0 >> 5], mask << sh);
-                                if (sh + n > 32u) atomicOr(&heads[(e0 >> 5) + 1u], mask >> (32u - sh));
+                                mark(e0, n);
                             } else {
                                 ptr[e0] = (uint16_t)(e0 - off);
                                 val[e0] = (uint8_t)off;
                                 val[e0 + 1u] = (uint8_t)(off >> 8);
-                                atomicOr(&heads[e0 >> 5], 1u << sh);
+                                mark(e0, 1u);
                             }
                         }
                         o += len;
@@ -892,7 +901,7 @@ k_wide_blocks(WideArea wa)
                             const uint32_t e = kWideWin + (o - o0);
                             val[e] = __ldg(src + q);
                             ptr[e] = (uint16_t)e;
-                            atomicOr(&heads[e >> 5], 1u << (e & 31u));
+                            mark(e, 1u);
                         }
                         o += 1u;
                         q += 1u;
@@ -900,6 +909,7 @@ k_wide_blocks(WideArea wa)
                 }
                 a = q;
             }
+            if (hm) atomicOr(&heads[hw], hm);
         }
         __syncthreads();
         if (sh_bad) {
