@@ -879,7 +879,11 @@ k_wide_blocks(WideArea wa)
                                 sh_bad = 1u;
                             } else if (n <= kWideShort) {
                                 if (off >= n) {                                  // no overlap: every byte copies the byte `off` back
-                                    for (uint32_t kk = 0; kk < n; kk++) ptr[e0 + kk] = (uint16_t)(e0 + kk - off);
+                                    const uint32_t p0 = e0 - off;
+#pragma unroll
+                                    for (uint32_t kk = 0; kk < 8u; kk++)         // straight-line, predicated: lanes sit in different items
+                                        if (kk < n) ptr[e0 + kk] = (uint16_t)(p0 + kk);
+                                    for (uint32_t kk = 8u; kk < n; kk++) ptr[e0 + kk] = (uint16_t)(p0 + kk);
                                 } else {
                                     uint32_t r = 0;
                                     for (uint32_t kk = 0; kk < n; kk++) {        // byte kk copies start - off + kk mod off (ppr:216-219)
