@@ -265,3 +265,24 @@ def test_fused_uint8_normalise_is_the_reference_formula_bit_for_bit(torch_cuda, 
     got = part.ind.view(torch.float32).cpu().numpy()
     assert got.shape == want.shape and got.tobytes() == want.tobytes()
     assert part.dep.cpu().numpy().tobytes() == ref["out_dep"].tobytes()
+
+
+def test_deliberate_deviation_on_offsets_outside_the_output(torch_cuda, coracle):
+    """A match with offset 0, or one that reaches before the start of the output, is reported corrupt here, while
+    the reference's Python decoder indexes its zero-filled bytearray with dest[dp - off] and, depending on the sizes,
+    returns bytes (offset 0; a negative index that wraps inside the buffer) or dies with an IndexError.  The golden
+    file records what it did (tests/golden/make_golden_deviation.py); DESIGN.md §5 lists the deviation."""
+    import da_oracle
+    from cerebro_ds_kpgi_b200 import segment
+    z = np.load(os.path.join(GOLDEN, "pglz_deviation.npz"))
+    names = [str(n) for n in z["names"]]
+    datums = [z["datum_%d" % i].tobytes() for i in range(len(names))]
+    ref = {n: (str(z["raised_%d" % i][0]), z["out_%d" % i].tobytes()) for i, n in enumerate(names)}
+    assert ref["offset_zero"] == ("", b"A\x00\x00\x00B")                                   # decodes: copies the zero it is about to write
+    assert ref["offset_before_start"][0].startswith("IndexError")
+    assert ref["offset_wraps_to_unwritten"][0] == "" and ref["offset_wraps_to_unwritten"][1][:5] == b"A\x00\x00\x00\x00"
+    out, codes = segment.pglz_decompress_batch(datums)
+    assert codes == [da_oracle.ERR_PGLZ_CORRUPT] * 3 and out == [None] * 3
+    for d in datums:                                                                           # the oracle agrees with the library
+        with pytest.raises(da_oracle.OracleError):
+            coracle.pglz_decompress(d)
