@@ -420,6 +420,105 @@ __device__ __forceinline__ void d_plan_scan2(const PlanArgs &A, int which)
     }
 }
 
+// Copy descriptor of one chunk (sequence number idx, `size` payload bytes at `loc`) of value v = 2 * row + att whose row
+// sits at result position pos.  The chunk checks are the caller's.  dst == 0: nothing to copy.
+__device__ __forceinline__ CopyOp make_copy_op(const PlanArgs &A, uint32_t v, uint32_t pos, uint32_t idx, uint32_t size, uint2 loc,
+                                               uint32_t va_rawsize, uint32_t va_extsize, unsigned long long rawlen)
+{
+    const uint32_t a = v & 1u;
+    const uint32_t half = A.ind_bf16 ? 1u : 0u, quad = A.ind_u8norm ? 2u : 0u;
+    CopyOp op;
+    const bool compressed = va_extsize != va_rawsize - 4u;
+    op.src_off = loc.y & 0xFFFFu;
+    op.len = size;
+    if (compressed && va_extsize >= 4u && (a == 1u || !(half | quad)) && pglz_literal_only(va_extsize - 4u, rawlen)) {
+        // literal-only pglz stream: stream bytes [s_lo, s_hi) of the value live in this chunk
+        const unsigned long long s_lo = idx ? (unsigned long long)idx * kChunkMax - 4ull : 0ull;
+        const uint32_t skip = idx ? 0u : 4u;                                 // chunk 0 starts with the rawsize word
+        const uint32_t n_stream = size - skip;
+        const unsigned long long s_hi = s_lo + n_stream;
+        const unsigned long long o_lo = s_lo - (s_lo + 8ull) / 9ull;
+        const unsigned long long s_fin = 9ull * (((rawlen + 7ull) >> 3) - 1ull);   // control byte of the final group
+        const uint32_t fin = (s_fin >= s_lo && s_fin < s_hi) ? (uint32_t)(rawlen & 7ull) : 0u;
+        op.dst = (unsigned long long)((a ? A.out_dep + A.pos_dep[pos] : A.out_ind + A.pos_ind[pos]) + o_lo);
+        op.src_off = ((loc.y & 0xFFFFu) + skip) | ((uint32_t)(s_lo % 9ull) << 16) | (fin << 20);
+        op.len = n_stream | kOpLiteral;
+    } else if (compressed) {
+        op.dst = (unsigned long long)(A.scratch + A.vscr[v]) + (unsigned long long)idx * kChunkMax;
+    } else if (a) {
+        op.dst = (unsigned long long)(A.out_dep + A.pos_dep[pos]) + (unsigned long long)idx * kChunkMax;
+    } else if (quad) {
+        const unsigned long long voff = (unsigned long long)idx * kChunkMax;     // byte (= pixel component) inside the value
+        op.dst = (unsigned long long)(A.out_ind + ((A.pos_ind[pos] + voff) << 2));
+        op.src_off |= (uint32_t)(voff % A.lut_channels) << 16;
+        op.len = size | kOpU8Norm;
+    } else if (!half) {
+        op.dst = (unsigned long long)(A.out_ind + A.pos_ind[pos]) + (unsigned long long)idx * kChunkMax;
+    } else if (((size | va_extsize) & 3u) == 0u && (A.pos_ind[pos] & 3ull) == 0ull) {
+        op.dst = (unsigned long long)(A.out_ind + ((A.pos_ind[pos] + (unsigned long long)idx * kChunkMax) >> 1));
+        op.len = size | kOpToBf16;
+    } else {
+        report(A.st, 4, pos, 1, 1, CDS_ERR_SHAPE);                           // not a whole number of float32 elements
+        op.dst = 0;
+    }
+    return op;
+}
+
+// pglz job of value v = 2 * row + att (row usable, at result position pos; the output fits): an inline datum, or a compressed
+// external value whose payload the gather stages.  slen == kNone: the value needs no job (or was refused, and reported).
+__device__ __forceinline__ PglzJob make_value_job(const PlanArgs &A, uint32_t v, uint32_t pos)
+{
+    DevState *st = A.st;
+    const uint32_t half = A.ind_bf16 ? 1u : 0u, quad = A.ind_u8norm ? 2u : 0u;
+    PglzJob job;
+    job.src = 0; job.dst = 0; job.slen = kNone; job.rawsize = 0; job.err_key = 0;
+    const uint32_t r = v >> 1, a = v & 1u;
+    const uint32_t *row = A.rows + (size_t)r * kRowWords;
+    const unsigned long long my_ind_off = A.pos_ind[pos], my_dep_off = A.pos_dep[pos];
+    if (a == 1 && row[RW_DEP_EXTERNAL] == 0) {
+        // inline datum: tupdata[24:] starts with the 8-byte PGLZ header (ppr:344, 537-543)
+        const uint8_t *src = A.heap + (((unsigned long long)row[RW_INLINE_OFF_HI] << 32) | row[RW_INLINE_OFF_LO]);
+        const uint32_t avail = row[RW_INLINE_LEN];
+        const uint32_t varsize = ld_u32be(src) & 0x3FFFFFFFu;
+        job.err_key = make_err_key(2, r, 0, 0, CDS_ERR_PGLZ_CORRUPT);
+        if (avail < 8u || varsize < 8u || varsize > avail) {
+            report_key(st, job.err_key);
+        } else {
+            job.src = (unsigned long long)(src + 8);
+            job.slen = varsize - 8u;
+            job.rawsize = (uint32_t)A.dep_len[r];
+            job.dst = (unsigned long long)(A.out_dep + my_dep_off);
+        }
+    } else if (A.vcount[v] != 0) {
+        const uint32_t *ptr = row + (a ? RW_DEP : RW_IND);
+        const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
+        const unsigned long long len = a ? A.dep_len[r] : A.ind_len[r];
+        const bool literal = va_extsize >= 4u && (a == 1u || !(half | quad)) && pglz_literal_only(va_extsize - 4u, len);
+        if (va_extsize != va_rawsize - 4u && !literal) {
+            job.err_key = make_err_key(3, A.vfirst[v], 3, 0, CDS_ERR_PGLZ_CORRUPT);
+            if (va_extsize < 4u) {
+                report_key(st, job.err_key);
+            } else {
+                // staged payload = LE rawsize + stream (ppr:574-594 builds header + payload)
+                job.src = (unsigned long long)(A.scratch + A.vscr[v] + 4);
+                job.slen = va_extsize - 4u;
+                job.rawsize = (uint32_t)len;
+                if (a) job.dst = (unsigned long long)(A.out_dep + my_dep_off);
+                else if (quad) { job.dst = (unsigned long long)(A.out_ind + (my_ind_off << 2)); job.slen |= kJobU8Norm; }
+                else if (!half) job.dst = (unsigned long long)(A.out_ind + my_ind_off);
+                else if ((len & 3ull) == 0ull && (my_ind_off & 3ull) == 0ull) {
+                    job.dst = (unsigned long long)(A.out_ind + (my_ind_off >> 1));
+                    job.slen |= kJobToBf16;
+                } else {
+                    report(st, 4, pos, 1, 1, CDS_ERR_SHAPE);
+                    job.slen = kNone;
+                }
+            }
+        }
+    }
+    return job;
+}
+
 // One thread per chunk: the reference's per-chunk checks (ppr:570-596) and the copy descriptor.
 // Also one pglz job per value (inline datums and compressed external values).
 __device__ __forceinline__ void d_resolve(const PlanArgs &A)
@@ -467,40 +566,7 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
             }
             const uint32_t pos = A.pos_of_row[r];
             if (ok && vb == va_extsize && fits && pos != kNone) {
-                const bool compressed = va_extsize != va_rawsize - 4u;
-                const unsigned long long rawlen = a ? A.dep_len[r] : A.ind_len[r];
-                op.src_off = loc.y & 0xFFFFu;
-                op.len = size;
-                if (compressed && va_extsize >= 4u && (a == 1u || !(half | quad)) && pglz_literal_only(va_extsize - 4u, rawlen)) {
-                    // literal-only pglz stream: stream bytes [s_lo, s_hi) of the value live in this chunk
-                    const unsigned long long s_lo = idx ? (unsigned long long)idx * kChunkMax - 4ull : 0ull;
-                    const uint32_t skip = idx ? 0u : 4u;                     // chunk 0 starts with the rawsize word
-                    const uint32_t n_stream = size - skip;
-                    const unsigned long long s_hi = s_lo + n_stream;
-                    const unsigned long long o_lo = s_lo - (s_lo + 8ull) / 9ull;
-                    const unsigned long long s_fin = 9ull * (((rawlen + 7ull) >> 3) - 1ull);   // control byte of the final group
-                    const uint32_t fin = (s_fin >= s_lo && s_fin < s_hi) ? (uint32_t)(rawlen & 7ull) : 0u;
-                    op.dst = (unsigned long long)((a ? A.out_dep + A.pos_dep[pos] : A.out_ind + A.pos_ind[pos]) + o_lo);
-                    op.src_off = ((loc.y & 0xFFFFu) + skip) | ((uint32_t)(s_lo % 9ull) << 16) | (fin << 20);
-                    op.len = n_stream | kOpLiteral;
-                } else if (compressed) {
-                    op.dst = (unsigned long long)(A.scratch + A.vscr[v]) + (unsigned long long)idx * kChunkMax;
-                } else if (a) {
-                    op.dst = (unsigned long long)(A.out_dep + A.pos_dep[pos]) + (unsigned long long)idx * kChunkMax;
-                } else if (quad) {
-                    const unsigned long long voff = (unsigned long long)idx * kChunkMax;     // byte (= pixel component) inside the value
-                    op.dst = (unsigned long long)(A.out_ind + ((A.pos_ind[pos] + voff) << 2));
-                    op.src_off |= (uint32_t)(voff % A.lut_channels) << 16;
-                    op.len = size | kOpU8Norm;
-                } else if (!half) {
-                    op.dst = (unsigned long long)(A.out_ind + A.pos_ind[pos]) + (unsigned long long)idx * kChunkMax;
-                } else if (((size | va_extsize) & 3u) == 0u && (A.pos_ind[pos] & 3ull) == 0ull) {
-                    op.dst = (unsigned long long)(A.out_ind + ((A.pos_ind[pos] + (unsigned long long)idx * kChunkMax) >> 1));
-                    op.len = size | kOpToBf16;
-                } else {
-                    report(st, 4, pos, 1, 1, CDS_ERR_SHAPE);                // not a whole number of float32 elements
-                    op.dst = 0;
-                }
+                op = make_copy_op(A, v, pos, idx, size, loc, va_rawsize, va_extsize, a ? A.dep_len[r] : A.ind_len[r]);
             }
         }
         A.ops[g] = op;
@@ -511,56 +577,15 @@ __device__ __forceinline__ void d_resolve(const PlanArgs &A)
     const uint32_t last_slot = 2u * n_rows - 1u;
     for (uint32_t v = tid; v < 2u * n_rows; v += nth) {
         PglzJob job;
-        job.src = 0; job.dst = 0; job.slen = kNone; job.rawsize = 0; job.err_key = 0;
+        job.slen = kNone;
         const uint32_t r = v >> 1, a = v & 1u;
         const uint32_t *row = rows + (size_t)r * kRowWords;
         const uint32_t pos = A.pos_of_row[r];
-        const unsigned long long my_ind_off = pos == kNone ? ~0ull : A.pos_ind[pos];
-        const unsigned long long my_dep_off = pos == kNone ? ~0ull : A.pos_dep[pos];
-        if (a == 0) { A.row_ind_off[r] = my_ind_off; A.row_dep_off[r] = my_dep_off; }   // exported to the host mirror
-        if (fits && pos != kNone && row[RW_INLINE_LEN] != kNone) {
-            if (a == 1 && row[RW_DEP_EXTERNAL] == 0) {
-                // inline datum: tupdata[24:] starts with the 8-byte PGLZ header (ppr:344, 537-543)
-                const uint8_t *src = A.heap + (((unsigned long long)row[RW_INLINE_OFF_HI] << 32) | row[RW_INLINE_OFF_LO]);
-                const uint32_t avail = row[RW_INLINE_LEN];
-                const uint32_t varsize = ld_u32be(src) & 0x3FFFFFFFu;
-                job.err_key = make_err_key(2, r, 0, 0, CDS_ERR_PGLZ_CORRUPT);
-                if (avail < 8u || varsize < 8u || varsize > avail) {
-                    report_key(st, job.err_key);
-                } else {
-                    job.src = (unsigned long long)(src + 8);
-                    job.slen = varsize - 8u;
-                    job.rawsize = (uint32_t)A.dep_len[r];
-                    job.dst = (unsigned long long)(A.out_dep + my_dep_off);
-                }
-            } else if (A.vcount[v] != 0) {
-                const uint32_t *ptr = row + (a ? RW_DEP : RW_IND);
-                const uint32_t va_rawsize = ptr[1], va_extsize = ptr[2];
-                const unsigned long long len = a ? A.dep_len[r] : A.ind_len[r];
-                const bool literal = va_extsize >= 4u && (a == 1u || !(half | quad)) && pglz_literal_only(va_extsize - 4u, len);
-                if (va_extsize != va_rawsize - 4u && !literal) {
-                    job.err_key = make_err_key(3, A.vfirst[v], 3, 0, CDS_ERR_PGLZ_CORRUPT);
-                    if (va_extsize < 4u) {
-                        report_key(st, job.err_key);
-                    } else {
-                        // staged payload = LE rawsize + stream (ppr:574-594 builds header + payload)
-                        job.src = (unsigned long long)(A.scratch + A.vscr[v] + 4);
-                        job.slen = va_extsize - 4u;
-                        job.rawsize = (uint32_t)len;
-                        if (a) job.dst = (unsigned long long)(A.out_dep + my_dep_off);
-                        else if (quad) { job.dst = (unsigned long long)(A.out_ind + (my_ind_off << 2)); job.slen |= kJobU8Norm; }
-                        else if (!half) job.dst = (unsigned long long)(A.out_ind + my_ind_off);
-                        else if ((len & 3ull) == 0ull && (my_ind_off & 3ull) == 0ull) {
-                            job.dst = (unsigned long long)(A.out_ind + (my_ind_off >> 1));
-                            job.slen |= kJobToBf16;
-                        } else {
-                            report(st, 4, pos, 1, 1, CDS_ERR_SHAPE);
-                            job.slen = kNone;
-                        }
-                    }
-                }
-            }
+        if (a == 0) {                                                        // exported to the host mirror
+            A.row_ind_off[r] = pos == kNone ? ~0ull : A.pos_ind[pos];
+            A.row_dep_off[r] = pos == kNone ? ~0ull : A.pos_dep[pos];
         }
+        if (fits && pos != kNone && row[RW_INLINE_LEN] != kNone) job = make_value_job(A, v, pos);
         if (job.slen != kNone) {
             // front list = the expensive streams (really compressed, not tiny): handed out first, so that the cheap ones
             // (literal-only streams copy 256 bytes per step; small labels) fill the tail of the launch
