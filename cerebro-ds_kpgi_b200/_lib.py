@@ -61,6 +61,8 @@ PROTOTYPES = {
                                  ctypes.POINTER(Summary)]),
     "cds_decode_host": (_int, [_vp, _vp, _u64, _vp, _u64, _u32, _u32, _vp, _u64, _vp, _u64, _vp,
                                ctypes.POINTER(Summary)]),
+    "cds_set_host_streaming": (_int, [_vp, _u32]),
+    "cds_stream_counts": (_int, [ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]),
     "cds_launch_count": (ctypes.c_ulonglong, []),
     "cds_timing_enable": (_int, [_vp, _u32]),
     "cds_timing_read": (_int, [_vp, _vp, _u32, _pu32]),

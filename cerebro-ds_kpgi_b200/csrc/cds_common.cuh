@@ -16,6 +16,7 @@ constexpr uint32_t kRowWords = CDS_ROW_WORDS;
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr unsigned long long kNoErr = ~0ull;
 constexpr uint32_t kFlagRowOverflow = 1u, kFlagChunkOverflow = 2u;
+constexpr uint32_t kFlagStreamRedo = 8u;  // the streamed decode assumed a plan that the complete directory does not bear out (or met an error): cds_finish decodes again
 constexpr uint32_t kFlagNeedWide = 4u;   // the classification took values for the wide decoder, whose kernels were not enqueued (cds_finish runs them)
 
 // row words (cds_export_rows layout)
@@ -42,7 +43,8 @@ struct DevState {
     uint32_t n_jobs_front;        // compacted pglz jobs: large values from slot 0 up ...
     uint32_t n_jobs_back;         // ... small values from the last slot down
     uint32_t n_wide;              // compressed values at or above the wide-decode threshold (pglz_wide.cuh)
-    uint32_t pad_[3];
+    uint32_t n_wide_taken;        // values the wide decoder accepted, summed over the classifications of this decode
+    uint32_t pad_[2];
 };
 
 // One TOAST chunk -> one copy.  dst == 0: chunk not referenced (or refused); nothing is copied.

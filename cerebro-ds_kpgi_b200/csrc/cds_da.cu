@@ -15,6 +15,7 @@
 #include "page_scan.cuh"
 #include "pglz_decode.cuh"
 #include "pglz_wide.cuh"
+#include "stream_decode.cuh"
 #include "text_etl.cuh"
 #include "toast_gather.cuh"
 #include "util_kernels.cuh"
@@ -27,6 +28,7 @@ static unsigned long long g_launches = 0;   // kernels launched by this library 
 static uint32_t g_wide_threshold = 1u << 20;   // cds_set_wide_pglz_threshold
 static int g_wide_force = 0;                   // ... its second argument: skip the cost model
 static unsigned long long g_wide_decoded = 0;  // values decoded by the wide decoder so far (cds_wide_decoded_count)
+static unsigned long long g_streamed = 0, g_stream_redone = 0;   // cds_decode_host calls that took the streamed path / were decoded again
 
 static int cuda_fail(cudaError_t e, const char *what)
 {
@@ -121,6 +123,15 @@ struct cds_segment {
     ScanWs ws[7];                               // heap index, TOAST index, inline rank, chunk rank, ind, dep, staging
     DevState *state = nullptr;
     DevState *h_state = nullptr;   // pinned
+    // streamed cds_decode_host (stream_decode.cuh): copy stream, one event per page range, the assumed plan
+    uint32_t stream_range_pages = 2048;   // cds_set_host_streaming: pages per range (0: off)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copy[kMaxStreamRanges + 2] = {};
+    StreamArgs sargs = {};
+    ScanWs ws_range[kMaxStreamRanges];
+    uint8_t *stream_mem = nullptr;
+    bool stream_pending = false;          // the last decode was streamed and has not been checked by cds_finish yet
+    struct { uint64_t n_heap_pages, n_toast_pages; uint32_t isb, dsb; void *out_ind, *out_dep; uint64_t ind_cap, dep_cap; } redo = {};
     // optional CUDA-event timing (cds_timing_enable): kTimedStages event pairs per sample
     cudaEvent_t *ev = nullptr;
     uint32_t ev_cap = 0, ev_used = 0;
@@ -245,9 +256,10 @@ static int wide_pipeline(WideArea wa, int num_sms, cudaStream_t st, cudaEvent_t 
 }
 
 static int launch_wide(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int num_sms, cudaStream_t st,
-                       bool with_pipeline = true, cudaEvent_t *ev4 = nullptr, unsigned ev_flags = cudaEventRecordDefault)
+                       bool with_pipeline = true, cudaEvent_t *ev4 = nullptr, unsigned ev_flags = cudaEventRecordDefault,
+                       const uint32_t *d_first = nullptr)
 {
-    k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa, with_pipeline ? 0 : 1);
+    k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa, with_pipeline ? 0 : 1, d_first);
     CU(cudaGetLastError());
     LAUNCHED(1);
     return with_pipeline ? wide_pipeline(wa, num_sms, st, ev4, ev_flags) : CDS_OK;
@@ -277,6 +289,9 @@ extern "C" int cds_segment_destroy(cds_segment *s)
                     s->row_first, s->pos_of_row, s->row_at_pos, s->ind_len, s->dep_len, s->pos_ind, s->pos_dep,
                     s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch, s->wide_mem};
     for (void *b : bufs) if (b) cudaFree(b);
+    if (s->stream_mem) cudaFree(s->stream_mem);
+    if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+    for (cudaEvent_t e : s->ev_copy) if (e) cudaEventDestroy(e);
     if (s->h_state) cudaFreeHost(s->h_state);
     if (s->d_lut) cudaFree(s->d_lut);
     if (s->ev) {
@@ -323,10 +338,16 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
         const uint64_t lens[7] = {max_heap_pages, max_toast_pages, R, C, R, R, V};
         uint64_t tiles[7], total_tiles = 0;
         for (int i = 0; i < 7; i++) { tiles[i] = lens[i] / kScanMinTile + 2; total_tiles += tiles[i]; }
-        const uint64_t state_bytes = 256, ws_bytes = ((8 + total_tiles) * 4 + 255) & ~255ull;
+        // streamed decode (only with stage buffers): 5 more scans for the assumed plan, one page-index scan per range,
+        // StreamState, the batch bookkeeping: all of it starts from zero too
+        const uint64_t range_tiles = max_toast_pages / kScanMinTile + 2;
+        uint64_t stream_tiles = 0;
+        if (stage_pages) stream_tiles = (R / kScanMinTile + 2) * 4 + (V / kScanMinTile + 2) + range_tiles * kMaxStreamRanges;
+        const uint64_t stream_words = stage_pages ? 16 + 2 * (kMaxStreamRanges + 2) + 8 + kMaxStreamRanges + stream_tiles : 0;
+        const uint64_t state_bytes = 256, ws_bytes = ((8 + total_tiles + stream_words) * 4 + 255) & ~255ull;
         s->zero_bytes = state_bytes + ws_bytes + hsize * 8;
         if (e == cudaSuccess) e = dalloc(&s->zero_region, s->zero_bytes);
-        if (e == cudaSuccess) e = dalloc(&s->scan_vals, 2 * total_tiles);
+        if (e == cudaSuccess) e = dalloc(&s->scan_vals, 2 * (total_tiles + stream_tiles));
         if (e == cudaSuccess) {
             s->state = reinterpret_cast<DevState *>(s->zero_region);
             uint32_t *w = reinterpret_cast<uint32_t *>(s->zero_region + state_bytes);
@@ -339,9 +360,39 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
                 s->ws[i].incl = s->scan_vals + 2 * t0 + tiles[i];
                 t0 += tiles[i];
             }
+            if (stage_pages) {
+                uint32_t *sw = w + 8 + total_tiles;                         // behind the classic scans' status words
+                s->sargs.ss = reinterpret_cast<StreamState *>(sw); sw += 16;
+                s->sargs.range_first = sw; sw += kMaxStreamRanges + 2;
+                s->sargs.range_ticket = sw; sw += kMaxStreamRanges + 2;
+                uint32_t *tickets = sw; sw += 8 + kMaxStreamRanges;
+                auto carve = [&](ScanWs &x, uint64_t nt, uint32_t *ticket) {
+                    x.ticket = ticket; x.status = sw; x.agg = s->scan_vals + 2 * t0; x.incl = s->scan_vals + 2 * t0 + nt;
+                    sw += nt; t0 += nt;
+                };
+                for (int i = 0; i < 4; i++) carve(s->sargs.ws[i], R / kScanMinTile + 2, tickets + i);
+                carve(s->sargs.ws[4], V / kScanMinTile + 2, tickets + 4);
+                for (uint32_t k = 0; k < kMaxStreamRanges; k++) carve(s->ws_range[k], range_tiles, tickets + 8 + k);
+            }
         }
     }
-    if (stage_pages) { A(stage_heap, max_heap_pages * (uint64_t)kPage); A(stage_toast, max_toast_pages * (uint64_t)kPage); }
+    if (stage_pages) {
+        A(stage_heap, max_heap_pages * (uint64_t)kPage); A(stage_toast, max_toast_pages * (uint64_t)kPage);
+        // the assumed plan of the streamed decode: [ext_flag R+1 | o_pos_of_row R | vjob V] u32, [o_ind_len R | o_dep_len R] u64
+        const uint64_t u32s = (R + 1) + R + V, bytes = ((u32s * 4 + 15) & ~15ull) + 16 * R;
+        A(stream_mem, bytes);
+        if (e == cudaSuccess) {
+            uint32_t *q = reinterpret_cast<uint32_t *>(s->stream_mem);
+            s->sargs.ext_flag = q; q += R + 1;
+            s->sargs.o_pos_of_row = q; q += R;
+            s->sargs.vjob = q;
+            unsigned long long *q8 = reinterpret_cast<unsigned long long *>(s->stream_mem + ((u32s * 4 + 15) & ~15ull));
+            s->sargs.o_ind_len = q8;
+            s->sargs.o_dep_len = q8 + R;
+            e = cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking);
+            for (uint32_t k = 0; e == cudaSuccess && k < kMaxStreamRanges + 2; k++) e = cudaEventCreateWithFlags(&s->ev_copy[k], cudaEventDisableTiming);
+        }
+    }
     if (s->cap_scratch) {
         // wide pglz: 8 bytes per 512-byte source segment of the staged (compressed) values
         const uint64_t cj = 1024, cs = s->cap_scratch / kWideSeg + cj * kWideSuper, cb = s->cap_scratch / kWideSeg + cj;
@@ -478,7 +529,7 @@ extern "C" int cds_toast_scan(cds_segment *s, const void *d_toast_pages, uint64_
     if (n_pages) {
         k_toast_walk<<<(uint32_t)((n_pages + 127) / 128), 128, 0, st>>>(
             s->d_toast, (uint32_t)n_pages, s->toast_base, s->htab, s->hmask, s->dir_id, s->dir_loc, s->dir_ref,
-            s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state);
+            s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state, 0u);
         CU(cudaGetLastError());
         LAUNCHED(1);
     }
@@ -626,13 +677,25 @@ extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
     if (!s) return CDS_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     ON_DEVICE(s->device);
-    WideState wide_counts;
-    memset(&wide_counts, 0, sizeof(wide_counts));
-    for (int pass = 0; pass < 2; pass++) {
+    for (int pass = 0; pass < 3; pass++) {
         CU(cudaMemcpyAsync(s->h_state, s->state, sizeof(DevState), cudaMemcpyDeviceToHost, st));
-        if (s->wide_launched) CU(cudaMemcpyAsync(&wide_counts, s->wide.state, sizeof(WideState), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
-        if (pass == 0 && s->wide_launched && (s->h_state->flags & kFlagNeedWide)) {
+        const uint32_t flags = s->h_state->flags;
+        if (s->stream_pending) {
+            // A streamed cds_decode_host: its assumed plan was compared with the complete directory on the device.
+            s->stream_pending = false;
+            if (flags & (kFlagStreamRedo | kFlagNeedWide)) {
+                // It does not hold (or an error was met, or large values turned up whose decoder was not enqueued): decode
+                // again the classic way from the pages, which are all in the stage buffers now.
+                g_stream_redone++;
+                if (flags & kFlagNeedWide) s->wide_hint = true;
+                int rc = cds_decode_device(s, s->stage_heap, s->redo.n_heap_pages, s->stage_toast, s->redo.n_toast_pages, s->redo.isb,
+                                           s->redo.dsb, s->redo.out_ind, s->redo.ind_cap, s->redo.out_dep, s->redo.dep_cap, stream, nullptr);
+                if (rc) return rc;
+                continue;
+            }
+        }
+        if (s->wide_launched && (flags & kFlagNeedWide)) {
             // The classification of this decode took values for the wide decoder, but its kernels were not enqueued with
             // the decode (the handle had not seen such values before): decode them now.  One extra round trip, once.
             k_clear_flag<<<1, 1, 0, st>>>(s->state, kFlagNeedWide);
@@ -643,14 +706,14 @@ extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
         }
         break;
     }
+    const DevState &h = *s->h_state;
     if (s->wide_launched) {
-        g_wide_decoded += wide_counts.n_taken;
-        s->wide_hint = wide_counts.n_taken != 0;
+        g_wide_decoded += h.n_wide_taken;
+        s->wide_hint = h.n_wide_taken != 0;
         s->wide_launched = false;
     }
     cds_summary local;
     memset(&local, 0, sizeof(local));
-    const DevState &h = *s->h_state;
     local.n_rows = h.n_rows; local.n_positions = h.n_pos; local.ind_bytes = h.ind_bytes; local.dep_bytes = h.dep_bytes;
     local.n_chunks = h.n_chunks; local.n_inline = h.n_inline; local.scratch_bytes = h.scratch_bytes;
     local.n_wide_values = h.n_wide;
@@ -704,7 +767,7 @@ extern "C" int cds_decode_device(cds_segment *s, const void *d_heap, uint64_t n_
         if (n_toast_pages) {
             k_toast_walk<<<(uint32_t)((n_toast_pages + 127) / 128), 128, 0, st>>>(
                 s->d_toast, (uint32_t)n_toast_pages, s->toast_base, s->htab, s->hmask, s->dir_id, s->dir_loc, s->dir_ref,
-                s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state);
+                s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state, 0u);
             CU(cudaGetLastError());
             LAUNCHED(1);
         }
@@ -720,18 +783,146 @@ extern "C" int cds_decode_device(cds_segment *s, const void *d_heap, uint64_t n_
     return sum ? cds_finish(s, stream, sum) : CDS_OK;
 }
 
+// The pglz stage over one batch of jobs (slots [*d_first, n_jobs_front) of the plain job list): streamed decode.
+static int launch_pglz_batch(cds_segment *s, const uint32_t *d_first, uint32_t *d_ticket, bool may_be_wide, cudaStream_t st)
+{
+    const float *lut = s->ind_format == 2 ? s->d_lut : nullptr;
+    if (may_be_wide && s->wide_mem && g_wide_threshold && s->wide_mode != 0) {
+        WideArea wa = s->wide;
+        wa.threshold = g_wide_threshold;
+        wa.force = (s->wide_mode == 1 || g_wide_force) ? 1u : 0u;
+        wa.st = s->state;
+        wa.lut = lut;
+        wa.lut_channels = s->lut_channels ? s->lut_channels : 1u;
+        s->last_wa = wa;
+        const bool pipeline = s->wide_mode != 2 || s->wide_hint;
+        int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st, pipeline, nullptr, cudaEventRecordDefault, d_first);
+        if (rc) return rc;
+        s->wide_launched = true;
+    }
+    k_pglz_decode<<<(uint32_t)s->num_sms * kPglzCtasPerSm, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
+        s->jobs, s->state, 0u, nullptr, s->state, d_ticket, lut, s->lut_channels, d_first);
+    CU(cudaGetLastError());
+    LAUNCHED(1);
+    return CDS_OK;
+}
+
+// cds_decode_host with the decode overlapped with the copy (stream_decode.cuh).  The heap goes first; the TOAST relation
+// follows in ranges of `stream_range_pages` pages on a copy stream, and each range is processed on `st` as soon as its
+// event has fired.  The check of the assumed plan is enqueued last; cds_finish reads its verdict.
+static int decode_host_streamed(cds_segment *s, const void *h_heap, uint64_t n_heap_pages, const void *h_toast, uint64_t n_toast_pages,
+                                uint32_t isb, uint32_t dsb, void *d_out_ind, uint64_t ind_cap, void *d_out_dep, uint64_t dep_cap,
+                                cudaStream_t st)
+{
+    const uint64_t rp = s->stream_range_pages;
+    const uint32_t n_ranges = (uint32_t)((n_toast_pages + rp - 1) / rp);
+    int rc;
+    if ((rc = reset_state(s, st))) return rc;
+    // the stage buffers may still be read by work enqueued earlier on `st`
+    CU(cudaEventRecord(s->ev_copy[kMaxStreamRanges + 1], st));
+    CU(cudaStreamWaitEvent(s->copy_stream, s->ev_copy[kMaxStreamRanges + 1], 0));
+    CU(cudaMemcpyAsync(s->stage_heap, h_heap, n_heap_pages * (uint64_t)kPage, cudaMemcpyHostToDevice, s->copy_stream));
+    CU(cudaEventRecord(s->ev_copy[kMaxStreamRanges], s->copy_stream));
+    for (uint32_t k = 0; k < n_ranges; k++) {
+        const uint64_t p0 = k * rp, np = (p0 + rp <= n_toast_pages ? rp : n_toast_pages - p0);
+        CU(cudaMemcpyAsync(s->stage_toast + p0 * kPage, static_cast<const uint8_t *>(h_toast) + p0 * kPage, np * (uint64_t)kPage,
+                           cudaMemcpyHostToDevice, s->copy_stream));
+        CU(cudaEventRecord(s->ev_copy[k], s->copy_stream));
+    }
+    s->d_heap = s->stage_heap; s->n_heap_pages = n_heap_pages;
+    s->d_toast = s->stage_toast; s->n_toast_pages = n_toast_pages;
+    // ---- heap: rows, value index, and the plan the heap alone implies
+    CU(cudaStreamWaitEvent(st, s->ev_copy[kMaxStreamRanges], 0));
+    k_page_index<<<scan_grid(s, n_heap_pages, 4), kScanThreads, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, s->state, 0,
+                                                                       (uint32_t)s->cap_rows, s->ws[0]);
+    {
+        uint64_t want = n_heap_pages * kHeapSub, cap = (uint64_t)s->num_sms * 16u;
+        k_heap_rows<<<(uint32_t)(want < cap ? want : cap), 64, 0, st>>>(s->d_heap, (uint32_t)n_heap_pages, s->heap_base, s->rows, s->state,
+                                                                      s->htab, s->hmask, s->vfirst, s->vcount, s->vbytes, s->vseq0);
+    }
+    PlanArgs A = plan_args(s, isb, dsb, d_out_ind, ind_cap, d_out_dep, dep_cap);
+    const StreamArgs S = s->sargs;
+    const uint32_t g = small_grid(s);
+    k_stream_rows<<<g, 256, 0, st>>>(A, S);
+    k_stream_scan1<<<dim3(scan_grid(s, s->cap_rows, 8), 2), kScanThreads, 0, st>>>(A, S);
+    k_stream_assign<<<g, 256, 0, st>>>(A, S);
+    k_stream_scan2<<<dim3(scan_grid(s, 2 * s->cap_rows, 8), 3), kScanThreads, 0, st>>>(A, S);
+    k_stream_mark<<<1, 1, 0, st>>>(s->state, S.range_first);
+    k_stream_inline_jobs<<<g, 256, 0, st>>>(A, S);
+    CU(cudaGetLastError());
+    LAUNCHED(8);
+    if ((rc = launch_pglz_batch(s, S.range_first, S.range_ticket, false, st))) return rc;
+    // ---- TOAST, range by range
+    for (uint32_t k = 0; k < n_ranges; k++) {
+        const uint64_t p0 = k * rp, np = (p0 + rp <= n_toast_pages ? rp : n_toast_pages - p0);
+        const uint8_t *pages = s->d_toast + p0 * kPage;
+        uint32_t *base = s->toast_base + p0;
+        CU(cudaStreamWaitEvent(st, s->ev_copy[k], 0));
+        k_page_index<<<scan_grid(s, np, 4), kScanThreads, 0, st>>>(pages, (uint32_t)np, base, s->state, 1, (uint32_t)s->cap_chunks, s->ws_range[k]);
+        k_stream_fixup<<<1, 256, 0, st>>>(base, (uint32_t)np, s->state, S.ss, (uint32_t)s->cap_chunks);
+        k_toast_walk<<<(uint32_t)((np + 127) / 128), 128, 0, st>>>(pages, (uint32_t)np, base, s->htab, s->hmask, s->dir_id, s->dir_loc, s->dir_ref,
+                                                                  s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state, (uint32_t)p0);
+        k_stream_mark<<<1, 1, 0, st>>>(s->state, S.range_first + k + 1);
+        k_stream_resolve<<<g, 256, 0, st>>>(A, S, base, base + np);
+        const uint32_t grid = (uint32_t)(np < (uint64_t)s->num_sms ? np : (uint64_t)s->num_sms);
+        k_toast_gather<<<grid, kGatherThreads, kGatherSmemBytes, st>>>(pages, (uint32_t)np, base, s->ops, s->state,
+                                                                       s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels, s->dir_ref, s->vfirst);
+        CU(cudaGetLastError());
+        LAUNCHED(6);
+        if ((rc = launch_pglz_batch(s, S.range_first + k + 1, S.range_ticket + k + 1, true, st))) return rc;
+    }
+    // ---- the classic plan and checks over the complete directory, compared with what was assumed
+    k_stream_prefinal<<<1, 1, 0, st>>>(s->state);
+    s->have_rows = s->have_chunks = true;
+    if ((rc = launch_plan(s, A, true, st))) return rc;
+    k_stream_compare<<<g, 256, 0, st>>>(A, S);
+    CU(cudaGetLastError());
+    LAUNCHED(2);
+    s->have_plan = s->have_ops = true;
+    s->stream_pending = true;
+    s->redo = {n_heap_pages, n_toast_pages, isb, dsb, d_out_ind, d_out_dep, ind_cap, dep_cap};
+    g_streamed++;
+    return CDS_OK;
+}
+
 extern "C" int cds_decode_host(cds_segment *s, const void *h_heap, uint64_t n_heap_pages, const void *h_toast,
                                uint64_t n_toast_pages, uint32_t isb, uint32_t dsb, void *d_out_ind, uint64_t ind_cap,
                                void *d_out_dep, uint64_t dep_cap, void *stream, cds_summary *sum)
 {
     if (!s || !s->stage_heap || !s->stage_toast) return CDS_ERR_ARG;
+    if ((!h_heap && n_heap_pages) || (!h_toast && n_toast_pages)) return CDS_ERR_ARG;
     if (n_heap_pages > s->cap_heap_pages || n_toast_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
     cudaStream_t st = (cudaStream_t)stream;
     ON_DEVICE(s->device);
+    // Streamed when the TOAST relation spans more than one range and the calling stream is not being captured (the copy
+    // stream and its events are the library's own).
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+    const uint64_t rp = s->stream_range_pages;
+    if (rp && n_heap_pages && n_toast_pages > rp && (n_toast_pages + rp - 1) / rp <= kMaxStreamRanges && cap == cudaStreamCaptureStatusNone &&
+        !(s->ev && s->ev_used < s->ev_cap)) {
+        int rc = decode_host_streamed(s, h_heap, n_heap_pages, h_toast, n_toast_pages, isb, dsb, d_out_ind, ind_cap, d_out_dep, dep_cap, st);
+        if (rc) return rc;
+        return sum ? cds_finish(s, stream, sum) : CDS_OK;
+    }
     CU(cudaMemcpyAsync(s->stage_heap, h_heap, n_heap_pages * (uint64_t)kPage, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s->stage_toast, h_toast, n_toast_pages * (uint64_t)kPage, cudaMemcpyHostToDevice, st));
     return cds_decode_device(s, s->stage_heap, n_heap_pages, s->stage_toast, n_toast_pages, isb, dsb, d_out_ind, ind_cap,
                              d_out_dep, dep_cap, stream, sum);
+}
+
+extern "C" int cds_set_host_streaming(cds_segment *s, uint32_t range_pages)
+{
+    if (!s) return CDS_ERR_ARG;
+    s->stream_range_pages = range_pages;
+    return CDS_OK;
+}
+
+extern "C" int cds_stream_counts(unsigned long long *streamed, unsigned long long *decoded_again)
+{
+    if (streamed) *streamed = g_streamed;
+    if (decoded_again) *decoded_again = g_stream_redone;
+    return CDS_OK;
 }
 
 // ---- measurement hooks ---------------------------------------------------------------------------

@@ -209,8 +209,9 @@ k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t
              const unsigned long long *__restrict__ htab, uint32_t hmask,
              uint2 *__restrict__ dir_id, uint2 *__restrict__ dir_loc, uint32_t *__restrict__ dir_ref,
              uint32_t *__restrict__ chunk_flag,
-             uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0, DevState *st)
+             uint32_t *vfirst, uint32_t *vcount, unsigned long long *vbytes, uint32_t *vseq0, DevState *st, uint32_t page0)
 {
+    // (`toast`, `base`: the first page of this launch, which is page `page0` of the relation)
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pages || (st->flags & kFlagChunkOverflow)) return;
     const uint8_t *pg = toast + (size_t)p * kPage;
@@ -278,7 +279,7 @@ k_toast_walk(const uint8_t *__restrict__ toast, uint32_t n_pages, const uint32_t
             }
         }
         dir_id[g] = make_uint2(id, seq);
-        dir_loc[g] = make_uint2(p, loc_off | (loc_len << 16));
+        dir_loc[g] = make_uint2(page0 + p, loc_off | (loc_len << 16));
         dir_ref[g] = (ref == kNone) ? kNone : (ref | ((hdr0 & 0xC0u) ? 0x40000000u : 0u));
         chunk_flag[g] = 0;
     }

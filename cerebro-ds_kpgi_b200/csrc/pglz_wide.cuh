@@ -200,12 +200,14 @@ __device__ __forceinline__ bool wide_candidate(const PglzJob &job, uint32_t thre
 }
 
 // (A block of 1024 threads; every thread of the block must call it.)
-__device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, const WideArea &wa)
+__device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, const WideArea &wa,
+                                                const uint32_t *d_first)
 {
     __shared__ uint32_t sh_w[3][32];
     __shared__ uint32_t sh_base[3];
-    const uint32_t front = st_counts ? st_counts->n_jobs_front : n_jobs_host;
-    const uint32_t back = st_counts ? st_counts->n_jobs_back : 0u;
+    const uint32_t first = d_first ? *d_first : 0u;                          // streamed decode: slots [*d_first, n_jobs_front)
+    const uint32_t front = (st_counts ? st_counts->n_jobs_front : n_jobs_host) - first;
+    const uint32_t back = (st_counts && !d_first) ? st_counts->n_jobs_back : 0u;
     const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
     const uint32_t n_jobs = front + back, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x < 3) sh_base[threadIdx.x] = 0;
@@ -215,7 +217,7 @@ __device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *s
     if (!wa.force) {
         unsigned long long sum_raw = 0, sum_units = 0, max_units = 0;
         for (uint32_t t = threadIdx.x; t < n_jobs; t += blockDim.x) {
-            const PglzJob job = jobs[t < front ? t : last_slot - (t - front)];
+            const PglzJob job = jobs[t < front ? first + t : last_slot - (t - front)];
             if (!wide_candidate(job, wa.threshold)) continue;
             const unsigned long long units = (unsigned long long)job.rawsize *
                                              ((unsigned long long)(job.slen & ~kFlagBits) * 8ull < job.rawsize ? kWarpUnitsSparse : kWarpUnitsDense);
@@ -243,7 +245,7 @@ __device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *s
     }
     for (uint32_t base = 0; base < n_jobs; base += blockDim.x) {
         const uint32_t t = base + threadIdx.x;
-        const uint32_t j = t < front ? t : last_slot - (t - front);
+        const uint32_t j = t < front ? first + t : last_slot - (t - front);
         PglzJob job;
         job.slen = kNone;
         if (t < n_jobs) job = jobs[j];
@@ -302,14 +304,18 @@ __device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *s
 // The WideState header is cleared here (the rest of the zeroed area only matters to the kernels that follow).
 // deferred != 0: those kernels were not enqueued with this decode; tell cds_finish when they are needed after all.
 __global__ void __launch_bounds__(1024)
-k_wide_classify(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int deferred)
+k_wide_classify(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int deferred, const uint32_t *d_first)
 {
     if (st_counts) {                                       // (the batch entry points clear the header with a memset)
         if (threadIdx.x < sizeof(WideState) / 4u) reinterpret_cast<uint32_t *>(wa.state)[threadIdx.x] = 0u;
         __syncthreads();
     }
-    d_wide_classify(jobs, st_counts, n_jobs_host, wa);
-    if (deferred && threadIdx.x == 0 && wa.state->n_jobs != 0u && st_counts) atomicOr(&st_counts->flags, kFlagNeedWide);
+    d_wide_classify(jobs, st_counts, n_jobs_host, wa, d_first);
+    __syncthreads();
+    if (threadIdx.x == 0 && st_counts) {
+        if (wa.state->n_taken) atomicAdd(&st_counts->n_wide_taken, wa.state->n_taken);
+        if (deferred && wa.state->n_jobs != 0u) atomicOr(&st_counts->flags, kFlagNeedWide);
+    }
 }
 
 // Clears the scan status words and the block flags behind the WideState header (the device-launched pipeline:

@@ -143,13 +143,27 @@ int cds_decode_device(cds_segment *seg, const void *d_heap_pages, uint64_t n_hea
                       void *d_out_ind, uint64_t ind_cap_bytes, void *d_out_dep, uint64_t dep_cap_bytes,
                       void *stream, cds_summary *summary);
 
-/* Same with HOST page buffers (pinned for async copies): H2D over `stream`, then the device
- * path.  Needs a handle created with stage_pages != 0. */
+/* Same with HOST page buffers (pinned for async copies).  Needs a handle created with stage_pages != 0.
+ * The decode is overlapped with the copy (the reference reads and parses page by page, ppr:358-379): the heap goes
+ * first, the TOAST relation follows in ranges of pages on the library's own copy stream, and every range is indexed,
+ * walked, gathered and its completed values decompressed on `stream` as soon as it has arrived.  That needs the plan
+ * before the TOAST relation is there; it is taken from the heap alone, assuming that external values lie in the TOAST
+ * relation in table order and that a value decodes to va_rawsize - 4 bytes — true of every table a loader writes.  The
+ * complete chunk directory is checked against that plan at the end; if it does not bear it out, or any error was
+ * met, cds_finish decodes the segment again the classic way from the pages (all on the device by then), so results,
+ * status codes and their order are those of cds_decode_device in every case.  As with the other entry points, the
+ * outputs of an enqueue-only call (summary == NULL) are final once cds_finish has returned.
+ * Not streamed: relations of a single range, a `stream` that is being captured, a call with timing enabled. */
 int cds_decode_host(cds_segment *seg, const void *h_heap_pages, uint64_t n_heap_pages,
                     const void *h_toast_pages, uint64_t n_toast_pages,
                     uint32_t ind_sample_bytes, uint32_t dep_sample_bytes,
                     void *d_out_ind, uint64_t ind_cap_bytes, void *d_out_dep, uint64_t dep_cap_bytes,
                     void *stream, cds_summary *summary);
+
+/* Pages per range of the streamed cds_decode_host (default 2048 = 64 MiB; 0 = copy everything, then decode). */
+int cds_set_host_streaming(cds_segment *seg, uint32_t range_pages);
+/* cds_decode_host calls of this process that were streamed, and how many of those cds_finish had to decode again. */
+int cds_stream_counts(unsigned long long *streamed, unsigned long long *decoded_again);
 
 /* ---- measurement hooks (bench.py) ------------------------------------------------------------ */
 

@@ -1,0 +1,155 @@
+"""The streamed cds_decode_host (decode overlapped with its own host -> HBM copy, csrc/stream_decode.cuh) against the
+classic decode of the same pages: same bytes, same status, same summary — on segments cut into ranges of one to three
+pages, so that nearly every value straddles a range edge.  Segments whose TOAST order differs from the table order, and
+damaged segments, must come out exactly as the classic path gives them (cds_finish decodes them again)."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, SEGMENT_CASES, load_golden_segment
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("GPU tests need a CUDA device")
+    torch.cuda.set_device(0)
+    return torch
+
+
+def stream_counts(L):
+    a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+    L.cds_stream_counts(ctypes.byref(a), ctypes.byref(b))
+    return int(a.value), int(b.value)
+
+
+def both_ways(torch, heap, toast, range_pages, fmt=None, isb=0, dsb=0):
+    """Decode (heap, toast) with cds_decode_device and with the streamed cds_decode_host.  Returns both results."""
+    from cerebro_ds_kpgi_b200 import _lib, segment
+    L = _lib.require_device()
+    heap, toast = np.ascontiguousarray(heap), np.ascontiguousarray(toast)
+    hp, tp = heap.size // 32768, toast.size // 32768
+    ds = segment.DeviceSegment(hp, tp, device=0, stage=True)
+    if fmt == "bf16":
+        ds.set_output_format(True)
+    elif fmt == "u8norm":
+        from cerebro_ds_kpgi_b200 import synth
+        ds.set_output_format(False, synth.norm_lut())
+    cap_i = 4 * (heap.size + 12 * toast.size) + 4096
+    cap_d = heap.size + 12 * toast.size + 4096
+    res = []
+    for mode in ("device", "host"):
+        out_ind = torch.full((cap_i,), 0xC3, dtype=torch.uint8, device="cuda")
+        out_dep = torch.full((cap_d,), 0x3C, dtype=torch.uint8, device="cuda")
+        if mode == "device":
+            s = ds.decode_device(torch.from_numpy(heap).cuda(), torch.from_numpy(toast).cuda(), out_ind, out_dep, isb, dsb)
+        else:
+            _lib.check(L.cds_set_host_streaming(ds._h, range_pages))
+            ph, pt = segment.PinnedBuffer(heap.size), segment.PinnedBuffer(toast.size)
+            ph.array[:] = heap
+            pt.array[:] = toast
+            before = stream_counts(L)
+            s = ds.decode_host(ph.array, pt.array, out_ind, out_dep, isb, dsb)
+            after = stream_counts(L)
+            res.append((after[0] - before[0], after[1] - before[1]))
+        torch.cuda.synchronize()
+        res.append((s, out_ind.cpu().numpy(), out_dep.cpu().numpy()))
+    ds.close()
+    (s_a, ind_a, dep_a), counts, (s_b, ind_b, dep_b) = res[0], res[1], res[2]
+    return s_a, ind_a, dep_a, s_b, ind_b, dep_b, counts
+
+
+def assert_same(s_a, ind_a, dep_a, s_b, ind_b, dep_b):
+    for f in ("status", "err_stage", "err_where", "n_rows", "n_positions", "ind_bytes", "dep_bytes", "n_chunks", "n_inline"):
+        assert getattr(s_a, f) == getattr(s_b, f), f
+    if s_a.status == 0:
+        assert ind_a.tobytes() == ind_b.tobytes()          # includes the untouched bytes behind the values
+        assert dep_a.tobytes() == dep_b.tobytes()
+
+
+@pytest.mark.parametrize("name", SEGMENT_CASES)
+@pytest.mark.parametrize("range_pages", [1, 3])
+def test_streamed_matches_classic_on_golden_segments(name, range_pages, torch_cuda):
+    heap, toast, order, expected = load_golden_segment(name)
+    if toast.size // 32768 <= range_pages:
+        pytest.skip("a single range is not streamed")
+    r = both_ways(torch_cuda, heap, toast, range_pages)
+    assert_same(*r[:6])
+    streamed, redone = r[6]
+    assert streamed == 1
+    # the two segments written in a scrambled TOAST order do not bear the assumed plan out
+    assert redone == (1 if "shuffled" in name else 0), (name, redone)
+
+
+def test_streamed_config_shapes_and_formats(torch_cuda):
+    """Rows of BASELINE's shapes in every storage form, ranges of 2 pages (an ImageNet row spans 5): plain, bfloat16 and
+    uint8 -> normalised float32 outputs."""
+    from cerebro_ds_kpgi_b200 import synth
+    a_ind, a_dep = synth.imagenet_rows(9, seed=31, kind="norm_u8")
+    b_ind, b_dep = synth.imagenet_rows(9, seed=32, kind="normal")
+    seg = synth.build_segment(a_ind + b_ind, a_dep + b_dep,
+                              ind_storage=["ext_pglz", "ext_raw", "ext_literal"] * 6,
+                              dep_storage=["inline_pglz", "inline_literal", "inline_pglz"] * 6)
+    for fmt in (None, "bf16"):
+        r = both_ways(torch_cuda, seg.heap, seg.toast, 2, fmt=fmt, isb=150528, dsb=2000)
+        assert r[0].status == 0 and r[6] == (1, 0), fmt
+        assert_same(*r[:6])
+    # external dependent_var: the order comes from the TOAST walk; written in table order it is what the heap implies
+    seg = synth.build_segment(a_ind, a_dep, ind_storage="ext_pglz", dep_storage=["ext_raw", "ext_pglz", "ext_literal"] * 3)
+    r = both_ways(torch_cuda, seg.heap, seg.toast, 2, isb=150528, dsb=2000)
+    assert r[0].status == 0 and r[6] == (1, 0)
+    assert_same(*r[:6])
+    # uint8 pixels leaving as normalised float32
+    px = [np.random.default_rng(5 + i).integers(0, 256, (1, 112, 112, 3), dtype=np.uint8) for i in range(6)]
+    seg = synth.build_segment(px, a_dep[:6], ind_storage=["ext_pglz", "ext_raw"] * 3, dep_storage="inline_pglz")
+    r = both_ways(torch_cuda, seg.heap, seg.toast, 1, fmt="u8norm")
+    assert r[0].status == 0 and r[6] == (1, 0)
+    assert_same(*r[:6])
+
+
+def test_streamed_packed_buffers_go_wide(torch_cuda):
+    """Values large enough for the intra-value parallel decoder, completed in different ranges."""
+    from cerebro_ds_kpgi_b200 import _lib, synth
+    L = _lib.require_device()
+    ind, dep = synth.imagenet_rows(3, seed=77, kind="norm_u8", images_per_row=12)          # 1.8 MB per value
+    seg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="ext_pglz")
+    before = int(L.cds_wide_decoded_count())
+    r = both_ways(torch_cuda, seg.heap, seg.toast, 16)
+    assert r[0].status == 0
+    assert_same(*r[:6])
+    assert int(L.cds_wide_decoded_count()) - before >= 6          # three values, both ways
+    assert r[6][0] == 1
+
+
+def test_streamed_damaged_segments_report_what_the_classic_path_reports(torch_cuda):
+    z = np.load(os.path.join(GOLDEN, "error_cases.npz"))
+    checked = 0
+    for i, name in enumerate(z["names"]):
+        name = str(name)
+        heap, toast = z["heap_%d" % i], z["toast_%d" % i]
+        if name in ("partial_page", "shape_mismatch") or toast.size // 32768 < 2:
+            continue
+        r = both_ways(torch_cuda, heap, toast, 1)
+        assert r[0].status != 0, name
+        assert_same(*r[:6])
+        checked += 1
+    assert checked >= 3
+    # random damage on a multi-range segment: a flipped byte anywhere in the TOAST relation
+    from cerebro_ds_kpgi_b200 import synth
+    ind, dep = synth.imagenet_rows(10, seed=9, shape=(40, 40, 3), classes=30)
+    seg = synth.build_segment(ind, dep, ind_storage=["ext_pglz", "ext_literal"] * 5, dep_storage=["inline_pglz", "ext_pglz"] * 5)
+    rng = np.random.default_rng(123)
+    n_bad = 0
+    for _ in range(25):
+        toast = seg.toast.copy()
+        k = int(rng.integers(0, toast.size))
+        toast[k] ^= int(rng.integers(1, 256))
+        r = both_ways(torch_cuda, seg.heap, toast, 2)
+        assert_same(*r[:6])
+        n_bad += int(r[0].status != 0)
+    assert n_bad >= 3
