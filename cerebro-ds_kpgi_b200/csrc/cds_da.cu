@@ -81,6 +81,7 @@ static int current_sm_count()
     return sm_count(dev);
 }
 
+constexpr uint32_t kStreamDecoders = 4;
 constexpr uint32_t kTimedStages = 4;   // 0 gather, 1 pglz stage (classify + wide + warp decoder), 2 / 3 the wide block passes
 
 struct cds_segment {
@@ -127,6 +128,8 @@ struct cds_segment {
     uint32_t stream_range_pages = 2048;   // cds_set_host_streaming: pages per range (0: off)
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_copy[kMaxStreamRanges + 2] = {};
+    cudaStream_t dec_stream[kStreamDecoders] = {};           // the warp decoder of each batch runs beside the main stream
+    cudaEvent_t ev_batch[kMaxStreamRanges + 1] = {}, ev_dec[kStreamDecoders] = {};
     StreamArgs sargs = {};
     ScanWs ws_range[kMaxStreamRanges];
     uint8_t *stream_mem = nullptr;
@@ -259,7 +262,7 @@ static int launch_wide(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host,
                        bool with_pipeline = true, cudaEvent_t *ev4 = nullptr, unsigned ev_flags = cudaEventRecordDefault,
                        const uint32_t *d_first = nullptr)
 {
-    k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa, with_pipeline ? 0 : 1, d_first);
+    k_wide_classify<<<1, 1024, 0, st>>>(jobs, st_counts, n_jobs_host, wa, with_pipeline ? 0 : 1, d_first, d_first ? d_first + 1 : nullptr);
     CU(cudaGetLastError());
     LAUNCHED(1);
     return with_pipeline ? wide_pipeline(wa, num_sms, st, ev4, ev_flags) : CDS_OK;
@@ -291,7 +294,10 @@ extern "C" int cds_segment_destroy(cds_segment *s)
     for (void *b : bufs) if (b) cudaFree(b);
     if (s->stream_mem) cudaFree(s->stream_mem);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+    for (cudaStream_t x : s->dec_stream) if (x) cudaStreamDestroy(x);
     for (cudaEvent_t e : s->ev_copy) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : s->ev_batch) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : s->ev_dec) if (e) cudaEventDestroy(e);
     if (s->h_state) cudaFreeHost(s->h_state);
     if (s->d_lut) cudaFree(s->d_lut);
     if (s->ev) {
@@ -391,6 +397,11 @@ extern "C" int cds_segment_create(cds_segment **out, int device, uint64_t max_he
             s->sargs.o_dep_len = q8 + R;
             e = cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking);
             for (uint32_t k = 0; e == cudaSuccess && k < kMaxStreamRanges + 2; k++) e = cudaEventCreateWithFlags(&s->ev_copy[k], cudaEventDisableTiming);
+            for (uint32_t k = 0; e == cudaSuccess && k < kMaxStreamRanges + 1; k++) e = cudaEventCreateWithFlags(&s->ev_batch[k], cudaEventDisableTiming);
+            for (uint32_t k = 0; e == cudaSuccess && k < kStreamDecoders; k++) {
+                e = cudaStreamCreateWithFlags(&s->dec_stream[k], cudaStreamNonBlocking);
+                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->ev_dec[k], cudaEventDisableTiming);
+            }
         }
     }
     if (s->cap_scratch) {
@@ -783,10 +794,14 @@ extern "C" int cds_decode_device(cds_segment *s, const void *d_heap, uint64_t n_
     return sum ? cds_finish(s, stream, sum) : CDS_OK;
 }
 
-// The pglz stage over one batch of jobs (slots [*d_first, n_jobs_front) of the plain job list): streamed decode.
-static int launch_pglz_batch(cds_segment *s, const uint32_t *d_first, uint32_t *d_ticket, bool may_be_wide, cudaStream_t st)
+// The pglz stage over batch j of the streamed decode (slots [range_first[j], range_first[j + 1]) of the plain job list).
+// The classification and the wide decoder share one work area, so they stay on the main stream; the warp decoder of the
+// batch runs on a side stream, beside the ranges that follow (a 150 KB value keeps its warp busy for milliseconds: batches
+// must overlap each other, or the decode falls behind the copy).
+static int launch_pglz_batch(cds_segment *s, uint32_t j, bool may_be_wide, cudaStream_t st)
 {
     const float *lut = s->ind_format == 2 ? s->d_lut : nullptr;
+    const uint32_t *d_first = s->sargs.range_first + j;
     if (may_be_wide && s->wide_mem && g_wide_threshold && s->wide_mode != 0) {
         WideArea wa = s->wide;
         wa.threshold = g_wide_threshold;
@@ -800,8 +815,11 @@ static int launch_pglz_batch(cds_segment *s, const uint32_t *d_first, uint32_t *
         if (rc) return rc;
         s->wide_launched = true;
     }
-    k_pglz_decode<<<(uint32_t)s->num_sms * kPglzCtasPerSm, 32 * kPglzWarps, kPglzSmemBytes, st>>>(
-        s->jobs, s->state, 0u, nullptr, s->state, d_ticket, lut, s->lut_channels, d_first);
+    cudaStream_t side = s->dec_stream[j % kStreamDecoders];
+    CU(cudaEventRecord(s->ev_batch[j], st));
+    CU(cudaStreamWaitEvent(side, s->ev_batch[j], 0));
+    k_pglz_decode<<<(uint32_t)s->num_sms * kPglzCtasPerSm, 32 * kPglzWarps, kPglzSmemBytes, side>>>(
+        s->jobs, s->state, 0u, nullptr, s->state, s->sargs.range_ticket + j, lut, s->lut_channels, d_first, d_first + 1);
     CU(cudaGetLastError());
     LAUNCHED(1);
     return CDS_OK;
@@ -849,9 +867,10 @@ static int decode_host_streamed(cds_segment *s, const void *h_heap, uint64_t n_h
     k_stream_scan2<<<dim3(scan_grid(s, 2 * s->cap_rows, 8), 3), kScanThreads, 0, st>>>(A, S);
     k_stream_mark<<<1, 1, 0, st>>>(s->state, S.range_first);
     k_stream_inline_jobs<<<g, 256, 0, st>>>(A, S);
+    k_stream_mark<<<1, 1, 0, st>>>(s->state, S.range_first + 1);
     CU(cudaGetLastError());
-    LAUNCHED(8);
-    if ((rc = launch_pglz_batch(s, S.range_first, S.range_ticket, false, st))) return rc;
+    LAUNCHED(9);
+    if ((rc = launch_pglz_batch(s, 0, false, st))) return rc;
     // ---- TOAST, range by range
     for (uint32_t k = 0; k < n_ranges; k++) {
         const uint64_t p0 = k * rp, np = (p0 + rp <= n_toast_pages ? rp : n_toast_pages - p0);
@@ -862,14 +881,20 @@ static int decode_host_streamed(cds_segment *s, const void *h_heap, uint64_t n_h
         k_stream_fixup<<<1, 256, 0, st>>>(base, (uint32_t)np, s->state, S.ss, (uint32_t)s->cap_chunks);
         k_toast_walk<<<(uint32_t)((np + 127) / 128), 128, 0, st>>>(pages, (uint32_t)np, base, s->htab, s->hmask, s->dir_id, s->dir_loc, s->dir_ref,
                                                                   s->chunk_flag, s->vfirst, s->vcount, s->vbytes, s->vseq0, s->state, (uint32_t)p0);
-        k_stream_mark<<<1, 1, 0, st>>>(s->state, S.range_first + k + 1);
         k_stream_resolve<<<g, 256, 0, st>>>(A, S, base, base + np);
+        k_stream_mark<<<1, 1, 0, st>>>(s->state, S.range_first + k + 2);
         const uint32_t grid = (uint32_t)(np < (uint64_t)s->num_sms ? np : (uint64_t)s->num_sms);
         k_toast_gather<<<grid, kGatherThreads, kGatherSmemBytes, st>>>(pages, (uint32_t)np, base, s->ops, s->state,
                                                                        s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels, s->dir_ref, s->vfirst);
         CU(cudaGetLastError());
         LAUNCHED(6);
-        if ((rc = launch_pglz_batch(s, S.range_first + k + 1, S.range_ticket + k + 1, true, st))) return rc;
+        if ((rc = launch_pglz_batch(s, k + 1, true, st))) return rc;
+    }
+    // the decoders of all batches join `st` here: what follows rebuilds the job list they read, and whatever the caller
+    // enqueues on `st` next must see the complete decode
+    for (uint32_t i = 0; i < kStreamDecoders; i++) {
+        CU(cudaEventRecord(s->ev_dec[i], s->dec_stream[i]));
+        CU(cudaStreamWaitEvent(st, s->ev_dec[i], 0));
     }
     // ---- the classic plan and checks over the complete directory, compared with what was assumed
     k_stream_prefinal<<<1, 1, 0, st>>>(s->state);

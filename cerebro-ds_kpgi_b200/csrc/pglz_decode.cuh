@@ -558,14 +558,14 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
 __global__ void __launch_bounds__(32 * kPglzWarps, 2)
 k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint32_t n_jobs_host,
               int32_t *status, DevState *st, uint32_t *ticket, const float *__restrict__ lut, uint32_t lut_channels,
-              const uint32_t *d_first = nullptr)
+              const uint32_t *d_first = nullptr, const uint32_t *d_end = nullptr)
 {
     extern __shared__ __align__(16) uint8_t smem_ring[];
     uint8_t *ring = smem_ring + (size_t)(threadIdx.x >> 5) * kRing;
     const uint32_t lane = threadIdx.x & 31;
-    // d_first (streamed decode): the jobs are slots [*d_first, n_jobs_front) of a plain list
+    // d_first, d_end (streamed decode): the jobs are slots [*d_first, *d_end) of a plain list
     const uint32_t first = d_first ? *d_first : 0u;
-    const uint32_t front = (st_counts ? st_counts->n_jobs_front : n_jobs_host) - first;
+    const uint32_t front = (d_end ? *d_end : st_counts ? st_counts->n_jobs_front : n_jobs_host) - first;
     const uint32_t back = (st_counts && !d_first) ? st_counts->n_jobs_back : 0u;
     const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
     const uint32_t n_jobs = front + back;

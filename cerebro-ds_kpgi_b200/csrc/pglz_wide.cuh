@@ -201,12 +201,12 @@ __device__ __forceinline__ bool wide_candidate(const PglzJob &job, uint32_t thre
 
 // (A block of 1024 threads; every thread of the block must call it.)
 __device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *st_counts, uint32_t n_jobs_host, const WideArea &wa,
-                                                const uint32_t *d_first)
+                                                const uint32_t *d_first, const uint32_t *d_end)
 {
     __shared__ uint32_t sh_w[3][32];
     __shared__ uint32_t sh_base[3];
-    const uint32_t first = d_first ? *d_first : 0u;                          // streamed decode: slots [*d_first, n_jobs_front)
-    const uint32_t front = (st_counts ? st_counts->n_jobs_front : n_jobs_host) - first;
+    const uint32_t first = d_first ? *d_first : 0u;                          // streamed decode: slots [*d_first, *d_end)
+    const uint32_t front = (d_end ? *d_end : st_counts ? st_counts->n_jobs_front : n_jobs_host) - first;
     const uint32_t back = (st_counts && !d_first) ? st_counts->n_jobs_back : 0u;
     const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
     const uint32_t n_jobs = front + back, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -304,13 +304,14 @@ __device__ __forceinline__ void d_wide_classify(PglzJob *jobs, const DevState *s
 // The WideState header is cleared here (the rest of the zeroed area only matters to the kernels that follow).
 // deferred != 0: those kernels were not enqueued with this decode; tell cds_finish when they are needed after all.
 __global__ void __launch_bounds__(1024)
-k_wide_classify(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int deferred, const uint32_t *d_first)
+k_wide_classify(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host, WideArea wa, int deferred, const uint32_t *d_first,
+                const uint32_t *d_end)
 {
     if (st_counts) {                                       // (the batch entry points clear the header with a memset)
         if (threadIdx.x < sizeof(WideState) / 4u) reinterpret_cast<uint32_t *>(wa.state)[threadIdx.x] = 0u;
         __syncthreads();
     }
-    d_wide_classify(jobs, st_counts, n_jobs_host, wa, d_first);
+    d_wide_classify(jobs, st_counts, n_jobs_host, wa, d_first, d_end);
     __syncthreads();
     if (threadIdx.x == 0 && st_counts) {
         if (wa.state->n_taken) atomicAdd(&st_counts->n_wide_taken, wa.state->n_taken);

@@ -82,8 +82,14 @@ def test_streamed_matches_classic_on_golden_segments(name, range_pages, torch_cu
     assert_same(*r[:6])
     streamed, redone = r[6]
     assert streamed == 1
-    # the two segments written in a scrambled TOAST order do not bear the assumed plan out
-    assert redone == (1 if "shuffled" in name else 0), (name, redone)
+    # Rows with an inline dependent_var enter the result in table order whatever the TOAST relation looks like; the
+    # segments written in a scrambled TOAST order do not bear the assumed plan out and are decoded again.  (So are small
+    # external values that START in the same page: the walk goes up a page from pd_upper, i.e. against the order in which
+    # the tuples were added, ppr:391-414.  Values of more than a page, like every value of BASELINE's tables, do not.)
+    if name in ("seg_imagenet_rows", "seg_criteo"):
+        assert redone == 0, (name, redone)
+    if "shuffled" in name:
+        assert redone == 1, (name, redone)
 
 
 def test_streamed_config_shapes_and_formats(torch_cuda):
@@ -145,9 +151,12 @@ def test_streamed_damaged_segments_report_what_the_classic_path_reports(torch_cu
     seg = synth.build_segment(ind, dep, ind_storage=["ext_pglz", "ext_literal"] * 5, dep_storage=["inline_pglz", "ext_pglz"] * 5)
     rng = np.random.default_rng(123)
     n_bad = 0
-    for _ in range(25):
+    for trial in range(30):
         toast = seg.toast.copy()
-        k = int(rng.integers(0, toast.size))
+        if trial % 2:                                        # a page header field (pd_lower .. pd_special)
+            k = int(rng.integers(0, toast.size // 32768)) * 32768 + int(rng.integers(12, 18))
+        else:
+            k = int(rng.integers(0, toast.size))
         toast[k] ^= int(rng.integers(1, 256))
         r = both_ways(torch_cuda, seg.heap, toast, 2)
         assert_same(*r[:6])
