@@ -919,12 +919,13 @@ extern "C" int cds_decode_host(cds_segment *s, const void *h_heap, uint64_t n_he
     if (n_heap_pages > s->cap_heap_pages || n_toast_pages > s->cap_toast_pages) return CDS_ERR_CAPACITY;
     cudaStream_t st = (cudaStream_t)stream;
     ON_DEVICE(s->device);
-    // Streamed when the TOAST relation spans more than one range and the calling stream is not being captured (the copy
+    // Streamed when the TOAST relation spans more than three ranges (below that the copy is too short to hide anything: a
+    // Criteo segment of 104 MiB copies in 2 ms and decodes in 10) and the calling stream is not being captured (the copy
     // stream and its events are the library's own).
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
     const uint64_t rp = s->stream_range_pages;
-    if (rp && n_heap_pages && n_toast_pages > rp && (n_toast_pages + rp - 1) / rp <= kMaxStreamRanges && cap == cudaStreamCaptureStatusNone &&
+    if (rp && n_heap_pages && n_toast_pages > 3 * rp && (n_toast_pages + rp - 1) / rp <= kMaxStreamRanges && cap == cudaStreamCaptureStatusNone &&
         !(s->ev && s->ev_used < s->ev_cap)) {
         int rc = decode_host_streamed(s, h_heap, n_heap_pages, h_toast, n_toast_pages, isb, dsb, d_out_ind, ind_cap, d_out_dep, dep_cap, st);
         if (rc) return rc;

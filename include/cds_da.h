@@ -153,7 +153,8 @@ int cds_decode_device(cds_segment *seg, const void *d_heap_pages, uint64_t n_hea
  * met, cds_finish decodes the segment again the classic way from the pages (all on the device by then), so results,
  * status codes and their order are those of cds_decode_device in every case.  As with the other entry points, the
  * outputs of an enqueue-only call (summary == NULL) are final once cds_finish has returned.
- * Not streamed: relations of a single range, a `stream` that is being captured, a call with timing enabled. */
+ * Not streamed: relations of three ranges or fewer (the copy is too short to hide anything), a `stream` that is
+ * being captured, a call with timing enabled. */
 int cds_decode_host(cds_segment *seg, const void *h_heap_pages, uint64_t n_heap_pages,
                     const void *h_toast_pages, uint64_t n_toast_pages,
                     uint32_t ind_sample_bytes, uint32_t dep_sample_bytes,
