@@ -832,7 +832,7 @@ static int decode_host_streamed(cds_segment *s, const void *h_heap, uint64_t n_h
                                 uint32_t isb, uint32_t dsb, void *d_out_ind, uint64_t ind_cap, void *d_out_dep, uint64_t dep_cap,
                                 cudaStream_t st)
 {
-    const uint64_t rp = s->stream_range_pages;
+    const uint64_t rp = s->stream_range_pages & 0x7FFFFFFFu;
     const uint32_t n_ranges = (uint32_t)((n_toast_pages + rp - 1) / rp);
     int rc;
     if ((rc = reset_state(s, st))) return rc;
@@ -924,8 +924,9 @@ extern "C" int cds_decode_host(cds_segment *s, const void *h_heap, uint64_t n_he
     // stream and its events are the library's own).
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
-    const uint64_t rp = s->stream_range_pages;
-    if (rp && n_heap_pages && n_toast_pages > 3 * rp && (n_toast_pages + rp - 1) / rp <= kMaxStreamRanges && cap == cudaStreamCaptureStatusNone &&
+    const uint64_t rp = s->stream_range_pages & 0x7FFFFFFFu;
+    const uint64_t min_ranges = (s->stream_range_pages & 0x80000000u) ? 1 : 3;   // (tests: stream anything of more than one range)
+    if (rp && n_heap_pages && n_toast_pages > min_ranges * rp && (n_toast_pages + rp - 1) / rp <= kMaxStreamRanges && cap == cudaStreamCaptureStatusNone &&
         !(s->ev && s->ev_used < s->ev_cap)) {
         int rc = decode_host_streamed(s, h_heap, n_heap_pages, h_toast, n_toast_pages, isb, dsb, d_out_ind, ind_cap, d_out_dep, dep_cap, st);
         if (rc) return rc;

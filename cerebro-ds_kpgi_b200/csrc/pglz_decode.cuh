@@ -243,9 +243,20 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
             if (undone == 0u) break;
             if (!done && (need & undone) == 0u) {
                 const uint32_t sr = d0 - moff;
-                if (((d0 | sr | len) & 3u) == 0u) {                          // whole aligned words (float data: the usual case)
+                if (((d0 | sr | len) & 3u) == 0u) {                          // whole aligned words
                     for (uint32_t k = 0; k < len; k += 4u)
                         *reinterpret_cast<uint32_t *>(ring + ((d0 + k) & M_)) = *reinterpret_cast<const uint32_t *>(ring + ((sr + k) & M_));
+                } else if (moff >= len && len <= 8u) {
+                    // up to 8 bytes that do not overlap their source: three aligned words re-aligned by funnel shifts, then
+                    // straight-line predicated byte stores (no loop: the lanes of a warp sit in items of different lengths)
+                    const uint32_t sa = sr & ~3u, sh = (sr & 3u) * 8u;
+                    const uint32_t x0 = *reinterpret_cast<const uint32_t *>(ring + (sa & M_));
+                    const uint32_t x1 = *reinterpret_cast<const uint32_t *>(ring + ((sa + 4u) & M_));
+                    const uint32_t x2 = *reinterpret_cast<const uint32_t *>(ring + ((sa + 8u) & M_));
+                    const uint32_t lo = __funnelshift_r(x0, x1, sh), hi = __funnelshift_r(x1, x2, sh);
+#pragma unroll
+                    for (uint32_t k = 0; k < 8u; k++)
+                        if (k < len) ring[(d0 + k) & M_] = (uint8_t)((k < 4u ? lo : hi) >> (8u * (k & 3u)));
                 } else {
                     for (uint32_t k = 0; k < len; k++) ring[(d0 + k) & M_] = ring[(sr + k) & M_];
                 }
@@ -456,7 +467,27 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
             const uint32_t g = lane >> 3, k = lane & 7u, below = (1u << k) - 1u;
             uint32_t M = 0, my_p = 0, my_bit = 0, ng = 0, consumed = 0;
             bool conv = false;
-            for (int it = 0; it < 4 && !conv; it++) {
+            {
+                // First try, "no tag carries an extension byte" (always true of short matches): a group that starts at
+                // position p is 9 + popc(byte p) long whatever else is in it, so every lane knows where the group after
+                // "a group at my position" starts, and the four group starts are three hops through those values.
+                const uint32_t nx_lo = lane + 9u + __popc(byte), nx_hi = lane + 41u + __popc(byte1);
+                const uint32_t S1 = __shfl_sync(0xffffffffu, nx_lo, 0);                       // 9..17
+                const uint32_t S2 = __shfl_sync(0xffffffffu, nx_lo, S1);                      // 18..34
+                const uint32_t a3 = __shfl_sync(0xffffffffu, nx_lo, S2 & 31u), b3 = __shfl_sync(0xffffffffu, nx_hi, S2 & 31u);
+                const uint32_t S3 = S2 < 32u ? a3 : b3;                                       // 27..51
+                const uint32_t a4 = __shfl_sync(0xffffffffu, nx_lo, S3 & 31u), b4 = __shfl_sync(0xffffffffu, nx_hi, S3 & 31u);
+                ng = S3 <= 39u ? 4u : 3u;                                                     // whole groups inside the 64 bytes
+                consumed = ng == 4u ? (S3 < 32u ? a4 : b4) : S3;
+                const uint32_t myS = g == 0u ? 0u : g == 1u ? S1 : g == 2u ? S2 : S3;
+                const uint32_t myC = (__shfl_sync(0xffffffffu, W, myS & 31u) >> ((myS >> 5) * 8u)) & 0xFFu;
+                my_bit = (myC >> k) & 1u;
+                my_p = myS + 1u + k + __popc(myC & below);
+                const uint32_t ebit = ((my_p < 32u ? e_lo : e_hi) >> (my_p & 31u)) & 1u;
+                M = __ballot_sync(0xffffffffu, g < ng && my_bit && ebit);
+                conv = M == 0u;
+            }
+            for (int it = 1; it < 4 && !conv; it++) {
                 uint32_t S = 0, myS = 0, myC = 0;
                 ng = 0;
 #pragma unroll

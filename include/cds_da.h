@@ -161,7 +161,8 @@ int cds_decode_host(cds_segment *seg, const void *h_heap_pages, uint64_t n_heap_
                     void *d_out_ind, uint64_t ind_cap_bytes, void *d_out_dep, uint64_t dep_cap_bytes,
                     void *stream, cds_summary *summary);
 
-/* Pages per range of the streamed cds_decode_host (default 2048 = 64 MiB; 0 = copy everything, then decode). */
+/* Pages per range of the streamed cds_decode_host (default 2048 = 64 MiB; 0 = copy everything, then decode).
+ * range_pages | 0x80000000 streams every relation of more than one range (tests). */
 int cds_set_host_streaming(cds_segment *seg, uint32_t range_pages);
 /* cds_decode_host calls of this process that were streamed, and how many of those cds_finish had to decode again. */
 int cds_stream_counts(unsigned long long *streamed, unsigned long long *decoded_again);

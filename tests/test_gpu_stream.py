@@ -49,7 +49,7 @@ def both_ways(torch, heap, toast, range_pages, fmt=None, isb=0, dsb=0):
         if mode == "device":
             s = ds.decode_device(torch.from_numpy(heap).cuda(), torch.from_numpy(toast).cuda(), out_ind, out_dep, isb, dsb)
         else:
-            _lib.check(L.cds_set_host_streaming(ds._h, range_pages))
+            _lib.check(L.cds_set_host_streaming(ds._h, range_pages | 0x80000000))
             ph, pt = segment.PinnedBuffer(heap.size), segment.PinnedBuffer(toast.size)
             ph.array[:] = heap
             pt.array[:] = toast
@@ -76,8 +76,8 @@ def assert_same(s_a, ind_a, dep_a, s_b, ind_b, dep_b):
 @pytest.mark.parametrize("range_pages", [1, 3])
 def test_streamed_matches_classic_on_golden_segments(name, range_pages, torch_cuda):
     heap, toast, order, expected = load_golden_segment(name)
-    if toast.size // 32768 <= 3 * range_pages:
-        pytest.skip("relations of three ranges or fewer are not streamed")
+    if toast.size // 32768 <= range_pages:
+        pytest.skip("a single range is not streamed")
     r = both_ways(torch_cuda, heap, toast, range_pages)
     assert_same(*r[:6])
     streamed, redone = r[6]
@@ -138,7 +138,7 @@ def test_streamed_damaged_segments_report_what_the_classic_path_reports(torch_cu
     for i, name in enumerate(z["names"]):
         name = str(name)
         heap, toast = z["heap_%d" % i], z["toast_%d" % i]
-        if name in ("partial_page", "shape_mismatch") or toast.size // 32768 < 4:
+        if name in ("partial_page", "shape_mismatch") or toast.size // 32768 < 2:
             continue
         r = both_ways(torch_cuda, heap, toast, 1)
         assert r[0].status != 0, name
