@@ -216,3 +216,22 @@ def test_literal_only_control_bytes_are_checked(torch_cuda, coracle):
         assert status == want_code, name
         if want is not None:
             assert part.ind.cpu().numpy().tobytes() == want["out_ind"].tobytes(), name
+
+
+def test_helper_work_memory_is_kept_and_can_be_trimmed(torch_cuda):
+    """cds_pglz_decompress_batch keeps its work memory between calls (no cudaMalloc per call); cds_trim_work_memory
+    frees it and the next call simply allocates again."""
+    from cerebro_ds_kpgi_b200 import _lib, segment, synth
+    L = _lib.require_device()
+    rng = np.random.default_rng(2)
+    datums = [synth.pglz_varlena(rng.integers(0, 4, size=5000, dtype=np.uint8), "lz") for _ in range(20)]
+    want, codes = segment.pglz_decompress_batch(datums)
+    assert codes == [0] * 20
+    free0 = torch_cuda.cuda.mem_get_info()[0]
+    for _ in range(5):
+        got, codes = segment.pglz_decompress_batch(datums)
+        assert got == want
+    assert torch_cuda.cuda.mem_get_info()[0] == free0          # nothing was allocated or freed on the way
+    assert L.cds_trim_work_memory(0) == 0
+    got, codes = segment.pglz_decompress_batch(datums)
+    assert got == want and codes == [0] * 20
