@@ -377,75 +377,11 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
     return true;
 }
 
-// ---- two warps per datum --------------------------------------------------------------------------------------
-// When a launch has fewer (expensive) datums than half its warps, a datum gets a PAIR of warps: the even warp parses the
-// stream — control groups, item layout, lengths, offsets, output positions and every check that needs no output byte —
-// and pushes one record per item into a queue; the odd warp pops records, expands them in its ring and flushes.
-// Parsing depends on the source only, so the parser runs ahead, and the expander no longer waits for window fetches,
-// group walks and scans between its copies: one warp alone cannot hide its own latencies (Criteo: 7 datums per SM).
-// The queue lives in the shared memory that is the even warp's ring in the one-warp mode.
-constexpr uint32_t kQCap = 496;                               // records; 496 * 16 + control words <= kRing
-enum : uint32_t { kRecLiteral = 0, kRecMatch = 1, kRecSource = 2, kRecBegin = 3, kRecEnd = 4, kRecQuit = 5 };
-struct PairQueue {
-    uint4 rec[kQCap];                                         // {output position, len | offset << 9 | kind << 21, literal byte / source offset / job slot / ok, -}
-    uint32_t tail, head, abort_, pad_;                        // tail: records pushed; head: records the expander is done with
-};
-static_assert(sizeof(PairQueue) <= kRing, "the queue must fit one ring");
-constexpr uint32_t kSpinLimit = 1u << 22;                     // x ~100 ns: a stuck partner ends the datum instead of hanging the GPU
-
-struct Producer {
-    PairQueue *q;
-    uint32_t tail;                                            // my copy
-    uint32_t head_seen;
-};
-
-// Push `n` records (lane i < n holds record i).  Returns false when the partner has stopped answering.
-__device__ __forceinline__ bool q_push(Producer &P, uint32_t n, uint4 r, uint32_t lane)
-{
-    uint32_t spins = 0;
-    while (P.tail + n - P.head_seen > kQCap) {
-        P.head_seen = *reinterpret_cast<volatile uint32_t *>(&P.q->head);
-        if (P.tail + n - P.head_seen <= kQCap) break;
-        __nanosleep(64);
-        if (++spins > kSpinLimit || *reinterpret_cast<volatile uint32_t *>(&P.q->abort_)) return false;
-    }
-    if (lane < n) P.q->rec[(P.tail + lane) % kQCap] = r;
-    __syncwarp();
-    __threadfence_block();
-    P.tail += n;
-    if (lane == 0) *reinterpret_cast<volatile uint32_t *>(&P.q->tail) = P.tail;
-    return true;
-}
-
-// Parser side of pglz_expand_items: the same checks (ppr:213-215, 221-222), then one record per item instead of bytes.
-__device__ __forceinline__ bool pglz_produce_items(uint32_t nitems, bool is_match, uint32_t len, uint32_t moff, uint32_t litbyte,
-                                                   uint32_t &dp, uint32_t rawsize, Producer &P, uint32_t lane)
-{
-    const bool is_item = lane < nitems;
-    is_match = is_match && is_item;
-    const uint32_t olen = is_item ? (is_match ? len : 1u) : 0u;
-    uint32_t incl = olen;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= (uint32_t)d) incl += o;
-    }
-    const uint32_t my_o = incl - olen, total = __shfl_sync(0xffffffffu, incl, 31);
-    const bool bad = is_item && ((dp + my_o + olen > rawsize) || (is_match && (moff == 0u || moff > dp + my_o)));
-    if (__ballot_sync(0xffffffffu, bad)) return false;
-    const uint4 r = make_uint4(dp + my_o, len | (moff << 9) | ((is_match ? kRecMatch : kRecLiteral) << 21), litbyte, 0u);
-    if (!q_push(P, nitems, r, lane)) return false;
-    dp += total;
-    return true;
-}
-
 // Decode one datum with the calling warp.  Returns true when the stream is well-formed.
 // kOut: 0 = the decoded bytes, 1 = float32 -> bfloat16, 2 = uint8 -> float32 through `lut`.
-// kProduce: the calling warp is the PARSER of a pair: `ring` is unused, items and literal streaks go to the queue `P`
-// (kOut is 0 then; the expander knows the output format).
-template <int kOut, bool kProduce = false>
+template <int kOut>
 __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen, uint8_t *dst, uint32_t rawsize,
-                                 uint8_t *ring, const float *__restrict__ lut, uint32_t lut_channels, Producer *P = nullptr)
+                                 uint8_t *ring, const float *__restrict__ lut, uint32_t lut_channels)
 {
     const uint32_t lane = threadIdx.x & 31;
     // ring index = output position + shift, chosen so that ring vectors line up with aligned global stores
@@ -489,10 +425,7 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
                 uint32_t streak = (m == 0xffffffffu) ? 32u : (uint32_t)(__ffs((int)~m) - 1);
                 const uint32_t room = (rawsize - dp) >> 3;                   // whole groups that still fit
                 if (streak > room) streak = room;
-                if (kProduce) {
-                    // one record for the whole streak: 8 * streak literals that lie 9 bytes apart from stream offset sp on
-                    if (streak && !q_push(*P, 1u, make_uint4(dp, (8u * streak) | (kRecSource << 21), sp, 0u), lane)) { corrupt = true; break; }
-                } else if (lane < streak) {
+                if (lane < streak) {
                     const uint32_t lo = (uint32_t)(((((unsigned long long)w1) << 32) | w0) >> (sh + 8u));
                     const uint32_t hi = (uint32_t)(((((unsigned long long)w2) << 32) | w1) >> (sh + 8u));
                     const uint32_t o = dp + 8u * lane + shift;
@@ -510,7 +443,7 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
                 sp += 9u * streak;
                 dp += 8u * streak;
                 __syncwarp();
-                if (!kProduce && dp - flushed >= kFlushAt) {
+                if (dp - flushed >= kFlushAt) {
                     const uint32_t to = dp - ((dp + shift) & 15u);
                     flush(flushed, to);
                     flushed = to;
@@ -584,9 +517,8 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
                 uint32_t len = (b0 & 0x0Fu) + 3u;                            // ppr:205
                 const uint32_t moff = ((b0 & 0xF0u) << 4) | b1;              // ppr:206-208
                 if ((b0 & 0x0Fu) == 0x0Fu) len += b2;                        // ppr:210-212
-                bool too_big = false;
-                if (kProduce ? !pglz_produce_items(8u * ng, my_bit != 0u, len, moff, b0, dp, rawsize, *P, lane)
-                             : !pglz_expand_items(8u * ng, my_bit != 0u, len, moff, b0, dp, rawsize, ring, shift, lane, 2048u, &too_big)) {
+                bool too_big;
+                if (!pglz_expand_items(8u * ng, my_bit != 0u, len, moff, b0, dp, rawsize, ring, shift, lane, 2048u, &too_big)) {
                     corrupt = true;
                     break;
                 }
@@ -630,121 +562,25 @@ __device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen,
             const uint32_t moff = ((b0 & 0xF0u) << 4) | b1;                  // ppr:206-208
             if ((b0 & 0x0Fu) == 0x0Fu) len += b2;                            // ppr:210-212
             bool too_big;
-            if (kProduce ? !pglz_produce_items(nitems, ((ctrl >> lane) & 1u) != 0u, len, moff, b0, dp, rawsize, *P, lane)
-                         : !pglz_expand_items(nitems, ((ctrl >> lane) & 1u) != 0u, len, moff, b0, dp, rawsize, ring, shift, lane,
-                                              0xFFFFFFFFu, &too_big)) {
+            if (!pglz_expand_items(nitems, ((ctrl >> lane) & 1u) != 0u, len, moff, b0, dp, rawsize, ring, shift, lane,
+                                   0xFFFFFFFFu, &too_big)) {
                 corrupt = true;
                 break;
             }
             sp += pnext;
         }
-        if (!kProduce && dp - flushed >= kFlushAt) {
+        if (dp - flushed >= kFlushAt) {
             const uint32_t to = dp - ((dp + shift) & 15u);
             flush(flushed, to);
             flushed = to;
             __syncwarp();
         }
     }
-    if (!kProduce && !corrupt) {
+    if (!corrupt) {
         __syncwarp();
         flush(flushed, dp);
     }
     return !corrupt && dp == rawsize && sp == slen;                          // ppr:229-230
-}
-
-// Expander of a pair: pops the records of ONE datum (up to its end record) and turns them into bytes.  Returns the
-// parser's verdict && every record was consistent; *quit is set when the parser has no more datums.
-template <int kOut>
-__device__ bool pglz_consume_datum(PairQueue *q, uint32_t &head, const uint8_t *__restrict__ src, uint8_t *dst, uint32_t rawsize, uint8_t *ring,
-                                   const float *__restrict__ lut, uint32_t lut_channels)
-{
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t shift = kOut == 1 ? (uint32_t)((2u * reinterpret_cast<uintptr_t>(dst)) & 15u)
-                         : kOut == 2 ? (uint32_t)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3u)
-                                     : (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15u);
-    auto flush = [&](uint32_t from, uint32_t to) {
-        if (kOut == 1) pglz_flush_bf16(ring, dst, shift, from, to, lane);
-        else if (kOut == 2) pglz_flush_u8norm(ring, reinterpret_cast<float *>(dst), shift, from, to, lane, lut, lut_channels);
-        else pglz_flush(ring, dst, shift, from, to, lane);
-    };
-    constexpr uint32_t M = kRing - 1;
-    uint32_t dp = 0, flushed = 0;
-    bool ok = true;
-    for (;;) {
-        // records available
-        uint32_t tail = 0, spins = 0;
-        for (;;) {
-            if (lane == 0) tail = *reinterpret_cast<volatile uint32_t *>(&q->tail);
-            tail = __shfl_sync(0xffffffffu, tail, 0);
-            if (tail != head) break;
-            __nanosleep(64);
-            if (++spins > kSpinLimit) { if (lane == 0) *reinterpret_cast<volatile uint32_t *>(&q->abort_) = 1u; return false; }
-        }
-        __threadfence_block();
-        const uint32_t n = min(tail - head, 32u);
-        uint4 r = make_uint4(0u, 0u, 0u, 0u);
-        if (lane < n) r = q->rec[(head + lane) % kQCap];
-        const uint32_t kind = lane < n ? (r.y >> 21) & 7u : 7u;
-        const uint32_t special = __ballot_sync(0xffffffffu, lane < n && kind >= kRecSource);
-        uint32_t take;                                                       // records consumed in this round
-        if (special & 1u) {
-            // ---- a single record that is not an item
-            const uint32_t k0 = __shfl_sync(0xffffffffu, kind, 0), a0 = __shfl_sync(0xffffffffu, r.x, 0);
-            const uint32_t b0 = __shfl_sync(0xffffffffu, r.y, 0), c0 = __shfl_sync(0xffffffffu, r.z, 0);
-            take = 1;
-            if (k0 == kRecEnd) {
-                head += 1;
-                __syncwarp();
-                if (lane == 0) *reinterpret_cast<volatile uint32_t *>(&q->head) = head;
-                if (ok && c0) { __syncwarp(); flush(flushed, dp); }
-                return ok && c0 != 0u && dp == rawsize;
-            }
-            if (k0 == kRecSource && ok) {
-                // literal streak: (b0 & 0x1FF...) bytes = groups of 8 literals behind a control byte, from stream offset c0
-                const uint32_t nbytes = b0 & 0x1FFFFFu, groups = nbytes >> 3;
-                if (a0 != dp || dp + nbytes > rawsize) ok = false;
-                else {
-                    if (lane < groups) {
-                        const uint8_t *g = src + c0 + 9u * lane + 1u;
-                        const uint32_t o = dp + 8u * lane + shift;
-#pragma unroll
-                        for (int k = 0; k < 8; k++) ring[(o + k) & M] = __ldg(g + k);
-                    }
-                    dp += nbytes;
-                }
-            } else if (k0 != kRecSource) {
-                ok = false;                                                  // begin / quit inside a datum: cannot happen
-            }
-        } else {
-            // ---- items up to the first special record, as many as fit one expansion (<= 2184 bytes: eight longest matches)
-            const uint32_t n_items = special ? (uint32_t)__ffs((int)special) - 1u : n;
-            const bool is_item = lane < n_items;
-            const bool is_match = is_item && kind == kRecMatch;
-            const uint32_t len = r.y & 0x1FFu, moff = (r.y >> 9) & 0xFFFu;
-            const uint32_t olen = is_item ? (is_match ? len : 1u) : 0u;
-            uint32_t incl = olen;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= (uint32_t)d) incl += o;
-            }
-            take = __popc(__ballot_sync(0xffffffffu, is_item && incl <= 2184u));
-            if (take == 0u) take = 1u;
-            const uint32_t first_pos = __shfl_sync(0xffffffffu, r.x, 0);
-            bool too_big;
-            if (ok && (first_pos != dp || !pglz_expand_items(take, is_match, len, moff, r.z, dp, rawsize, ring, shift, lane, 0xFFFFFFFFu, &too_big)))
-                ok = false;
-        }
-        head += take;
-        __syncwarp();
-        if (lane == 0) *reinterpret_cast<volatile uint32_t *>(&q->head) = head;
-        if (ok && dp - flushed >= kFlushAt) {
-            const uint32_t to = dp - ((dp + shift) & 15u);
-            flush(flushed, to);
-            flushed = to;
-            __syncwarp();
-        }
-    }
 }
 
 // Jobs are taken through *ticket (zero at launch).  With `st_counts` the job array is the compacted
@@ -765,91 +601,25 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
     const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
     const uint32_t n_jobs = front + back;
     if (n_jobs == 0) return;
-    const uint32_t warp = threadIdx.x >> 5;
-    // Fewer expensive datums than half the warps of the launch: two warps per datum (see PairQueue).
-    const bool pair_mode = 2u * front <= gridDim.x * (uint32_t)kPglzWarps;
-    auto slot_of = [&](uint32_t t) { return t < front ? first + t : last_slot - (t - front); };
-    if (!pair_mode) {
-        for (;;) {
-            uint32_t t = 0;
-            if (lane == 0) t = atomicAdd(ticket, 1u);
-            t = __shfl_sync(0xffffffffu, t, 0);
-            if (t >= n_jobs) break;
-            const uint32_t j = slot_of(t);
-            const PglzJob job = jobs[j];
-            if (job.slen == kNone) continue;
-            const uint8_t *jsrc = reinterpret_cast<const uint8_t *>(job.src);
-            uint8_t *jdst = reinterpret_cast<uint8_t *>(job.dst);
-            const uint32_t jlen = job.slen & ~kFlagBits;
-            const bool ok = (job.slen & kJobToBf16) ? pglz_warp_decode<1>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels)
-                          : (job.slen & kJobU8Norm) ? pglz_warp_decode<2>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels)
-                                                    : pglz_warp_decode<0>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels);
-            if (lane == 0) {
-                if (status) status[j] = ok ? CDS_OK : CDS_ERR_PGLZ_CORRUPT;
-                if (!ok && st && job.err_key) report_key(st, job.err_key);
-            }
-            __syncwarp();
+    for (;;) {
+        uint32_t t = 0;
+        if (lane == 0) t = atomicAdd(ticket, 1u);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= n_jobs) break;
+        const uint32_t j = t < front ? first + t : last_slot - (t - front);
+        const PglzJob job = jobs[j];
+        if (job.slen == kNone) continue;
+        const uint8_t *jsrc = reinterpret_cast<const uint8_t *>(job.src);
+        uint8_t *jdst = reinterpret_cast<uint8_t *>(job.dst);
+        const uint32_t jlen = job.slen & ~kFlagBits;
+        const bool ok = (job.slen & kJobToBf16) ? pglz_warp_decode<1>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels)
+                      : (job.slen & kJobU8Norm) ? pglz_warp_decode<2>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels)
+                                                : pglz_warp_decode<0>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels);
+        if (lane == 0) {
+            if (status) status[j] = ok ? CDS_OK : CDS_ERR_PGLZ_CORRUPT;
+            if (!ok && st && job.err_key) report_key(st, job.err_key);
         }
-        return;
-    }
-    PairQueue *q = reinterpret_cast<PairQueue *>(smem_ring + (size_t)(warp & ~1u) * kRing);
-    if ((warp & 1u) == 0u && lane == 0) { q->tail = 0; q->head = 0; q->abort_ = 0; }
-    __syncthreads();
-    if ((warp & 1u) == 0u) {
-        // ---- parser
-        Producer P;
-        P.q = q; P.tail = 0; P.head_seen = 0;
-        for (;;) {
-            uint32_t t = 0;
-            if (lane == 0) t = atomicAdd(ticket, 1u);
-            t = __shfl_sync(0xffffffffu, t, 0);
-            if (t >= n_jobs) { q_push(P, 1u, make_uint4(0u, kRecQuit << 21, 0u, 0u), lane); break; }
-            const uint32_t j = slot_of(t);
-            const PglzJob job = jobs[j];
-            if (job.slen == kNone) continue;
-            if (!q_push(P, 1u, make_uint4(0u, kRecBegin << 21, j, 0u), lane)) break;
-            const bool ok = pglz_warp_decode<0, true>(reinterpret_cast<const uint8_t *>(job.src), job.slen & ~kFlagBits, nullptr, job.rawsize,
-                                                      nullptr, lut, lut_channels, &P);
-            if (!q_push(P, 1u, make_uint4(0u, kRecEnd << 21, ok ? 1u : 0u, 0u), lane)) break;
-        }
-    } else {
-        // ---- expander (its own 8 KB are the ring)
-        uint32_t head = 0;
-        for (;;) {
-            uint32_t tail = 0, spins = 0;
-            bool dead = false;
-            for (;;) {
-                if (lane == 0) tail = *reinterpret_cast<volatile uint32_t *>(&q->tail);
-                tail = __shfl_sync(0xffffffffu, tail, 0);
-                if (tail != head) break;
-                __nanosleep(64);
-                if (++spins > kSpinLimit) { dead = true; break; }
-            }
-            if (dead) { if (lane == 0) *reinterpret_cast<volatile uint32_t *>(&q->abort_) = 1u; break; }
-            __threadfence_block();
-            const uint4 r = q->rec[head % kQCap];
-            const uint32_t kind = (r.y >> 21) & 7u;
-            if (kind != kRecBegin) {                                         // quit (or a record out of place: stop both warps)
-                if (kind != kRecQuit && lane == 0) *reinterpret_cast<volatile uint32_t *>(&q->abort_) = 1u;
-                break;
-            }
-            head += 1;
-            __syncwarp();
-            if (lane == 0) *reinterpret_cast<volatile uint32_t *>(&q->head) = head;
-            const uint32_t j = r.z;
-            const PglzJob job = jobs[j];
-            const uint8_t *jsrc = reinterpret_cast<const uint8_t *>(job.src);
-            uint8_t *jdst = reinterpret_cast<uint8_t *>(job.dst);
-            const bool ok = (job.slen & kJobToBf16) ? pglz_consume_datum<1>(q, head, jsrc, jdst, job.rawsize, ring, lut, lut_channels)
-                          : (job.slen & kJobU8Norm) ? pglz_consume_datum<2>(q, head, jsrc, jdst, job.rawsize, ring, lut, lut_channels)
-                                                    : pglz_consume_datum<0>(q, head, jsrc, jdst, job.rawsize, ring, lut, lut_channels);
-            if (lane == 0) {
-                if (status) status[j] = ok ? CDS_OK : CDS_ERR_PGLZ_CORRUPT;
-                if (!ok && st && job.err_key) report_key(st, job.err_key);
-            }
-            __syncwarp();
-            if (*reinterpret_cast<volatile uint32_t *>(&q->abort_)) break;
-        }
+        __syncwarp();
     }
 }
 
