@@ -470,6 +470,12 @@ static inline uint32_t scan_grid(const cds_segment *s, uint64_t n, uint32_t item
 // A decode starts from zeros: state, scan tickets/status and the hash table, one memset.
 static int reset_state(cds_segment *s, cudaStream_t st)
 {
+    // A streamed cds_decode_host whose verdict was never collected (no cds_finish since): collect it now, so that a segment
+    // whose assumed plan did not hold is decoded again before its stage buffers and its state are reused.
+    if (s->stream_pending) {
+        int rc = cds_finish(s, (void *)st, nullptr);
+        if (rc >= 100) return rc;
+    }
     CU(cudaMemsetAsync(s->zero_region, 0, s->zero_bytes, st));
     s->have_rows = s->have_chunks = s->have_plan = s->have_ops = false;
     s->wide_launched = false;

@@ -162,3 +162,43 @@ def test_streamed_damaged_segments_report_what_the_classic_path_reports(torch_cu
         assert_same(*r[:6])
         n_bad += int(r[0].status != 0)
     assert n_bad >= 3
+
+
+def test_streamed_decode_without_finish_is_settled_by_the_next_call(torch_cuda):
+    """Two enqueue-only cds_decode_host calls back to back on one handle, the first on a segment whose TOAST order does not
+    bear the assumed plan out: the second call collects the first one's verdict (and decodes it again) before it reuses the
+    handle, so both outputs are right although cds_finish ran only once, at the end."""
+    from cerebro_ds_kpgi_b200 import _lib, segment
+    L = _lib.require_device()
+    heap_a, toast_a, _, _ = load_golden_segment("seg_many_shuffled")
+    heap_b, toast_b, _, _ = load_golden_segment("seg_criteo")
+    hp = max(heap_a.size, heap_b.size) // 32768
+    tp = max(toast_a.size, toast_b.size) // 32768
+    ds = segment.DeviceSegment(hp, tp, device=0, stage=True)
+    _lib.check(L.cds_set_host_streaming(ds._h, 1 | 0x80000000))
+    outs, want = [], []
+    for heap, toast in ((heap_a, toast_a), (heap_b, toast_b)):
+        heap, toast = np.ascontiguousarray(heap), np.ascontiguousarray(toast)
+        cap = 16 * (heap.size + toast.size) + 4096
+        oi = torch_cuda.full((cap,), 0x11, dtype=torch_cuda.uint8, device="cuda")
+        od = torch_cuda.full((cap,), 0x22, dtype=torch_cuda.uint8, device="cuda")
+        ri, rd = torch_cuda.full((cap,), 0x11, dtype=torch_cuda.uint8, device="cuda"), torch_cuda.full((cap,), 0x22, dtype=torch_cuda.uint8, device="cuda")
+        ref = segment.DeviceSegment(hp, tp, device=0)
+        s = ref.decode_device(torch_cuda.from_numpy(heap).cuda(), torch_cuda.from_numpy(toast).cuda(), ri, rd)
+        assert s.status == 0
+        ref.close()
+        want.append((ri.cpu().numpy(), rd.cpu().numpy()))
+        ph, pt = segment.PinnedBuffer(heap.size), segment.PinnedBuffer(toast.size)
+        ph.array[:] = heap
+        pt.array[:] = toast
+        outs.append((oi, od, ph, pt))
+    before = stream_counts(L)
+    for oi, od, ph, pt in outs:
+        ds.decode_host(ph.array, pt.array, oi, od, sync=False)
+    s = ds.finish()
+    after = stream_counts(L)
+    assert s.status == 0
+    assert after[0] - before[0] == 2 and after[1] - before[1] >= 1
+    for (oi, od, _, _), (ri, rd) in zip(outs, want):
+        assert oi.cpu().numpy().tobytes() == ri.tobytes() and od.cpu().numpy().tobytes() == rd.tobytes()
+    ds.close()
