@@ -171,7 +171,7 @@ def test_streamed_decode_without_finish_is_settled_by_the_next_call(torch_cuda):
     from cerebro_ds_kpgi_b200 import _lib, segment
     L = _lib.require_device()
     heap_a, toast_a, _, _ = load_golden_segment("seg_many_shuffled")
-    heap_b, toast_b, _, _ = load_golden_segment("seg_criteo")
+    heap_b, toast_b, _, _ = load_golden_segment("seg_imagenet_rows")
     hp = max(heap_a.size, heap_b.size) // 32768
     tp = max(toast_a.size, toast_b.size) // 32768
     ds = segment.DeviceSegment(hp, tp, device=0, stage=True)
