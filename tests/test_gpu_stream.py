@@ -202,3 +202,47 @@ def test_streamed_decode_without_finish_is_settled_by_the_next_call(torch_cuda):
     for (oi, od, _, _), (ri, rd) in zip(outs, want):
         assert oi.cpu().numpy().tobytes() == ri.tobytes() and od.cpu().numpy().tobytes() == rd.tobytes()
     ds.close()
+
+
+SEED_SHIFT = int(os.environ.get("CDS_FUZZ_SEED", "0"))
+
+
+def test_streamed_layout_fuzz(torch_cuda):
+    """Random segments (every storage form, sizes around the chunk edge, TOAST written in table order or scrambled,
+    one random damaged byte in some) decoded both ways with random range sizes: identical status, summary and bytes."""
+    from cerebro_ds_kpgi_b200 import synth
+    rng = np.random.default_rng(4711 + SEED_SHIFT)
+    sizes = [1, 2, 3, 2034, 2035, 2036, 4069, 4070, 4071, 6105]
+    n_redone = n_err = 0
+    for trial in range(14):
+        n_rows = int(rng.integers(2, 40))
+        ind, dep, st_i, st_d = [], [], [], []
+        for r in range(n_rows):
+            b = int(rng.integers(1, 4))
+            k = int(rng.choice(sizes)) if rng.random() < 0.5 else int(rng.integers(1, 30000))
+            kind = rng.integers(0, 3)
+            if kind == 0:
+                x = rng.standard_normal((b, k)).astype(np.float32)
+            elif kind == 1:
+                x = np.zeros((b, k), dtype=np.float32)
+                x[:, ::7] = 1.0
+            else:
+                x = np.resize(rng.standard_normal(int(rng.integers(1, 40))).astype(np.float32), (b, k))
+            ind.append(x)
+            dep.append(rng.integers(-2, 3, size=(b, int(rng.integers(1, 40)))).astype(np.int16))
+            st_i.append(str(rng.choice(["ext_raw", "ext_pglz", "ext_literal"])))
+            st_d.append(str(rng.choice(["ext_raw", "ext_pglz", "inline_pglz", "inline_literal", "ext_literal"])))
+        n_ext = n_rows + sum(1 for s in st_d if s.startswith("ext"))
+        perm = list(rng.permutation(n_ext)) if rng.random() < 0.3 else None
+        seg = synth.build_segment(ind, dep, ind_storage=st_i, dep_storage=st_d, toast_perm=perm,
+                                  first_valueid=int(rng.integers(16384, 2 ** 31)), effort=int(rng.integers(1, 20)))
+        toast = seg.toast.copy()
+        if rng.random() < 0.3:
+            toast[int(rng.integers(0, toast.size))] ^= int(rng.integers(1, 256))
+        if toast.size // 32768 < 2:
+            continue
+        r = both_ways(torch_cuda, seg.heap, toast, int(rng.integers(1, 4)))
+        assert_same(*r[:6])
+        n_redone += r[6][1]
+        n_err += int(r[0].status != 0)
+    assert n_redone >= 1

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Run the randomised differential GPU tests (tests/test_gpu_fuzz.py, parts of tests/test_gpu_wide_pglz.py) over a range of
+"""Run the randomised differential GPU tests (tests/test_gpu_fuzz.py, parts of tests/test_gpu_wide_pglz.py and tests/test_gpu_stream.py) over a range of
 seed shifts in one process:   python tools/soak_fuzz.py FIRST LAST     (prints the shifts that failed; exit code 1 if any)."""
 import os
 import sys
@@ -19,6 +19,7 @@ def main():
     build.build_oracle()
     import test_gpu_fuzz as f
     import test_gpu_wide_pglz as w
+    import test_gpu_stream as sm
     co = da_oracle.COracle()
     L = _lib.require_device()
 
@@ -30,10 +31,11 @@ def main():
              ("layout_wide", lambda: f.test_segment_layout_fuzz(torch, co, True)),
              ("corruption", lambda: f.test_corruption_fuzz_never_disagrees_silently(torch, co)),
              ("wide_streams", lambda: w.test_wide_matches_oracle_on_structured_streams(torch, co, set_thr)),
-             ("wide_corrupt", lambda: w.test_wide_corrupt_streams_agree_with_oracle(torch, co, set_thr))]
+             ("wide_corrupt", lambda: w.test_wide_corrupt_streams_agree_with_oracle(torch, co, set_thr)),
+             ("streamed", lambda: sm.test_streamed_layout_fuzz(torch))]
     failed = []
     for k in range(first, last + 1):
-        f.SEED_SHIFT = w.SEED_SHIFT = k
+        f.SEED_SHIFT = w.SEED_SHIFT = sm.SEED_SHIFT = k
         for name, fn in cases:
             try:
                 fn()
