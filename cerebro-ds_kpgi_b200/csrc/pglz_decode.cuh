@@ -601,10 +601,15 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
     const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
     const uint32_t n_jobs = front + back;
     if (n_jobs == 0) return;
-    for (;;) {
-        uint32_t t = 0;
-        if (lane == 0) t = atomicAdd(ticket, 1u);
-        t = __shfl_sync(0xffffffffu, t, 0);
+    // The first job of every warp is fixed — consecutive jobs go to different CTAs, so that a launch with fewer jobs than
+    // warps spreads over all SMs instead of filling the CTAs that happen to start first; the rest are taken by ticket.
+    const uint32_t total_warps = gridDim.x * (uint32_t)kPglzWarps;
+    uint32_t t = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    for (bool first_job = true;; first_job = false) {
+        if (!first_job) {
+            if (lane == 0) t = total_warps + atomicAdd(ticket, 1u);
+            t = __shfl_sync(0xffffffffu, t, 0);
+        }
         if (t >= n_jobs) break;
         const uint32_t j = t < front ? first + t : last_slot - (t - front);
         const PglzJob job = jobs[j];
