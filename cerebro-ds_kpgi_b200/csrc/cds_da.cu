@@ -82,8 +82,6 @@ static int current_sm_count()
 }
 
 constexpr uint32_t kStreamDecoders = 4;
-constexpr uint32_t kStreamTailRanges = 3;            // streamed decode: the last ranges' values go through the wide decoder ...
-constexpr uint32_t kStreamTailWideBytes = 65536;     // ... when they decode to at least this many bytes
 constexpr uint32_t kTimedStages = 4;   // 0 gather, 1 pglz stage (classify + wide + warp decoder), 2 / 3 the wide block passes
 
 struct cds_segment {
@@ -806,7 +804,7 @@ extern "C" int cds_decode_device(cds_segment *s, const void *d_heap, uint64_t n_
 // The classification and the wide decoder share one work area, so they stay on the main stream; the warp decoder of the
 // batch runs on a side stream, beside the ranges that follow (a 150 KB value keeps its warp busy for milliseconds: batches
 // must overlap each other, or the decode falls behind the copy).
-static int launch_pglz_batch(cds_segment *s, uint32_t j, bool may_be_wide, bool tail, cudaStream_t st)
+static int launch_pglz_batch(cds_segment *s, uint32_t j, bool may_be_wide, cudaStream_t st)
 {
     const float *lut = s->ind_format == 2 ? s->d_lut : nullptr;
     const uint32_t *d_first = s->sargs.range_first + j;
@@ -814,15 +812,11 @@ static int launch_pglz_batch(cds_segment *s, uint32_t j, bool may_be_wide, bool 
         WideArea wa = s->wide;
         wa.threshold = g_wide_threshold;
         wa.force = (s->wide_mode == 1 || g_wide_force) ? 1u : 0u;
-        // The last ranges of a relation: nothing is left to hide their decode behind, and a value on one warp takes
-        // milliseconds (150 KB: ~2.5 ms).  Their values of 64 KiB and more go through the intra-value parallel decoder,
-        // which turns a few hundred of them into bytes in well under a millisecond.
-        if (tail && s->wide_mode == 2) { wa.threshold = kStreamTailWideBytes < wa.threshold ? kStreamTailWideBytes : wa.threshold; wa.force = 1u; }
         wa.st = s->state;
         wa.lut = lut;
         wa.lut_channels = s->lut_channels ? s->lut_channels : 1u;
         s->last_wa = wa;
-        const bool pipeline = s->wide_mode != 2 || s->wide_hint || tail;
+        const bool pipeline = s->wide_mode != 2 || s->wide_hint;
         int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st, pipeline, nullptr, cudaEventRecordDefault, d_first);
         if (rc) return rc;
         s->wide_launched = true;
@@ -882,7 +876,7 @@ static int decode_host_streamed(cds_segment *s, const void *h_heap, uint64_t n_h
     k_stream_mark<<<1, 1, 0, st>>>(s->state, S.range_first + 1);
     CU(cudaGetLastError());
     LAUNCHED(9);
-    if ((rc = launch_pglz_batch(s, 0, false, false, st))) return rc;
+    if ((rc = launch_pglz_batch(s, 0, false, st))) return rc;
     // ---- TOAST, range by range
     for (uint32_t k = 0; k < n_ranges; k++) {
         const uint64_t p0 = k * rp, np = (p0 + rp <= n_toast_pages ? rp : n_toast_pages - p0);
@@ -900,7 +894,7 @@ static int decode_host_streamed(cds_segment *s, const void *h_heap, uint64_t n_h
                                                                        s->ind_format == 2 ? s->d_lut : nullptr, s->lut_channels, s->dir_ref, s->vfirst);
         CU(cudaGetLastError());
         LAUNCHED(6);
-        if ((rc = launch_pglz_batch(s, k + 1, true, k + kStreamTailRanges >= n_ranges, st))) return rc;
+        if ((rc = launch_pglz_batch(s, k + 1, true, st))) return rc;
     }
     // the decoders of all batches join `st` here: what follows rebuilds the job list they read, and whatever the caller
     // enqueues on `st` next must see the complete decode
