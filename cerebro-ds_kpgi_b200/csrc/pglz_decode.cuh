@@ -601,10 +601,12 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
     const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
     const uint32_t n_jobs = front + back;
     if (n_jobs == 0) return;
-    // The first job of every warp is fixed — consecutive jobs go to different CTAs, so that a launch with fewer jobs than
-    // warps spreads over all SMs instead of filling the CTAs that happen to start first; the rest are taken by ticket.
+    // The first job of every warp is fixed, the rest are taken by ticket.  Consecutive jobs go to different CTAs, so that a
+    // launch with fewer jobs than warps spreads over all SMs instead of filling the CTAs that happen to start first
+    // (Criteo: 1 024 values on 4 144 warps).  The batches of a streamed decode do the opposite: they fill CTA after CTA,
+    // because a CTA keeps its 112 KB of shared memory until its last warp is done and the next batch needs room on the SMs.
     const uint32_t total_warps = gridDim.x * (uint32_t)kPglzWarps;
-    uint32_t t = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    uint32_t t = d_first ? blockIdx.x * (uint32_t)kPglzWarps + (threadIdx.x >> 5) : (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
     for (bool first_job = true;; first_job = false) {
         if (!first_job) {
             if (lane == 0) t = total_warps + atomicAdd(ticket, 1u);
