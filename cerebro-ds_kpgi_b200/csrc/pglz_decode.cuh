@@ -605,11 +605,15 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
     // launch with fewer jobs than warps spreads over all SMs instead of filling the CTAs that happen to start first
     // (Criteo: 1 024 values on 4 144 warps).  The batches of a streamed decode do the opposite: they fill CTA after CTA,
     // because a CTA keeps its 112 KB of shared memory until its last warp is done and the next batch needs room on the SMs.
+    // With at least half as many expensive jobs as warps everything goes by ticket, as the warps come up: measured 6 % faster
+    // on configs[2] (4 008 values on 4 144 warps) than the fixed spread, which in turn is 10 % faster on Criteo.
     const uint32_t total_warps = gridDim.x * (uint32_t)kPglzWarps;
+    const bool fixed_first = d_first != nullptr || 2u * front < total_warps;
+    const uint32_t ticket_base = fixed_first ? total_warps : 0u;
     uint32_t t = d_first ? blockIdx.x * (uint32_t)kPglzWarps + (threadIdx.x >> 5) : (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
-    for (bool first_job = true;; first_job = false) {
+    for (bool first_job = fixed_first;; first_job = false) {
         if (!first_job) {
-            if (lane == 0) t = total_warps + atomicAdd(ticket, 1u);
+            if (lane == 0) t = ticket_base + atomicAdd(ticket, 1u);
             t = __shfl_sync(0xffffffffu, t, 0);
         }
         if (t >= n_jobs) break;
