@@ -378,9 +378,10 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
 }
 
 // Decode one datum with the calling warp.  Returns true when the stream is well-formed.
-// kOut: 0 = the decoded bytes, 1 = float32 -> bfloat16, 2 = uint8 -> float32 through `lut`.
-template <int kOut>
-__device__ bool pglz_warp_decode(const uint8_t *__restrict__ src, uint32_t slen, uint8_t *dst, uint32_t rawsize,
+// kOut: 0 = the decoded bytes, 1 = float32 -> bfloat16, 2 = uint8 -> float32 through `lut`.  (A run-time value: only the
+// flush differs between the formats, and three copies of this function are 17 000 SASS instructions — more than the
+// instruction cache holds.)
+__device__ bool pglz_warp_decode(const uint32_t kOut, const uint8_t *__restrict__ src, uint32_t slen, uint8_t *dst, uint32_t rawsize,
                                  uint8_t *ring, const float *__restrict__ lut, uint32_t lut_channels)
 {
     const uint32_t lane = threadIdx.x & 31;
@@ -601,21 +602,19 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
     const uint32_t last_slot = st_counts ? 2u * st_counts->n_rows - 1u : 0u;
     const uint32_t n_jobs = front + back;
     if (n_jobs == 0) return;
-    // The first job of every warp is fixed, the rest are taken by ticket.  Consecutive jobs go to different CTAs, so that a
-    // launch with fewer jobs than warps spreads over all SMs instead of filling the CTAs that happen to start first
-    // (Criteo: 1 024 values on 4 144 warps).  The batches of a streamed decode do the opposite: they fill CTA after CTA,
+    // Fewer jobs than warps (Criteo: 2 048 on 4 144): the warps that come up first would take them all and fill a few SMs
+    // with 14 busy warps each while the other SMs idle.  Only as many warps per CTA as the jobs need stay, so the jobs
+    // spread over all CTAs; nothing has to wait for the warps that leave.  (A batch of a streamed decode keeps them: it
+    // should fill CTA after CTA, because a CTA holds its 112 KB of shared memory until its last warp is done.)
+    if (!d_first && (threadIdx.x >> 5) * gridDim.x >= n_jobs) return;
+    // Jobs are taken by ticket.  When a launch has few expensive jobs (fewer than half its warps: Criteo, 1 024 values on
+    // 4 144 warps) the warps that come up first would take them all and fill a few SMs, so only the first `quota` warps of
+    // every CTA take part in the first round; a batch of a streamed decode does the opposite and fills CTA after CTA,
     // because a CTA keeps its 112 KB of shared memory until its last warp is done and the next batch needs room on the SMs.
-    // With at least half as many expensive jobs as warps everything goes by ticket, as the warps come up: measured 6 % faster
-    // on configs[2] (4 008 values on 4 144 warps) than the fixed spread, which in turn is 10 % faster on Criteo.
-    const uint32_t total_warps = gridDim.x * (uint32_t)kPglzWarps;
-    const bool fixed_first = d_first != nullptr || 2u * front < total_warps;
-    const uint32_t ticket_base = fixed_first ? total_warps : 0u;
-    uint32_t t = d_first ? blockIdx.x * (uint32_t)kPglzWarps + (threadIdx.x >> 5) : (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
-    for (bool first_job = fixed_first;; first_job = false) {
-        if (!first_job) {
-            if (lane == 0) t = ticket_base + atomicAdd(ticket, 1u);
-            t = __shfl_sync(0xffffffffu, t, 0);
-        }
+    for (;;) {
+        uint32_t t = 0;
+        if (lane == 0) t = atomicAdd(ticket, 1u);
+        t = __shfl_sync(0xffffffffu, t, 0);
         if (t >= n_jobs) break;
         const uint32_t j = t < front ? first + t : last_slot - (t - front);
         const PglzJob job = jobs[j];
@@ -623,9 +622,8 @@ k_pglz_decode(const PglzJob *__restrict__ jobs, const DevState *st_counts, uint3
         const uint8_t *jsrc = reinterpret_cast<const uint8_t *>(job.src);
         uint8_t *jdst = reinterpret_cast<uint8_t *>(job.dst);
         const uint32_t jlen = job.slen & ~kFlagBits;
-        const bool ok = (job.slen & kJobToBf16) ? pglz_warp_decode<1>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels)
-                      : (job.slen & kJobU8Norm) ? pglz_warp_decode<2>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels)
-                                                : pglz_warp_decode<0>(jsrc, jlen, jdst, job.rawsize, ring, lut, lut_channels);
+        const bool ok = pglz_warp_decode((job.slen & kJobToBf16) ? 1u : (job.slen & kJobU8Norm) ? 2u : 0u, jsrc, jlen, jdst, job.rawsize, ring, lut,
+                                         lut_channels);
         if (lane == 0) {
             if (status) status[j] = ok ? CDS_OK : CDS_ERR_PGLZ_CORRUPT;
             if (!ok && st && job.err_key) report_key(st, job.err_key);
