@@ -219,7 +219,7 @@ static cudaError_t wide_prepare()
     return e;
 }
 
-// The 14 kernels behind the classification, on stream `st`.
+// The 13 kernels behind the classification, on stream `st`.
 #define CDS_WIDE_PIPELINE(wa, sms, st, BEFORE_B1, AFTER_B1, BEFORE_B3, AFTER_B3)            \
     do {                                                                                    \
         k_wide_maps<<<(sms) * 8u, 256, 0, st>>>(wa);                                        \
@@ -231,7 +231,6 @@ static cudaError_t wide_prepare()
         k_wide_check<<<8, 256, 0, st>>>(wa);                                                \
         k_wide_blkmap<<<(sms) * 2u, 256, 0, st>>>(wa);                                      \
         BEFORE_B1;                                                                          \
-        if (kWideLazyTail) k_wide_tailmap<<<(sms) * 2u, 1024, 0, st>>>(wa);                 \
         k_wide_blocks<1><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
         AFTER_B1;                                                                           \
         k_wide_tails<0><<<(sms), 1024, 0, st>>>(wa);                                        \
@@ -254,7 +253,7 @@ static int wide_pipeline(WideArea wa, int num_sms, cudaStream_t st, cudaEvent_t 
                       if (ev4) cudaEventRecordWithFlags(ev4[0], st, ev_flags), if (ev4) cudaEventRecordWithFlags(ev4[1], st, ev_flags),
                       if (ev4) cudaEventRecordWithFlags(ev4[2], st, ev_flags), if (ev4) cudaEventRecordWithFlags(ev4[3], st, ev_flags));
     CU(cudaGetLastError());
-    LAUNCHED(14);
+    LAUNCHED(13);
     return CDS_OK;
 }
 

@@ -80,9 +80,7 @@ struct WideState {       // zero when a decode starts
     uint32_t n_jobs, n_segs, n_blks;
     uint32_t t_maps, t_l1, t_l3, t_scan;
     uint32_t n_taken;    // values this decoder accepted (the rest stay with the warp decoder)
-    uint32_t t_lazy;     // ticket of k_wide_tailmap
-    uint32_t n_full;     // blocks whose tail map needed the full forest (statistics)
-    uint32_t pad[6];
+    uint32_t pad[8];
 };
 
 struct WideArea {
@@ -99,7 +97,6 @@ struct WideArea {
     uint32_t *sub_entry;     // per flat sub-segment: (output position of its first group relative to the segment's) << 5 | its offset
                              // (31: no group starts here)
     uint32_t *blk_sub0;      // per flat block: local sub-segment holding the group that produces its first byte
-    uint8_t *blk_full;       // per flat block: k_wide_tailmap gave up (chains too long), k_wide_blocks<1> builds the tail map
     uint32_t cap_jobs, cap_segs, cap_blks;
     uint32_t zero_bytes;
     uint32_t threshold;      // values with rawsize >= threshold are candidates for this path
@@ -117,8 +114,7 @@ __host__ __device__ inline size_t wide_area_bytes(uint32_t cap_jobs, uint32_t ca
     const size_t tiles = wide_scan_tiles(cap_segs), nss = (size_t)cap_segs / kWideSuper + 1;
     return wide_align(256 + 4 * tiles + 4 * ((size_t)cap_blks + 1)) + wide_align(16 * tiles) + wide_align(sizeof(WideJob) * (size_t)cap_jobs) +
            wide_align((size_t)cap_segs) + wide_align(4 * (size_t)cap_segs) + wide_align(8 * ((size_t)cap_segs + 1)) +
-           wide_align(32 * nss) + wide_align(nss) + wide_align(4 * (size_t)cap_segs * kWideSubs) + wide_align(4 * ((size_t)cap_blks + 1)) +
-           wide_align((size_t)cap_blks + 1);
+           wide_align(32 * nss) + wide_align(nss) + wide_align(4 * (size_t)cap_segs * kWideSubs) + wide_align(4 * ((size_t)cap_blks + 1));
 }
 
 // Carve the work area out of one 256-byte aligned allocation (host side).
@@ -142,8 +138,7 @@ inline WideArea wide_area_carve(uint8_t *base, uint32_t cap_jobs, uint32_t cap_s
     wa.supermap = p; p += wide_align(32 * nss);
     wa.sseg_e = p; p += wide_align(nss);
     wa.sub_entry = reinterpret_cast<uint32_t *>(p); p += wide_align(4 * (size_t)cap_segs * kWideSubs);
-    wa.blk_sub0 = reinterpret_cast<uint32_t *>(p); p += wide_align(4 * ((size_t)cap_blks + 1));
-    wa.blk_full = p;
+    wa.blk_sub0 = reinterpret_cast<uint32_t *>(p);
     wa.cap_jobs = cap_jobs; wa.cap_segs = cap_segs; wa.cap_blks = cap_blks;
     wa.threshold = 0; wa.force = 0; wa.status = nullptr; wa.st = nullptr; wa.lut = nullptr; wa.lut_channels = 1;
     return wa;
@@ -658,132 +653,6 @@ k_wide_blkmap(WideArea wa)
 
 // ---- B: blocks -----------------------------------------------------------------------------------------
 
-// Tail map of a block WITHOUT building the block: for each of the block's last 4095 bytes follow its chain of copies
-// item by item — find the item that produces the byte (binary search over the block's sub-segment records, then a
-// walk over at most 32 bytes of source), step to the byte it copies, repeat — until the chain ends in a literal
-// (the byte's value is known) or leaves the block (an index into the previous block's tail).  Image-like data needs
-// 3-4 hops per byte, which is an order of magnitude less work than the forest of the whole block that pass 1 used to
-// build just to read these 4095 roots.  A block with a chain longer than kWideLazyHops (long offset-1 runs chained
-// through each other: sparse data) is handed to k_wide_blocks<1> instead (blk_full).
-constexpr uint32_t kWideMaxSubs = 2304;            // sub-segments one block can span: 57344 * 9/8 / 32 = 2016, + slack
-constexpr uint32_t kWideLazyHops = 48;
-constexpr bool kWideLazyTail = false;              // measured on packed ImageNet buffers: 31.9 ms against 8 ms for k_wide_blocks<1> (chains of
-                                                   // always-matched bytes run 35-40 hops and a warp waits for its longest one): kept for reference
-
-__global__ void __launch_bounds__(1024)
-k_wide_tailmap(WideArea wa)
-{
-    __shared__ int32_t spos[kWideMaxSubs];          // output position, relative to the block start, of the first group that starts in
-                                                    // sub-segment sub0 + i (0x7FFFFFFF: none starts there)
-    __shared__ uint8_t soff[kWideMaxSubs];
-    __shared__ uint32_t sh_b, sh_j, sh_full, sh_bad;
-    const uint32_t n_jobs = wa.state->n_jobs, n_blks = wa.state->n_blks, tid = threadIdx.x;
-    if (n_jobs == 0) return;
-    for (;;) {
-        __syncthreads();
-        if (tid == 0) {
-            sh_b = atomicAdd(&wa.state->t_lazy, 1u);
-            sh_full = 0; sh_bad = 0;
-            if (sh_b < n_blks) sh_j = wide_find_blk(wa, n_jobs, sh_b);
-        }
-        __syncthreads();
-        const uint32_t b = sh_b;
-        if (b >= n_blks) break;
-        const uint32_t jn = sh_j;
-        const WideJob wj = wa.jobs[jn];
-        const uint32_t k = b - wj.blk0;
-        if (wj.state != 0u || k >= wj.nblk || k + 1u == wj.nblk) continue;   // nobody needs the last block's tail
-        const uint32_t o0 = k * kWideBlock;                                  // (a block that hands a tail on is a full one)
-        const uint8_t *__restrict__ src = reinterpret_cast<const uint8_t *>(wj.src);
-        const uint32_t slen = wj.slen;
-        const uint32_t sub0 = wa.blk_sub0[b], sub1 = wa.blk_sub0[b + 1], nsub = sub1 - sub0 + 1u;
-        if (sub1 < sub0 || nsub > kWideMaxSubs) {
-            if (tid == 0) { wa.blk_full[b] = 1; atomicAdd(&wa.state->n_full, 1u); }
-            continue;
-        }
-        const uint32_t *fine = wa.sub_entry + (size_t)wj.seg0 * kWideSubs;
-        const unsigned long long value_base = wa.seg_base[wj.seg0];
-        for (uint32_t i = tid; i < nsub; i += blockDim.x) {
-            const uint32_t sb = sub0 + i, ent = fine[sb];
-            if ((ent & 31u) == 31u) { spos[i] = 0x7FFFFFFF; soff[i] = 31; continue; }
-            const long long pos = (long long)(wa.seg_base[wj.seg0 + sb / kWideSubs] - value_base) + (long long)(ent >> 5) - (long long)o0;
-            spos[i] = pos > 0x7FFFFFF0ll ? 0x7FFFFFF0 : (int32_t)pos;          // (only the first record can lie before the block: small negative)
-            soff[i] = (uint8_t)(ent & 31u);
-        }
-        __syncthreads();
-        uint16_t *map = reinterpret_cast<uint16_t *>((reinterpret_cast<uintptr_t>(reinterpret_cast<uint8_t *>(wj.dst) + wide_scale(wj.fmt, o0)) + 1u) & ~(uintptr_t)1u);
-        bool full = false, bad = false;
-#pragma unroll 1
-        for (uint32_t jj = 0; jj < 4; jj++) {
-            const uint32_t ti = tid + 1024u * jj;
-            if (ti >= kWideWin || full || bad) continue;
-            int32_t x = (int32_t)(kWideBlock - kWideWin + ti);               // position inside the block
-            uint32_t result = 0;
-            for (uint32_t hop = 0;; hop++) {
-                if (hop > kWideLazyHops) { full = true; break; }
-                // last sub-segment whose first group starts at or before x (record 0 does: it produces the block's first byte)
-                uint32_t lo = 0, hi = nsub;
-                while (hi - lo > 1u) {
-                    const uint32_t mid = (lo + hi) >> 1;
-                    if (spos[mid] <= x) lo = mid; else hi = mid;
-                }
-                uint32_t a = (sub0 + lo) * kWideSub + soff[lo];
-                int32_t o = spos[lo];
-                if (soff[lo] == 31u || o > x) { bad = true; break; }
-                int32_t nx = 0;
-                bool found = false, literal = false;
-                for (uint32_t guard = 0; guard < 64u && !found && a < slen; guard++) {       // groups (a record covers 32 source bytes)
-                    const uint32_t ctrl = __ldg(src + a);
-                    uint32_t q = a + 1u;
-#pragma unroll 1
-                    for (uint32_t it = 0; it < 8u && q < slen; it++) {
-                        if ((ctrl >> it) & 1u) {
-                            const uint32_t b0 = __ldg(src + q), b1 = q + 1u < slen ? __ldg(src + q + 1u) : 0u;
-                            const bool ext = (b0 & 0x0Fu) == 0x0Fu;
-                            uint32_t len = (b0 & 0x0Fu) + 3u;                         // ppr:205
-                            const uint32_t off = ((b0 & 0xF0u) << 4) | b1;            // ppr:206-208
-                            if (ext) len += q + 2u < slen ? __ldg(src + q + 2u) : 0u;  // ppr:210-212
-                            q += ext ? 3u : 2u;
-                            if (x < o + (int32_t)len) {
-                                if (off == 0u) { bad = true; }
-                                else {
-                                    const uint32_t kk = (uint32_t)(x - o);
-                                    nx = off > kk ? x - (int32_t)off : o - (int32_t)off + (int32_t)(kk % off);   // ppr:216-219
-                                }
-                                found = true;
-                                break;
-                            }
-                            o += (int32_t)len;
-                        } else {
-                            if (x == o) { result = 0x8000u | __ldg(src + q); found = true; literal = true; break; }
-                            o += 1;
-                            q += 1u;
-                        }
-                    }
-                    a = q;
-                }
-                if (!found) bad = true;
-                if (bad || literal) break;
-                if (nx < 0) {                                                // the chain leaves the block: at most 4095 bytes back
-                    if ((long long)o0 + nx < 0) bad = true;                  // before the start of the output
-                    else result = (uint32_t)((int32_t)kWideWin + nx);
-                    break;
-                }
-                x = nx;
-            }
-            if (!full && !bad) map[ti] = (uint16_t)result;
-        }
-        if (full) sh_full = 1u;
-        if (bad) sh_bad = 1u;
-        __syncthreads();
-        if (tid == 0) {
-            if (sh_bad) wide_fail(wa, jn);
-            wa.blk_full[b] = sh_full ? 1 : 0;
-            if (sh_full) atomicAdd(&wa.state->n_full, 1u);
-        }
-    }
-}
-
 __device__ __forceinline__ bool wide_is_head(const uint32_t *heads, uint32_t e) { return (heads[e >> 5] >> (e & 31u)) & 1u; }
 
 // Nearest item start at or below e (there is one within 273 entries of any emitted byte).
@@ -825,7 +694,7 @@ k_wide_blocks(WideArea wa)
             if (kMode == 3 && tid == 0) *reinterpret_cast<volatile uint32_t *>(&wa.blk_flag[b]) = 1u;
             continue;
         }
-        if (kMode == 1 && (k + 1u == wj.nblk || (kWideLazyTail && !wa.blk_full[b]))) continue;  // nobody needs the last block's tail
+        if (kMode == 1 && k + 1u == wj.nblk) continue;                       // nobody needs the last block's tail
         const uint32_t o0 = k * kWideBlock, o1 = min(o0 + kWideBlock, wj.rawsize), n_out = o1 - o0;
         const uint8_t *src = reinterpret_cast<const uint8_t *>(wj.src);
         uint8_t *dst = reinterpret_cast<uint8_t *>(wj.dst);
