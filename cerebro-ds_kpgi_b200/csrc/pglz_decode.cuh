@@ -264,39 +264,9 @@ __device__ __forceinline__ bool pglz_expand_items(uint32_t nitems, bool is_match
             }
             __syncwarp();
         }
-    } else if (total <= 128u) {
-        // ---- short items with a long one among them: one lane per output byte, 32 bytes per step
-        const uint32_t pack = moff | (len << 12) | ((is_match ? 1u : 0u) << 21);
-        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
-            const uint32_t c0 = __popc(__ballot_sync(0xffffffffu, is_item && my_o <= t0));
-            const uint32_t starts = __reduce_or_sync(0xffffffffu, (is_item && my_o > t0 && my_o < t0 + 32u) ? (1u << (my_o - t0)) : 0u);
-            const uint32_t k = (c0 - 1u + __popc(starts & ((2u << lane) - 1u))) & 31u;
-            const uint32_t kp = __shfl_sync(0xffffffffu, pack, k);
-            const uint32_t ko = __shfl_sync(0xffffffffu, my_o, k);
-            const uint32_t lit = __shfl_sync(0xffffffffu, litbyte, k);
-            const uint32_t t = t0 + lane;
-            const bool live = t < total;
-            bool resolved = true;
-            uint32_t val = lit, srcl = 0;
-            if (live && ((kp >> 21) & 1u)) {
-                const uint32_t kmoff = kp & 0xFFFu, klen = (kp >> 12) & 0x1FFu;
-                uint32_t j = t - ko;
-                if (kmoff < klen) j %= kmoff;                                // overlapping copy (ppr:216-219)
-                const uint32_t spos = dp + ko - kmoff + j;                   // absolute output position of the source byte
-                if (spos >= dp + t0) { resolved = false; srcl = spos - (dp + t0); }   // produced in this very step
-                else val = ring[(spos + shift) & (kRing - 1)];
-            }
-            for (;;) {                                                       // chase sources inside the step
-                const uint32_t r = __ballot_sync(0xffffffffu, resolved);
-                if (r == 0xffffffffu) break;
-                const uint32_t v = __shfl_sync(0xffffffffu, val, srcl);
-                if (!resolved && ((r >> srcl) & 1u)) { val = v; resolved = true; }
-            }
-            if (live) ring[(dp + t + shift) & (kRing - 1)] = (uint8_t)val;
-            __syncwarp();
-        }
     } else {
-        // ---- long matches: item after item.  (Here total <= 2184 or <= 2048, so offsets fit 12 bits.)
+        // ---- long matches (or short items with a long one among them): item after item.  (Here total <= 2184 or <= 2048, so
+        //      offsets fit 12 bits.)
         const uint32_t mbits = __ballot_sync(0xffffffffu, is_match);
         const uint32_t runbits = __ballot_sync(0xffffffffu, is_match && moff == 1u);
         const uint32_t packed = my_o | (len << 12);
