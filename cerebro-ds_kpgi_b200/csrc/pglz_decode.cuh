@@ -13,12 +13,14 @@
 //     a dependent global load.  Lane l then holds source byte sp+l (a group is <= 25 bytes);
 //     `__ballot_sync` of "(byte & 0x0F) == 0x0F" tells every lane where 3-byte tags are, so the
 //     item walk of the group is register-only and identical in all lanes.
-//   * Literal runs are written by the lanes that already hold those bytes; a match of length L
-//     is expanded by min(L,32) lanes at a time (overlapping matches read modulo the offset).
+//   * Up to four control groups (32 items) are laid out and decoded lane-parallel per step; short items are then
+//     expanded one lane per item (dependency rounds when a match copies bytes of the same step), long ones item
+//     after item with aligned 16-byte fills and copies.
 //   * Streaks of all-literal groups (control byte 0: incompressible data) are found with one
 //     ballot over the next 32 candidate control bytes and copied 256 bytes at a time, with the
 //     loads of the following 288 source bytes already in flight.
-//   * Datums are handed to warps through a ticket counter, large values first.
+//   * Datums are handed to warps through a ticket counter, large values first; when there are fewer datums than
+//     warps the surplus warps of every CTA leave, so that the datums spread over all SMs.
 //
 // Corruption semantics follow the reference: the datum is corrupt unless decoding ends with
 // dp == destend and sp == srcend (ppr:229-230).  Additionally reported as corrupt (the reference
