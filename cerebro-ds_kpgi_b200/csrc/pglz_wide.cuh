@@ -21,7 +21,7 @@
 //     k_wide_scan / k_wide_check prefix-sum the segments (the total must be rawsize); k_wide_blkmap finds
 //     the sub-segment each output block starts in.
 //
-//  B. What does a match copy?  Output is cut into blocks of 57344 bytes.  A block is rebuilt in shared
+//  B. What does a match copy?  Output is cut into blocks of 49152 bytes.  A block is rebuilt in shared
 //     memory as a forest: every output byte points at the byte it copies (a literal points at itself;
 //     byte k of a match points at start - off + (k mod off), i.e. always before its own item), offsets
 //     are <= 4095 so pointers leave the block only into the last 4095 bytes of the previous block.
@@ -50,15 +50,18 @@ constexpr uint32_t kWideSuper = 256;               // segments per folded map
 constexpr uint32_t kWideSub = 32;                  // source bytes per sub-segment (one emitting thread each; > 25, so a group starts in each)
 constexpr uint32_t kWideSubs = kWideSeg / kWideSub;
 constexpr uint32_t kWideWin = 4095;                // largest pglz offset
-constexpr uint32_t kWideBlock = 57344;             // output bytes per block
-constexpr uint32_t kWideIdx = 61440;               // index space of a block: [previous tail | block], rounded up
+constexpr uint32_t kWideBlock = 12u * 4096u;       // output bytes per block (at pglz ratios up to 0.66 one block is fed by at most 1024
+                                                   // sub-segments: one emission round of the CTA; 14 * 4096 left a second, nearly empty round)
+constexpr uint32_t kWideIdx = kWideBlock + 4096u;  // index space of a block: [previous tail | block], rounded up
 constexpr uint32_t kWideThreads = 1024;
-constexpr uint32_t kWidePer = kWideIdx / kWideThreads;   // 60 entries per thread
+constexpr uint32_t kWidePer = kWideIdx / kWideThreads;   // entries per thread
+static_assert(kWideIdx % kWideThreads == 0 && kWidePer <= 64 && kWideIdx < 65535, "block geometry");
 constexpr uint32_t kWideEnd = 30, kWideBad = 31;   // map states besides the entry offsets 0..24
 constexpr uint32_t kWideChase = 48;                // pass 1 follows a tail byte's chain this many hops before resolving the whole block
 constexpr uint32_t kWideShort = 16;                // (cut) matches up to this long are written byte by byte by the emitting thread (the fill
                                                    // pass below costs ~10x more per byte; only long matches, whose bytes would serialise one thread, go there)
 constexpr uint32_t kWideMinRaw = 1024;             // below this the maps would not fit the output region
+static_assert(kWideShort == 16, "the emission writes short matches as two predicated groups of 8");
 constexpr size_t kWideBlockSmem = (size_t)kWideIdx * 3 + kWideIdx / 8;
 
 struct __align__(16) WideJob {
@@ -653,9 +656,8 @@ k_wide_blkmap(WideArea wa)
 
 // ---- B: blocks -----------------------------------------------------------------------------------------
 
-__device__ __forceinline__ bool wide_is_head(const uint32_t *heads, uint32_t e) { return (heads[e >> 5] >> (e & 31u)) & 1u; }
 
-// Nearest item start at or below e (there is one within 273 entries of any emitted byte).
+// Nearest long-match head at or below e (within 273 entries of any byte of a long match's body).
 __device__ __forceinline__ uint32_t wide_head_of(const uint32_t *heads, uint32_t e)
 {
     uint32_t w = e >> 5;
@@ -702,6 +704,10 @@ k_wide_blocks(WideArea wa)
         const uint32_t slen = wj.slen;
 
         for (uint32_t i = tid; i < kWideIdx / 32; i += kWideThreads) heads[i] = 0;
+        // every entry of the block starts as "not written" (no pointer has this value: kWideIdx < 65535)
+        for (uint32_t i = (kWideWin + 1u) / 8u + tid; i < kWideIdx / 8u; i += kWideThreads)
+            reinterpret_cast<uint4 *>(ptr)[i] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+        if (tid == 0) ptr[kWideWin] = (uint16_t)0xFFFFu;
         // the previous tail: terminal entries (their bytes are known in pass 3 only: k_wide_tails left them at the end
         // of the previous block's region)
         for (uint32_t e = tid; e < kWideWin; e += kWideThreads) {
@@ -715,8 +721,9 @@ k_wide_blocks(WideArea wa)
         }
 
         // ---- items: one thread per 32-byte source sub-segment that feeds this block.  Literals and every byte of a
-        //      match of up to kWideShort bytes get their pointer here and are marked in the bitmap; of a longer match
-        //      only the first byte is (its offset is parked in the two unused value bytes), the body is filled in below.
+        //      match of up to kWideShort bytes get their pointer here; of a longer match only the first byte does (its
+        //      offset is parked in the two unused value bytes, its entry is marked in the bitmap of long-match heads), the
+        //      body keeps the "not written" value and is filled in below.
         const uint32_t floor_idx = k == 0u ? kWideWin : 0u;                  // nothing exists before the output start
         const uint32_t sub0 = wa.blk_sub0[b], sub1 = k + 1u < wj.nblk ? wa.blk_sub0[b + 1] : (slen ? (slen - 1u) / kWideSub : 0u);
         const uint32_t *fine = wa.sub_entry + (size_t)wj.seg0 * kWideSubs;
@@ -727,14 +734,6 @@ k_wide_blocks(WideArea wa)
             uint32_t a = sb * kWideSub + (ent & 31u);
             uint32_t o = (uint32_t)(wa.seg_base[wj.seg0 + sb / kWideSubs] - value_base) + (ent >> 5);
             const uint32_t send = min((sb + 1u) * kWideSub, slen);
-            // item starts are collected per 32-entry word of the bitmap and published with one atomic per word
-            uint32_t hw = kNone, hm = 0;
-            auto mark = [&](uint32_t e0, uint32_t n) {                           // n <= kWideShort < 32
-                const uint32_t w0 = e0 >> 5, sh = e0 & 31u, mask = (1u << n) - 1u;
-                if (w0 != hw) { if (hm) atomicOr(&heads[hw], hm); hw = w0; hm = 0; }
-                hm |= mask << sh;
-                if (sh + n > 32u) { atomicOr(&heads[hw], hm); hw = w0 + 1u; hm = mask >> (32u - sh); }
-            };
             while (a < send && o < o1) {
                 const uint32_t ctrl = __ldg(src + a);
                 uint32_t q = a + 1u;
@@ -767,12 +766,11 @@ k_wide_blocks(WideArea wa)
                                         if (++r == off) r = 0;
                                     }
                                 }
-                                mark(e0, n);
                             } else {
                                 ptr[e0] = (uint16_t)(e0 - off);
                                 val[e0] = (uint8_t)off;
                                 val[e0 + 1u] = (uint8_t)(off >> 8);
-                                mark(e0, 1u);
+                                atomicOr(&heads[e0 >> 5], 1u << (e0 & 31u));
                             }
                         }
                         o += len;
@@ -781,7 +779,6 @@ k_wide_blocks(WideArea wa)
                             const uint32_t e = kWideWin + (o - o0);
                             val[e] = __ldg(src + q);
                             ptr[e] = (uint16_t)e;
-                            mark(e, 1u);
                         }
                         o += 1u;
                         q += 1u;
@@ -789,7 +786,6 @@ k_wide_blocks(WideArea wa)
                 }
                 a = q;
             }
-            if (hm) atomicOr(&heads[hw], hm);
         }
         __syncthreads();
         if (sh_bad) {
@@ -800,13 +796,15 @@ k_wide_blocks(WideArea wa)
         }
 
         // ---- bodies of long matches: point at the byte they copy (always before their own item)
-        uint32_t act[2] = {0u, 0u};                                          // my entries that are not yet resolved
+        // my entries i * kWideThreads + tid of the block: i in [i_lo, i_hi)
+        const uint32_t i_lo = (kWideWin - tid + kWideThreads - 1u) / kWideThreads,
+                       i_hi = (kWideWin + n_out - tid + kWideThreads - 1u) / kWideThreads;
+        const unsigned long long act64 = (i_hi >= 64u ? ~0ull : (1ull << i_hi) - 1ull) & ~((1ull << i_lo) - 1ull);
+        uint32_t act[2] = {(uint32_t)act64, (uint32_t)(act64 >> 32)};        // my entries that are not yet resolved
 #pragma unroll 4
-        for (uint32_t i = 0; i < kWidePer; i++) {
+        for (uint32_t i = i_lo; i < i_hi; i++) {
             const uint32_t e = i * kWideThreads + tid;
-            if (e < kWideWin || e >= kWideWin + n_out) continue;
-            act[i >> 5] |= 1u << (i & 31u);
-            if (wide_is_head(heads, e)) continue;
+            if (ptr[e] != (uint16_t)0xFFFFu) continue;                       // written by the emission
             const uint32_t h = wide_head_of(heads, e);
             if (h == kNone) { sh_bad = 1u; ptr[e] = (uint16_t)e; continue; }  // cannot happen on a stream k_wide_chain accepted
             const uint32_t off = (uint32_t)val[h] | ((uint32_t)val[h + 1u] << 8), kk = e - h;
@@ -838,7 +836,7 @@ k_wide_blocks(WideArea wa)
         }
         // ---- pointer jumping (two hops a round) until every byte points at a literal of the block or into the
         //      previous tail; resolved entries leave the per-thread work mask
-        // (pointers only ever point backwards, so the forest has no cycle and log2(61440) rounds suffice; the bound is a
+        // (pointers only ever point backwards, so the forest has no cycle and log2(kWideIdx) rounds suffice; the bound is a
         // safety net: a kernel must not spin on damaged input)
         for (uint32_t round = 0; resolve_all; round++) {
             if (round > 24u) { sh_bad = 1u; break; }
@@ -931,9 +929,10 @@ k_wide_blocks(WideArea wa)
 //            of the next block reads them (the end of the block's own output region).
 // The maps do not depend on the chain, so they are fetched kTailAhead steps ahead; the serial step is a
 // shared-memory gather.  Folded maps and entering tails live in the group's first block's output region (regions
-// are at least 28672 bytes: float32 -> bfloat16 output halves them).
+// are at least kWideBlock / 2 = 24576 bytes: float32 -> bfloat16 output halves them).
 constexpr uint32_t kTailGroup = 32, kTailAhead = 6;
 constexpr uint32_t kTailGmapOff = 8192, kTailGtailOff = 16384;               // inside the first block of a group
+static_assert(kTailGtailOff + 4096u <= kWideBlock / 2u, "the tail scratch must fit the smallest block region");
 
 __device__ __forceinline__ const uint16_t *wide_u16_at(const uint8_t *p)
 {

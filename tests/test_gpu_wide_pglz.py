@@ -12,6 +12,7 @@ pytestmark = pytest.mark.gpu
 
 # CDS_FUZZ_SEED=k shifts every generator seed: soak runs over other random cases (0: the committed, reproducible ones)
 SEED_SHIFT = int(__import__("os").environ.get("CDS_FUZZ_SEED", "0"))
+BLOCK = 12 * 4096          # kWideBlock of csrc/pglz_wide.cuh: output bytes per block of the wide decoder
 
 
 @pytest.fixture(scope="module")
@@ -61,7 +62,7 @@ def test_wide_matches_oracle_on_structured_streams(torch_cuda, coracle, wide_thr
     wide_threshold(1024)
     rng = np.random.default_rng(4242 + SEED_SHIFT)
     datums, raws = [], []
-    sizes = [1024, 1025, 4095, 4096, 4097, 57343, 57344, 57345, 61439, 2 * 57344, 2 * 57344 + 1, 3 * 57344 - 1, 300001]
+    sizes = [1024, 1025, 4095, 4096, 4097, BLOCK - 1, BLOCK, BLOCK + 1, BLOCK + 4095, 2 * BLOCK, 2 * BLOCK + 1, 3 * BLOCK - 1, 57344, 300001]
     for t, n in enumerate(sizes + [int(rng.integers(1024, 400000)) for _ in range(24)]):
         kind = t % 4
         raw = (structured_bytes(rng, n) if kind == 0 else image_like(rng, n) if kind == 1 else
@@ -291,16 +292,16 @@ def test_more_wide_candidates_than_the_work_area_holds(torch_cuda, coracle, wide
 
 def test_wide_streams_ending_on_segment_and_block_boundaries(torch_cuda, coracle, wide_threshold):
     """Literal-only streams of 4096 m bytes are 4608 m = 9 * 512 m bytes long: the stream ends exactly on a source
-    segment boundary; 57344-byte multiples end exactly on an output block boundary."""
+    segment boundary; multiples of the output block (49152 bytes) end exactly on a block boundary."""
     from cerebro_ds_kpgi_b200 import segment, synth
     wide_threshold(1024)
     rng = np.random.default_rng(8 + SEED_SHIFT)
-    sizes = [4096, 4096 * 2, 4096 * 13, 4096 * 14, 4096 * 15, 4096 * 28, 4096 * 29, 57344 * 3]
+    sizes = [4096, 4096 * 2, 4096 * 11, 4096 * 12, 4096 * 13, 4096 * 14, 4096 * 24, 4096 * 25, BLOCK * 3]
     raws = [rng.integers(0, 256, n, dtype=np.uint8) for n in sizes]
     datums = [synth.pglz_varlena(r, "literal") for r in raws]
     for d, n in zip(datums, sizes):
         assert (len(d) - 8) % 512 == 0, n
-    raws += [structured_bytes(rng, n) for n in (57344, 57344 * 2, 57344 * 4)]
+    raws += [structured_bytes(rng, n) for n in (BLOCK, BLOCK * 2, BLOCK * 4, 57344)]
     datums += [synth.pglz_varlena(r, "lz") for r in raws[len(sizes):]]
     out, codes = segment.pglz_decompress_batch(datums)
     assert codes == [0] * len(datums)
