@@ -73,6 +73,7 @@ PROTOTYPES = {
     "cds_pglz_decompress_batch": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp]),
     "cds_pglz_decompress_batch_static": (_int, [_int, _vp, _vp, _vp, _vp, _u64, _vp, _vp, _vp]),
     "cds_set_wide_pglz_threshold": (_int, [_u32, _int]),
+    "cds_set_wide_store_limit": (_int, [_u64]),
     "cds_set_wide_pglz": (_int, [_vp, _int]),
     "cds_trim_work_memory": (_int, [_int]),
     "cds_wide_decoded_count": (ctypes.c_ulonglong, []),

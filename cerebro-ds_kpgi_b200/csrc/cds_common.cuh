@@ -44,7 +44,8 @@ struct DevState {
     uint32_t n_jobs_back;         // ... small values from the last slot down
     uint32_t n_wide;              // compressed values at or above the wide-decode threshold (pglz_wide.cuh)
     uint32_t n_wide_taken;        // values the wide decoder accepted, summed over the classifications of this decode
-    uint32_t pad_[2];
+    uint32_t n_wide_blks;         // most output blocks any one of those classifications handed to the wide decoder
+    uint32_t pad_[1];
 };
 
 // One TOAST chunk -> one copy.  dst == 0: chunk not referenced (or refused); nothing is copied.

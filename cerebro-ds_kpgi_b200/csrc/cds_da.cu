@@ -26,6 +26,7 @@ static thread_local char g_last_error[512] = "";
 static unsigned long long g_launches = 0;   // kernels launched by this library (bench.py reports it)
 #define LAUNCHED(n) (g_launches += (n))
 static uint32_t g_wide_threshold = 1u << 20;   // cds_set_wide_pglz_threshold
+static uint64_t g_wide_store_limit = ~0ull;   // cds_set_wide_store_limit: most bytes a handle's store of resolved blocks may take (0: none)
 static int g_wide_force = 0;                   // ... its second argument: skip the cost model
 static unsigned long long g_wide_decoded = 0;  // values decoded by the wide decoder so far (cds_wide_decoded_count)
 static unsigned long long g_streamed = 0, g_stream_redone = 0;   // cds_decode_host calls that took the streamed path / were decoded again
@@ -101,6 +102,8 @@ struct cds_segment {
     bool wide_launched = false;     // this decode classified its jobs: cds_finish reads the counters (and decodes what is left)
     WideArea last_wa;               // the work area as this decode's classification used it
     uint8_t *wide_mem = nullptr;    // work area of the intra-value parallel pglz decoder (pglz_wide.cuh)
+    uint16_t *wide_store = nullptr; // its store of resolved blocks (2 bytes per decoded byte of the wide values of one decode), sized by cds_finish
+    uint64_t wide_store_blks = 0;
     WideArea wide;
     uint32_t lut_channels = 0;
     // device buffers
@@ -215,11 +218,14 @@ static cudaError_t pglz_prepare(int device)
 static cudaError_t wide_prepare()
 {
     cudaError_t e = cudaFuncSetAttribute(k_wide_blocks<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_blocks<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_blocks<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideFinishSmem);
     return e;
 }
 
-// The 13 kernels behind the classification, on stream `st`.
+// The 15 kernels behind the classification, on stream `st` (of the four block kernels two return at once: <2> + finish run
+// when the decode's blocks fit the store of resolved blocks, <1> + <3> otherwise).
 #define CDS_WIDE_PIPELINE(wa, sms, st, BEFORE_B1, AFTER_B1, BEFORE_B3, AFTER_B3)            \
     do {                                                                                    \
         k_wide_maps<<<(sms) * 8u, 256, 0, st>>>(wa);                                        \
@@ -231,6 +237,7 @@ static cudaError_t wide_prepare()
         k_wide_check<<<8, 256, 0, st>>>(wa);                                                \
         k_wide_blkmap<<<(sms) * 2u, 256, 0, st>>>(wa);                                      \
         BEFORE_B1;                                                                          \
+        k_wide_blocks<2><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
         k_wide_blocks<1><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
         AFTER_B1;                                                                           \
         k_wide_tails<0><<<(sms), 1024, 0, st>>>(wa);                                        \
@@ -238,11 +245,12 @@ static cudaError_t wide_prepare()
         k_wide_tails<2><<<(sms), 1024, 0, st>>>(wa);                                        \
         BEFORE_B3;                                                                          \
         k_wide_blocks<3><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
+        k_wide_finish<<<(sms) * 2u, kFinishThreads, kWideFinishSmem, st>>>(wa);             \
         AFTER_B3;                                                                           \
     } while (0)
 
 // Classify the job list (cost model on the device); the jobs taken are blanked, so the warp decoder that runs
-// afterwards skips them.  with_pipeline: also decode them (the 13 kernels; `ev4`: optional event pairs around the two
+// afterwards skips them.  with_pipeline: also decode them (the 15 kernels; `ev4`: optional event pairs around the two
 // block passes).  Without it only the classification runs (one small launch): if it does take values,
 // kFlagNeedWide is raised and cds_finish runs wide_pipeline() for them.
 static int wide_pipeline(WideArea wa, int num_sms, cudaStream_t st, cudaEvent_t *ev4 = nullptr, unsigned ev_flags = cudaEventRecordDefault)
@@ -253,7 +261,7 @@ static int wide_pipeline(WideArea wa, int num_sms, cudaStream_t st, cudaEvent_t 
                       if (ev4) cudaEventRecordWithFlags(ev4[0], st, ev_flags), if (ev4) cudaEventRecordWithFlags(ev4[1], st, ev_flags),
                       if (ev4) cudaEventRecordWithFlags(ev4[2], st, ev_flags), if (ev4) cudaEventRecordWithFlags(ev4[3], st, ev_flags));
     CU(cudaGetLastError());
-    LAUNCHED(13);
+    LAUNCHED(15);
     return CDS_OK;
 }
 
@@ -291,6 +299,7 @@ extern "C" int cds_segment_destroy(cds_segment *s)
                     s->row_first, s->pos_of_row, s->row_at_pos, s->ind_len, s->dep_len, s->pos_ind, s->pos_dep,
                     s->row_ind_off, s->row_dep_off, s->ops, s->jobs, s->scratch, s->wide_mem};
     for (void *b : bufs) if (b) cudaFree(b);
+    if (s->wide_store) cudaFree(s->wide_store);
     if (s->stream_mem) cudaFree(s->stream_mem);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     for (cudaStream_t x : s->dec_stream) if (x) cudaStreamDestroy(x);
@@ -642,7 +651,7 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
         wa.lut = lut;
         wa.lut_channels = s->lut_channels ? s->lut_channels : 1u;
         s->last_wa = wa;
-        // mode 2: the 13 kernels of the wide decoder are enqueued when the handle's last summary saw values go wide;
+        // mode 2: the 15 kernels of the wide decoder are enqueued when the handle's last summary saw values go wide;
         // the classification always runs, and what it takes without them is decoded by cds_finish (see there)
         const bool pipeline = s->wide_mode != 2 || s->wide_hint;
         int rc = launch_wide(s->jobs, s->state, 0u, wa, s->num_sms, st, pipeline, (timed && pipeline) ? ev + 4 : nullptr, ev_flags);
@@ -688,6 +697,31 @@ static void decode_key(unsigned long long key, cds_summary *sum)
     sum->err_where = (key >> 28) & 0x1FFFFFFFFull;
 }
 
+// The store of resolved blocks follows what the handle's decodes need: when one handed the wide decoder more blocks than the
+// store holds (none at first), the store is replaced by one an eighth larger than that, for the decodes that follow --
+// if it stays within cds_set_wide_store_limit and half of the device memory that is free.  The stream is idle here.
+static void wide_store_follow(cds_segment *s, uint32_t blks)
+{
+    if (!g_wide_store_limit || blks <= s->wide_store_blks) return;
+    const uint64_t want = (uint64_t)blks + blks / 8u + 16u, bytes = want * kWideBlock * sizeof(uint16_t);
+    const uint64_t held = s->wide_store_blks * (uint64_t)kWideBlock * sizeof(uint16_t);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return; }
+    if (want > 0xFFFFFFFFull || bytes > g_wide_store_limit || bytes > ((uint64_t)free_b + held) / 2u) return;
+    if (s->wide_store) cudaFree(s->wide_store);
+    s->wide_store = nullptr; s->wide_store_blks = 0;
+    if (cudaMalloc(reinterpret_cast<void **>(&s->wide_store), bytes) != cudaSuccess) { cudaGetLastError(); s->wide_store = nullptr; }
+    else s->wide_store_blks = want;
+    s->wide.store = s->last_wa.store = s->wide_store;
+    s->wide.store_blks = s->last_wa.store_blks = (uint32_t)s->wide_store_blks;
+}
+
+extern "C" int cds_set_wide_store_limit(uint64_t bytes)
+{
+    g_wide_store_limit = bytes;
+    return CDS_OK;
+}
+
 extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
 {
     if (!s) return CDS_ERR_ARG;
@@ -727,6 +761,7 @@ extern "C" int cds_finish(cds_segment *s, void *stream, cds_summary *sum)
         g_wide_decoded += h.n_wide_taken;
         s->wide_hint = h.n_wide_taken != 0;
         s->wide_launched = false;
+        if (h.n_wide_taken) wide_store_follow(s, h.n_wide_blks);
     }
     cds_summary local;
     memset(&local, 0, sizeof(local));
@@ -1175,10 +1210,14 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
     // work area of this call: [offset tables | jobs | status words + ticket | wide area]
     const size_t off_bytes = align256(sizeof(uint64_t) * 2 * (n + 1)), job_bytes = align256(sizeof(PglzJob) * n),
                  stat_bytes = align256(sizeof(int32_t) * (n + 1));
-    const size_t total = off_bytes + job_bytes + stat_bytes + (any_wide ? wide_area_bytes(wj, ws_, wb) : 0);
+    const size_t total = off_bytes + job_bytes + stat_bytes + (any_wide ? align256(wide_area_bytes(wj, ws_, wb)) : 0);
+    // ... | store of resolved blocks] when the call has wide values and the store fits (else they are parsed twice)
+    size_t store_bytes = any_wide ? (size_t)wb * kWideBlock * sizeof(uint16_t) : 0;
+    if (store_bytes > g_wide_store_limit) store_bytes = 0;
     std::lock_guard<std::mutex> lock(g_work_mu[kWorkBatch]);
     uint8_t *base = nullptr;
-    cudaError_t e = work_reserve(device, kWorkBatch, total, &base);
+    cudaError_t e = work_reserve(device, kWorkBatch, total + store_bytes, &base);
+    if (e != cudaSuccess && store_bytes) { cudaGetLastError(); store_bytes = 0; e = work_reserve(device, kWorkBatch, total, &base); }
     if (e != cudaSuccess) return cuda_fail(e, "cds_pglz_decompress_batch: work area");
     unsigned long long *d_off = reinterpret_cast<unsigned long long *>(base);
     PglzJob *d_jobs = reinterpret_cast<PglzJob *>(base + off_bytes);
@@ -1199,6 +1238,7 @@ extern "C" int cds_pglz_decompress_batch(int device, const void *d_src, const ui
             wa.threshold = thr;
             wa.force = g_wide_force ? 1u : 0u;
             wa.status = d_stat;
+            if (store_bytes) { wa.store = reinterpret_cast<uint16_t *>(base + total); wa.store_blks = wb; }
             if (cudaMemsetAsync(wa.state, 0, 256, st) != cudaSuccess || launch_wide(d_jobs, nullptr, (uint32_t)n, wa, sms, st) != CDS_OK) e = cudaErrorUnknown;
         }
         uint32_t grid = (uint32_t)((n + kPglzWarps - 1) / kPglzWarps);

@@ -83,7 +83,8 @@ struct WideState {       // zero when a decode starts
     uint32_t n_jobs, n_segs, n_blks;
     uint32_t t_maps, t_l1, t_l3, t_scan;
     uint32_t n_taken;    // values this decoder accepted (the rest stay with the warp decoder)
-    uint32_t pad[8];
+    uint32_t t_l2;
+    uint32_t pad[7];
 };
 
 struct WideArea {
@@ -108,7 +109,15 @@ struct WideArea {
     DevState *st;            // first-error word (may be null)
     const float *lut;        // fmt 2: [channels][256]
     uint32_t lut_channels;
+    // Optional store of resolved blocks (not part of the carved area; the caller owns it): kWideBlock uint16 entries per flat
+    // output block, each "0x8000 | byte" or "index into the tail of the previous block".  With it a block is parsed once
+    // (k_wide_blocks<2>) and written by a streaming kernel (k_wide_finish); without it, or when a decode has more blocks
+    // than the store holds, the block is parsed twice (k_wide_blocks<1>, <3>).
+    uint16_t *store;
+    uint32_t store_blks;
 };
+
+__device__ __forceinline__ bool wide_stored(const WideArea &wa) { return wa.store != nullptr && wa.state->n_blks <= wa.store_blks; }
 
 __host__ __device__ inline size_t wide_align(size_t x) { return (x + 255) & ~(size_t)255; }
 __host__ __device__ inline size_t wide_scan_tiles(uint32_t cap_segs) { return (size_t)cap_segs / (kScanThreads * 8) + 2; }
@@ -144,6 +153,7 @@ inline WideArea wide_area_carve(uint8_t *base, uint32_t cap_jobs, uint32_t cap_s
     wa.blk_sub0 = reinterpret_cast<uint32_t *>(p);
     wa.cap_jobs = cap_jobs; wa.cap_segs = cap_segs; wa.cap_blks = cap_blks;
     wa.threshold = 0; wa.force = 0; wa.status = nullptr; wa.st = nullptr; wa.lut = nullptr; wa.lut_channels = 1;
+    wa.store = nullptr; wa.store_blks = 0;
     return wa;
 }
 
@@ -313,6 +323,7 @@ k_wide_classify(PglzJob *jobs, DevState *st_counts, uint32_t n_jobs_host, WideAr
     __syncthreads();
     if (threadIdx.x == 0 && st_counts) {
         if (wa.state->n_taken) atomicAdd(&st_counts->n_wide_taken, wa.state->n_taken);
+        atomicMax(&st_counts->n_wide_blks, wa.state->n_blks);
         if (deferred && wa.state->n_jobs != 0u) atomicOr(&st_counts->flags, kFlagNeedWide);
     }
 }
@@ -666,6 +677,38 @@ __device__ __forceinline__ uint32_t wide_head_of(const uint32_t *heads, uint32_t
     return m ? (w << 5) + 31u - (uint32_t)__clz((int)m) : kNone;
 }
 
+// Write bytes [0, n_out) of a block (byte(i) gives them) in the value's output format; `region` is the block's part of
+// the output buffer, o0 the block's offset in the decoded value.
+template <typename Byte>
+__device__ __forceinline__ void wide_write_block(uint32_t fmt, uint8_t *region, uint32_t o0, uint32_t n_out, const float *lut,
+                                                 uint32_t lut_channels, uint32_t tid, uint32_t nth, Byte byte)
+{
+    if (fmt == 1u) {
+        // float32 -> bfloat16 (round to nearest even), one element per thread and step
+        __nv_bfloat16 *g = reinterpret_cast<__nv_bfloat16 *>(region);
+        for (uint32_t f = tid; f < (n_out >> 2); f += nth) {
+            const uint32_t x = byte(4u * f) | (byte(4u * f + 1u) << 8) | (byte(4u * f + 2u) << 16) | (byte(4u * f + 3u) << 24);
+            g[f] = __float2bfloat16_rn(__uint_as_float(x));
+        }
+    } else if (fmt == 2u) {
+        // uint8 pixel component -> float32 table[channel][x]
+        float *g = reinterpret_cast<float *>(region);
+        for (uint32_t i = tid; i < n_out; i += nth) __stcs(g + i, __ldg(lut + ((o0 + i) % lut_channels) * 256u + byte(i)));
+    } else {
+        uint8_t *g = region;
+        const uint32_t head = min(n_out, (uint32_t)((4u - (reinterpret_cast<uintptr_t>(g) & 3u)) & 3u));
+        if (tid < head) g[tid] = (uint8_t)byte(tid);
+        const uint32_t nw = (n_out - head) >> 2;
+        for (uint32_t w = tid; w < nw; w += nth) {
+            const uint32_t i0 = head + 4u * w;
+            const uint32_t x = byte(i0) | (byte(i0 + 1u) << 8) | (byte(i0 + 2u) << 16) | (byte(i0 + 3u) << 24);
+            __stcs(reinterpret_cast<uint32_t *>(g + i0), x);
+        }
+        const uint32_t t0 = head + 4u * nw;
+        if (tid < n_out - t0) g[t0 + tid] = (uint8_t)byte(t0 + tid);
+    }
+}
+
 template <int kMode>
 __global__ void __launch_bounds__(kWideThreads, 1)
 k_wide_blocks(WideArea wa)
@@ -676,8 +719,9 @@ k_wide_blocks(WideArea wa)
     uint32_t *heads = reinterpret_cast<uint32_t *>(wide_smem + 3 * (size_t)kWideIdx);   // [kWideIdx / 32]
     __shared__ uint32_t sh_b, sh_j, sh_bad;
     const uint32_t n_jobs = wa.state->n_jobs, n_blks = wa.state->n_blks, tid = threadIdx.x;
-    uint32_t *ticket = kMode == 1 ? &wa.state->t_l1 : &wa.state->t_l3;
+    uint32_t *ticket = kMode == 1 ? &wa.state->t_l1 : kMode == 2 ? &wa.state->t_l2 : &wa.state->t_l3;
     if (n_jobs == 0) return;
+    if ((kMode == 2) != wide_stored(wa)) return;                             // one parse into the store, or two without it
     for (;;) {
         __syncthreads();
         if (tid == 0) {
@@ -820,7 +864,7 @@ k_wide_blocks(WideArea wa)
         // Pass 1 only needs the roots of the block's last 4095 bytes: follow those chains directly, a bounded number
         // of hops; only when a chain is longer (run-dominated data) resolve the whole block as pass 3 does.
         bool resolve_all = true;
-        uint32_t tail_root[4];
+        uint32_t tail_root[4] = {0u, 0u, 0u, 0u};
         if (kMode == 1) {
             int unfinished = 0;
 #pragma unroll
@@ -865,6 +909,20 @@ k_wide_blocks(WideArea wa)
             continue;
         }
 
+        if (kMode == 2) {
+            // every byte of the block as "value" or "index into the previous tail", 4 entries per thread and step
+            uint16_t *map = wa.store + (size_t)b * kWideBlock;
+            for (uint32_t f = tid; f < (n_out + 3u) / 4u; f += kWideThreads) {
+                uint32_t m[4];
+#pragma unroll
+                for (uint32_t j = 0; j < 4; j++) {
+                    const uint32_t r = 4u * f + j < n_out ? (uint32_t)ptr[kWideWin + 4u * f + j] : 0u;
+                    m[j] = r >= kWideWin ? 0x8000u | val[r] : r;
+                }
+                *reinterpret_cast<uint2 *>(map + 4u * f) = make_uint2(m[0] | (m[1] << 16), m[2] | (m[3] << 16));
+            }
+            continue;
+        }
         if (kMode == 1) {
             // the block's last 4095 bytes, each as "value" or "index into the previous tail"
             uint16_t *map = reinterpret_cast<uint16_t *>((reinterpret_cast<uintptr_t>(region) + 1u) & ~(uintptr_t)1u);
@@ -887,35 +945,8 @@ k_wide_blocks(WideArea wa)
             }
             __syncthreads();
         }
-        if (wj.fmt == 1u) {
-            // float32 -> bfloat16 (round to nearest even), one element per thread and step
-            __nv_bfloat16 *g = reinterpret_cast<__nv_bfloat16 *>(region);
-            for (uint32_t f = tid; f < (n_out >> 2); f += kWideThreads) {
-                const uint32_t e0 = kWideWin + 4u * f;
-                const uint32_t x = (uint32_t)val[ptr[e0]] | ((uint32_t)val[ptr[e0 + 1u]] << 8) |
-                                   ((uint32_t)val[ptr[e0 + 2u]] << 16) | ((uint32_t)val[ptr[e0 + 3u]] << 24);
-                g[f] = __float2bfloat16_rn(__uint_as_float(x));
-            }
-        } else if (wj.fmt == 2u) {
-            // uint8 pixel component -> float32 table[channel][x]
-            float *g = reinterpret_cast<float *>(region);
-            const uint32_t ch = wa.lut_channels;
-            for (uint32_t i = tid; i < n_out; i += kWideThreads)
-                __stcs(g + i, __ldg(wa.lut + ((o0 + i) % ch) * 256u + val[ptr[kWideWin + i]]));
-        } else {
-            uint8_t *g = region;
-            const uint32_t head = min(n_out, (uint32_t)((4u - (reinterpret_cast<uintptr_t>(g) & 3u)) & 3u));
-            if (tid < head) g[tid] = val[ptr[kWideWin + tid]];
-            const uint32_t nw = (n_out - head) >> 2;
-            for (uint32_t w = tid; w < nw; w += kWideThreads) {
-                const uint32_t e0 = kWideWin + head + 4u * w;
-                const uint32_t x = (uint32_t)val[ptr[e0]] | ((uint32_t)val[ptr[e0 + 1u]] << 8) |
-                                   ((uint32_t)val[ptr[e0 + 2u]] << 16) | ((uint32_t)val[ptr[e0 + 3u]] << 24);
-                __stcs(reinterpret_cast<uint32_t *>(g + head + 4u * w), x);
-            }
-            const uint32_t t0 = head + 4u * nw;
-            if (tid < n_out - t0) g[t0 + tid] = val[ptr[kWideWin + t0 + tid]];
-        }
+        wide_write_block(wj.fmt, region, o0, n_out, wa.lut, wa.lut_channels, tid, kWideThreads,
+                         [&](uint32_t i) { return (uint32_t)val[ptr[kWideWin + i]]; });
     }
 }
 
@@ -948,6 +979,7 @@ k_wide_tails(WideArea wa)
     const uint32_t n_jobs = wa.state->n_jobs, tid = threadIdx.x;
     if (n_jobs == 0) return;
     const uint32_t n_units = kPhase == 1 ? n_jobs : wa.state->n_blks;        // phase 1: values; phases 0, 2: group leaders
+    const bool stored = wide_stored(wa);
     for (uint32_t u = blockIdx.x; u < n_units; u += gridDim.x) {
         __syncthreads();
         if (tid == 0) sh_j = kPhase == 1 ? u : wide_find_blk(wa, n_jobs, u);
@@ -969,8 +1001,11 @@ k_wide_tails(WideArea wa)
         const uint32_t fmt = wj.fmt;
         auto region = [&](uint32_t blk) { return dst + wide_scale(fmt, (size_t)blk * kWideBlock); };   // block's part of the output buffer
         const size_t region_bytes = wide_scale(fmt, (size_t)kWideBlock);
+        // a block's tail map: the first 8190 bytes of its output region, or the last 4095 entries of its stored map
+        auto stored_map = [&](uint32_t blk) { return wa.store + (size_t)(wj.blk0 + blk) * kWideBlock + (kWideBlock - kWideWin); };
         auto map_of = [&](uint32_t step) {
-            return kPhase == 1 ? wide_u16_at(region(step * kTailGroup) + kTailGmapOff) : wide_u16_at(region(first + step));
+            return kPhase == 1 ? wide_u16_at(region(step * kTailGroup) + kTailGmapOff)
+                               : stored ? (const uint16_t *)stored_map(first + step) : wide_u16_at(region(first + step));
         };
         // state entering the unit
         for (uint32_t i = tid; i < 4096; i += blockDim.x) {
@@ -1008,7 +1043,10 @@ k_wide_tails(WideArea wa)
                         if (i < kWideWin) {
                             const uint32_t v = (mm & 0x8000u) ? mm : tail[cur][mm & 4095u];
                             tail[cur ^ 1u][i] = (uint16_t)v;
-                            if (kPhase == 2) out[i] = (uint8_t)v;
+                            if (kPhase == 2) {
+                                if (stored) stored_map(first + k)[i] = (uint16_t)(0x8000u | (v & 0xFFu));   // (read above, by this thread)
+                                else out[i] = (uint8_t)v;
+                            }
                         }
                         const uint32_t kn = k + kTailAhead;
                         m[a][j] = kn < nsteps && i < kWideWin ? map_of(kn)[i] : 0x8000u;
@@ -1022,6 +1060,42 @@ k_wide_tails(WideArea wa)
             uint16_t *gm = const_cast<uint16_t *>(wide_u16_at(region(first) + kTailGmapOff));
             for (uint32_t i = tid; i < kWideWin; i += blockDim.x) gm[i] = tail[cur][i];
         }
+    }
+}
+
+// Stored blocks -> output (the streaming half of the one-parse path): a block's map and the previous block's tail
+// (which k_wide_tails<2> has turned into bytes, in place) are staged in shared memory, then written in the output format.
+constexpr uint32_t kFinishThreads = 512;
+constexpr size_t kWideFinishSmem = 2 * (size_t)kWideBlock + 4096;
+__global__ void __launch_bounds__(kFinishThreads, 2)
+k_wide_finish(WideArea wa)
+{
+    extern __shared__ __align__(16) uint8_t wide_smem[];
+    uint16_t *map = reinterpret_cast<uint16_t *>(wide_smem);                 // [kWideBlock]
+    uint8_t *tail = wide_smem + 2 * (size_t)kWideBlock;                      // [4096]
+    __shared__ uint32_t sh_j;
+    const uint32_t n_jobs = wa.state->n_jobs, n_blks = wa.state->n_blks, tid = threadIdx.x;
+    if (n_jobs == 0 || !wide_stored(wa)) return;
+    for (uint32_t b = blockIdx.x; b < n_blks; b += gridDim.x) {
+        __syncthreads();
+        if (tid == 0) sh_j = wide_find_blk(wa, n_jobs, b);
+        __syncthreads();
+        const WideJob wj = wa.jobs[sh_j];
+        const uint32_t k = b - wj.blk0;
+        if (wj.state != 0u || k >= wj.nblk) continue;
+        const uint32_t o0 = k * kWideBlock, n_out = min(kWideBlock, wj.rawsize - o0);
+        const uint4 *g = reinterpret_cast<const uint4 *>(wa.store + (size_t)b * kWideBlock);
+        for (uint32_t i = tid; i < (n_out + 7u) / 8u; i += kFinishThreads) reinterpret_cast<uint4 *>(map)[i] = __ldcs(g + i);
+        if (k > 0u) {
+            const uint16_t *pt = wa.store + (size_t)(b - 1u) * kWideBlock + (kWideBlock - kWideWin);
+            for (uint32_t i = tid; i < kWideWin; i += kFinishThreads) tail[i] = (uint8_t)pt[i];
+        }
+        __syncthreads();
+        wide_write_block(wj.fmt, reinterpret_cast<uint8_t *>(wj.dst) + wide_scale(wj.fmt, o0), o0, n_out, wa.lut, wa.lut_channels, tid,
+                         kFinishThreads, [&](uint32_t i) {
+                             const uint32_t m = map[i];
+                             return (m & 0x8000u) ? (m & 0xFFu) : (uint32_t)tail[m & 4095u];
+                         });
     }
 }
 

@@ -219,8 +219,17 @@ int cds_pglz_decompress_batch(int device, const void *d_src, const uint64_t *h_s
  * (default 1 MiB; 0 switches the wide decoder off; values under 1024 bytes never take it);
  * skip_cost_model != 0 sends every value at or above the threshold through it (tests, measurements). */
 int cds_set_wide_pglz_threshold(uint32_t decoded_bytes, int skip_cost_model);
+/* The wide decoder parses every 48 KB output block once when it can keep the resolved block (2 bytes per decoded byte:
+ * the byte, or which byte of the previous block's last 4095 it copies) until the blocks' tails are known, and twice when
+ * it cannot.  cds_pglz_decompress_batch / pglz_decompress take that store from their cached work area; a handle gets
+ * one from cds_finish after the first decode that sent values to the wide decoder, sized for that decode plus an eighth
+ * (replaced by a larger one when a later decode needs it, freed by cds_segment_destroy), so the decodes that follow on
+ * the handle take the one-parse path.  Process-wide limit in bytes for any one store (default: none beyond "at most half
+ * of the free device memory"; 0: no store, always two parses).  Same bytes and verdicts either way.  No counterpart in
+ * the reference. */
+int cds_set_wide_store_limit(uint64_t bytes);
 /* Per handle: how the pglz stage of a decode is launched.  Which values go wide is always decided on the device
- * for THIS decode (one small classification kernel after the gather); the modes differ in whether the 13 kernels
+ * for THIS decode (one small classification kernel after the gather); the modes differ in whether the 15 kernels
  * of the wide decoder are enqueued along with it.
  *   2 (default) = they are enqueued when the handle's previous summary saw values go wide, or the handle has not
  *       produced a summary yet (a performance hint only).  When they were not enqueued and the classification does take values, cds_finish runs them before it

@@ -23,16 +23,22 @@ def torch_cuda():
     return torch
 
 
-@pytest.fixture()
-def wide_threshold():
-    """Lower the wide-decode threshold for one test, restore the default afterwards."""
+NO_LIMIT = 2 ** 64 - 1
+
+
+@pytest.fixture(params=["stored_blocks", "two_parses"])
+def wide_threshold(request):
+    """Lower the wide-decode threshold for one test, restore the default afterwards.  Every test runs twice: with the store
+    of resolved blocks (each block parsed once) and without it (cds_set_wide_store_limit(0): each block parsed twice)."""
     from cerebro_ds_kpgi_b200 import _lib
     L = _lib.require_device()
+    _lib.check(L.cds_set_wide_store_limit(NO_LIMIT if request.param == "stored_blocks" else 0))
 
     def set_to(n, force=1):
         _lib.check(L.cds_set_wide_pglz_threshold(int(n), int(force)))
     yield set_to
     _lib.check(L.cds_set_wide_pglz_threshold(1 << 20, 0))
+    _lib.check(L.cds_set_wide_store_limit(NO_LIMIT))
 
 
 def wide_count():
@@ -356,3 +362,39 @@ def test_wide_refuses_offset_zero_and_offsets_before_the_start_without_spinning(
         with pytest.raises(Exception):
             coracle.pglz_decompress(d)
     assert out[-1] == bytes(coracle.pglz_decompress(good))
+
+
+def test_a_handle_gets_its_store_after_the_first_wide_decode(torch_cuda, coracle, wide_threshold):
+    """One handle, three segments of packed buffers in a row: the first decode parses every block twice (the handle has no
+    store of resolved blocks yet), the later ones once -- also a larger segment, which the store does not hold yet, and a
+    smaller one after it.  Same bytes as the oracle every time, in all three output formats."""
+    from cerebro_ds_kpgi_b200 import segment, synth
+    torch = torch_cuda
+    wide_threshold(1 << 16)
+    segs = []
+    for seed, per_row in ((21, 12), (22, 12), (23, 30), (24, 5)):
+        ind, dep = synth.imagenet_rows(3, seed=seed + SEED_SHIFT, shape=(112, 112, 3), classes=1000, images_per_row=per_row)
+        sg = synth.build_segment(ind, dep, ind_storage="ext_pglz", dep_storage="ext_pglz")
+        segs.append((sg, coracle.decode(sg.heap, sg.toast)))
+    max_heap = max(sg.heap.size for sg, _ in segs) // 32768
+    max_toast = max(sg.toast.size for sg, _ in segs) // 32768
+    for bf16 in (False, True):
+        ds = segment.DeviceSegment(max_heap, max_toast)
+        ds.set_output_format(ind_bf16=bf16)
+        try:
+            for sg, want in segs:
+                ind_bytes = want["out_ind"].size // (2 if bf16 else 1)
+                out_ind = torch.full((ind_bytes + 64,), 0xA5, dtype=torch.uint8, device="cuda")
+                out_dep = torch.full((want["out_dep"].size + 64,), 0xA5, dtype=torch.uint8, device="cuda")
+                before = wide_count()
+                s = ds.decode_device(torch.from_numpy(sg.heap).cuda(), torch.from_numpy(sg.toast).cuda(), out_ind, out_dep)
+                assert s.status == 0 and wide_count() - before == 3
+                if bf16:
+                    ref = torch.from_numpy(want["out_ind"].view(np.float32).copy()).to(torch.bfloat16).view(torch.int16)
+                    assert torch.equal(out_ind[:ind_bytes].view(torch.int16).cpu(), ref)
+                else:
+                    assert out_ind[:ind_bytes].cpu().numpy().tobytes() == want["out_ind"].tobytes()
+                assert out_dep[:want["out_dep"].size].cpu().numpy().tobytes() == want["out_dep"].tobytes()
+                assert bool((out_ind[ind_bytes:] == 0xA5).all()) and bool((out_dep[want["out_dep"].size:] == 0xA5).all())
+        finally:
+            ds.close()

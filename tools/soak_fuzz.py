@@ -33,6 +33,16 @@ def main():
              ("wide_streams", lambda: w.test_wide_matches_oracle_on_structured_streams(torch, co, set_thr)),
              ("wide_corrupt", lambda: w.test_wide_corrupt_streams_agree_with_oracle(torch, co, set_thr)),
              ("streamed", lambda: sm.test_streamed_layout_fuzz(torch))]
+
+    def two_parses(fn):                                   # the same case without the store of resolved blocks
+        def run():
+            _lib.check(L.cds_set_wide_store_limit(0))
+            try:
+                fn()
+            finally:
+                _lib.check(L.cds_set_wide_store_limit(2 ** 64 - 1))
+        return run
+    cases += [(name + "_two_parses", two_parses(fn)) for name, fn in cases if name.startswith("wide_") or name == "layout_wide"]
     failed = []
     for k in range(first, last + 1):
         f.SEED_SHIFT = w.SEED_SHIFT = sm.SEED_SHIFT = k
