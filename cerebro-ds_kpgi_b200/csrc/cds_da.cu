@@ -220,7 +220,6 @@ static cudaError_t wide_prepare()
     cudaError_t e = cudaFuncSetAttribute(k_wide_blocks<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_blocks<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_blocks<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideFinishSmem);
     return e;
 }
 
@@ -245,7 +244,7 @@ static cudaError_t wide_prepare()
         k_wide_tails<2><<<(sms), 1024, 0, st>>>(wa);                                        \
         BEFORE_B3;                                                                          \
         k_wide_blocks<3><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
-        k_wide_finish<<<(sms) * 2u, kFinishThreads, kWideFinishSmem, st>>>(wa);             \
+        k_wide_finish<<<(sms) * 4u, kFinishThreads, 0, st>>>(wa);                           \
         AFTER_B3;                                                                           \
     } while (0)
 

@@ -26,15 +26,23 @@
 //     byte k of a match points at start - off + (k mod off), i.e. always before its own item), offsets
 //     are <= 4095 so pointers leave the block only into the last 4095 bytes of the previous block.
 //     Pointer jumping (ptr[i] = ptr[ptr[ptr[i]]], in place) resolves every byte to a literal of the block
-//     or to one of those 4095 previous bytes in O(log depth) rounds.  Pass 1 (k_wide_blocks<1>) does this
-//     with the previous tail unknown and publishes, for the block's own last 4095 bytes, "value" or
-//     "index into the previous tail"; k_wide_tails<0,1,2> turns these maps into bytes (folded over
-//     groups of 32 blocks, so the serial part is short); pass 3 (k_wide_blocks<3>) repeats the block
-//     with the previous tail known and writes the output, 128 contiguous bytes per warp store.
+//     or to one of those 4095 previous bytes in O(log depth) rounds.  What a block copies from the previous
+//     one is only known once that one is known, and so on down the value: a chain of nblk - 1 gathers of
+//     4095 bytes, k_wide_tails<0,1,2> (folded over groups of 32 blocks, so the serial part is short).
+//     Around it, one of two shapes:
+//       * with a store of resolved blocks (2 bytes per output byte, WideArea::store): k_wide_blocks<2>
+//         parses and resolves every block once and stores each byte as "value" or "index into the previous
+//         tail"; the tail kernels turn the last 4095 entries of every stored block into values, in place;
+//         k_wide_finish streams the store into the output (HBM-bound: 2 bytes read per byte written);
+//       * without it (no room, or more blocks than it holds): k_wide_blocks<1> parses every block with the
+//         previous tail unknown and publishes only its own last 4095 bytes as such a map; after the tail
+//         kernels pass 3 (k_wide_blocks<3>) parses the block again with the previous tail known and writes
+//         the output, 128 contiguous bytes per warp store.
 //
-// Work memory: 4 bytes per 32 bytes of source + 13 bytes per 512-byte segment.  The segment maps, the tail
-// maps and the resolved tails live inside the value's own (not yet written) output region and are
-// overwritten by pass 3, which therefore runs from the last block to the first behind a flag per block.
+// Work memory: 4 bytes per 32 bytes of source + 13 bytes per 512-byte segment (+ the optional store).  The
+// segment maps, and in the two-parse shape the tail maps and the resolved tails, live inside the value's own
+// (not yet written) output region and are overwritten by the last kernel; pass 3 therefore runs from the last
+// block to the first behind a flag per block.
 #pragma once
 #include <cuda_bf16.h>
 
@@ -344,14 +352,33 @@ k_wide_zero(WideArea wa)
 // byte and the "length-extension" bits of the following bytes (bit i of `ext`: byte i after the control byte
 // is 0x?F).  0: a tag runs past the source, or the control byte has no item; both end in "corrupt"
 // (ppr:229-230).  Register-only: where a group ends depends on nothing but these bits.
-__device__ __forceinline__ uint32_t wide_group_len(uint32_t ctrl, uint32_t ext, uint32_t avail)
+// tags[c]: bit i = "byte i after control byte c starts a tag", as long as no earlier tag of the group is extended.
+__device__ __forceinline__ uint32_t wide_tag_starts(uint32_t ctrl)
 {
-    uint32_t q = 1;
-    if (avail >= 26u) {                                                      // the whole group lies inside the stream
+    uint32_t m = 0, q = 0;
 #pragma unroll
-        for (uint32_t k = 0; k < 8; k++) q += ((ctrl >> k) & 1u) ? 2u + ((ext >> (q - 1u)) & 1u) : 1u;
-        return q;
+    for (uint32_t k = 0; k < 8; k++) {
+        if ((ctrl >> k) & 1u) { m |= 1u << q; q += 2u; } else q += 1u;
     }
+    return m;
+}
+
+__device__ __forceinline__ uint32_t wide_group_len(uint32_t ctrl, uint32_t ext, uint32_t avail, const uint32_t *tags)
+{
+    if (avail >= 26u) {                                                      // the whole group lies inside the stream
+        // 1 + 8 items + one more byte per tag + one more per extended tag.  Most groups have none of those: the tags'
+        // first bytes are where the table says, and none of them has the extension bit.  Otherwise the first one that
+        // has it is a real extended tag (nothing before it moved), and every tag after it starts one byte later.
+        uint32_t len = 9u + (uint32_t)__popc(ctrl), tm = tags[ctrl], hit = ext & tm;
+        while (hit) {
+            const uint32_t p = (uint32_t)__ffs((int)hit) - 1u;
+            len += 1u;
+            tm = (tm & ~((2u << p) - 1u)) << 1;
+            hit = ext & tm;
+        }
+        return len;
+    }
+    uint32_t q = 1;
 #pragma unroll
     for (uint32_t k = 0; k < 8; k++) {
         if (q < avail) {                                                     // `sp < srcend` of the inner loop (ppr:203)
@@ -382,9 +409,11 @@ k_wide_maps(WideArea wa)
     __shared__ uint8_t sctrl_extra[64];                                      // source bytes 4096..4159 of the chunk
     __shared__ __align__(16) uint8_t sdelta[kWideChunk + 32];
     __shared__ uint32_t sh_c;
+    __shared__ uint32_t stags[256];
     const uint32_t n_jobs = wa.state->n_jobs, n_chunks = wa.state->n_segs / kWideChunkSegs;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, t = threadIdx.x;
     if (n_jobs == 0) return;
+    stags[t] = wide_tag_starts(t);                                           // (256 threads)
     for (;;) {
         __syncthreads();
         if (t == 0) sh_c = atomicAdd(&wa.state->t_maps, 1u);
@@ -431,7 +460,7 @@ k_wide_maps(WideArea wa)
             for (uint32_t j = 0; j < 16; j++) {
                 const uint32_t a = p0 + j;
                 uint32_t d = 0;
-                if (a < slen) d = wide_group_len((w[j >> 2] >> (8u * (j & 3u))) & 0xFFu, (uint32_t)(e >> (j + 1u)), slen - a);
+                if (a < slen) d = wide_group_len((w[j >> 2] >> (8u * (j & 3u))) & 0xFFu, (uint32_t)(e >> (j + 1u)), slen - a, stags);
                 if ((j & 3u) == 0u) packed[j >> 2] = d; else packed[j >> 2] |= d << (8u * (j & 3u));
             }
             *reinterpret_cast<uint4 *>(sdelta + 16u * t) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
@@ -441,7 +470,7 @@ k_wide_maps(WideArea wa)
             const unsigned long long e = (unsigned long long)sext[256 + (t >> 4)] | ((unsigned long long)sext[257 + (t >> 4)] << 16) |
                                          ((unsigned long long)sext[258 + (t >> 4)] << 32);
             uint32_t d = 0;
-            if (a < slen) d = wide_group_len(sctrl_extra[t], (uint32_t)(e >> ((t & 15u) + 1u)), slen - a);
+            if (a < slen) d = wide_group_len(sctrl_extra[t], (uint32_t)(e >> ((t & 15u) + 1u)), slen - a, stags);
             sdelta[kWideChunk + t] = (uint8_t)d;
         }
         __syncthreads();
@@ -1063,16 +1092,14 @@ k_wide_tails(WideArea wa)
     }
 }
 
-// Stored blocks -> output (the streaming half of the one-parse path): a block's map and the previous block's tail
-// (which k_wide_tails<2> has turned into bytes, in place) are staged in shared memory, then written in the output format.
+// Stored blocks -> output (the streaming half of the one-parse path).  Only the previous block's tail (which
+// k_wide_tails<2> has turned into bytes, in place) goes through shared memory; the block's own entries are read once,
+// 8 per thread and step, and leave in the output format.
 constexpr uint32_t kFinishThreads = 512;
-constexpr size_t kWideFinishSmem = 2 * (size_t)kWideBlock + 4096;
-__global__ void __launch_bounds__(kFinishThreads, 2)
+__global__ void __launch_bounds__(kFinishThreads, 4)
 k_wide_finish(WideArea wa)
 {
-    extern __shared__ __align__(16) uint8_t wide_smem[];
-    uint16_t *map = reinterpret_cast<uint16_t *>(wide_smem);                 // [kWideBlock]
-    uint8_t *tail = wide_smem + 2 * (size_t)kWideBlock;                      // [4096]
+    __shared__ __align__(16) uint8_t tail[4096];
     __shared__ uint32_t sh_j;
     const uint32_t n_jobs = wa.state->n_jobs, n_blks = wa.state->n_blks, tid = threadIdx.x;
     if (n_jobs == 0 || !wide_stored(wa)) return;
@@ -1084,18 +1111,44 @@ k_wide_finish(WideArea wa)
         const uint32_t k = b - wj.blk0;
         if (wj.state != 0u || k >= wj.nblk) continue;
         const uint32_t o0 = k * kWideBlock, n_out = min(kWideBlock, wj.rawsize - o0);
-        const uint4 *g = reinterpret_cast<const uint4 *>(wa.store + (size_t)b * kWideBlock);
-        for (uint32_t i = tid; i < (n_out + 7u) / 8u; i += kFinishThreads) reinterpret_cast<uint4 *>(map)[i] = __ldcs(g + i);
+        const uint16_t *map = wa.store + (size_t)b * kWideBlock;
         if (k > 0u) {
-            const uint16_t *pt = wa.store + (size_t)(b - 1u) * kWideBlock + (kWideBlock - kWideWin);
+            const uint16_t *pt = map - kWideWin;                             // the last 4095 entries of the previous block
             for (uint32_t i = tid; i < kWideWin; i += kFinishThreads) tail[i] = (uint8_t)pt[i];
         }
         __syncthreads();
-        wide_write_block(wj.fmt, reinterpret_cast<uint8_t *>(wj.dst) + wide_scale(wj.fmt, o0), o0, n_out, wa.lut, wa.lut_channels, tid,
-                         kFinishThreads, [&](uint32_t i) {
-                             const uint32_t m = map[i];
-                             return (m & 0x8000u) ? (m & 0xFFu) : (uint32_t)tail[m & 4095u];
-                         });
+        auto byte_of = [&](uint32_t m) { return (m & 0x8000u) ? (m & 0xFFu) : (uint32_t)tail[m & 4095u]; };
+        uint8_t *region = reinterpret_cast<uint8_t *>(wj.dst) + wide_scale(wj.fmt, o0);
+        if (wj.fmt != 2u && (reinterpret_cast<uintptr_t>(region) & 3u) == 0u) {
+            // 8 entries = 8 output bytes, or 2 float32 -> 2 bfloat16
+            const uint4 *g = reinterpret_cast<const uint4 *>(map);
+            const uint32_t n8 = n_out >> 3;
+            for (uint32_t i = tid; i < n8; i += kFinishThreads) {
+                const uint4 v = __ldcs(g + i);
+                const uint32_t lo = byte_of(v.x & 0xFFFFu) | (byte_of(v.x >> 16) << 8) | (byte_of(v.y & 0xFFFFu) << 16) | (byte_of(v.y >> 16) << 24);
+                const uint32_t hi = byte_of(v.z & 0xFFFFu) | (byte_of(v.z >> 16) << 8) | (byte_of(v.w & 0xFFFFu) << 16) | (byte_of(v.w >> 16) << 24);
+                if (wj.fmt == 1u) {
+                    const __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(lo), __uint_as_float(hi));
+                    __stcs(reinterpret_cast<uint32_t *>(region) + i, *reinterpret_cast<const uint32_t *>(&h));
+                } else {
+                    __stcs(reinterpret_cast<uint32_t *>(region) + 2u * i, lo);
+                    __stcs(reinterpret_cast<uint32_t *>(region) + 2u * i + 1u, hi);
+                }
+            }
+            // the last 1..7 bytes of a value
+            const uint32_t t0 = n8 << 3;
+            if (wj.fmt == 1u) {
+                if (tid == 0 && n_out - t0 >= 4u) {
+                    const uint32_t x = byte_of(map[t0]) | (byte_of(map[t0 + 1u]) << 8) | (byte_of(map[t0 + 2u]) << 16) | (byte_of(map[t0 + 3u]) << 24);
+                    reinterpret_cast<__nv_bfloat16 *>(region)[t0 >> 2] = __float2bfloat16_rn(__uint_as_float(x));
+                }
+            } else if (tid < n_out - t0) {
+                region[t0 + tid] = (uint8_t)byte_of(map[t0 + tid]);
+            }
+        } else {
+            wide_write_block(wj.fmt, region, o0, n_out, wa.lut, wa.lut_channels, tid, kFinishThreads,
+                             [&](uint32_t i) { return byte_of(__ldg(map + i)); });
+        }
     }
 }
 
