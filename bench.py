@@ -681,7 +681,7 @@ def gpu_leg(ctx, name, steps, warmup, graph_wanted, with_cpu, sampler=None):
     if meta["pglz_out_bytes"] == 0:
         dom, dom_ms, dom_bytes = "k_toast_gather", gather_ms_max, gather_bytes
     elif went_wide:
-        dom, dom_ms, dom_bytes = ("wide pglz pipeline (k_wide_* : 14 kernels incl. the two k_wide_blocks passes, + k_pglz_decode for the small "
+        dom, dom_ms, dom_bytes = ("wide pglz pipeline (k_wide_* : 16 kernels incl. k_wide_blocks + k_wide_finish, + k_pglz_decode for the small "
                                   "values; one CUDA-event pair around the stage)"), stage_ms_max, stage_bytes
         blocks_ms = float(np.mean(b1_ms) + np.mean(b3_ms)) if len(b1_ms) and len(b3_ms) else None
     else:
@@ -699,7 +699,7 @@ def gpu_leg(ctx, name, steps, warmup, graph_wanted, with_cpu, sampler=None):
                      "algorithmic_bytes_per_launch": dom_bytes, "launch_ms": dom_ms,
                      "share_of_step": dom_ms / dev_ms_max if dev_ms_max else None,
                      "traffic": (load_profile_traffic(name) or {}).get("dram_bytes_per_launch"),
-                     "stages_ms": {"gather": gather_ms_max, "pglz_stage": stage_ms_max, "k_wide_blocks_1_plus_3 (rank 0)": blocks_ms}},
+                     "stages_ms": {"gather": gather_ms_max, "pglz_stage": stage_ms_max, "k_wide_blocks_and_finish (rank 0)": blocks_ms}},
         "e2e": {"value": rows_total / (e2e_ms_max / 1000.0), "unit": "rows/s", "ms_per_step": e2e_ms_max,
                 "h2d_bytes_per_step": int(seg.heap.size + seg.toast.size),
                 "d2h_bytes_per_step": int(meta["samples"] * 8 + 96), "steps": e2e_steps,

@@ -173,7 +173,9 @@ int cds_stream_counts(unsigned long long *streamed, unsigned long long *decoded_
 unsigned long long cds_launch_count(void);
 /* Record CUDA-event pairs on the launching stream inside the next `max_samples` cds_materialize / cds_decode_*
  * calls (0 disables).  Stages: 0 = the gather kernel; 1 = the pglz stage (classification, wide decoder, warp
- * decoder); 2, 3 = the two block passes of the wide decoder (when its kernels are enqueued with the decode).
+ * decoder); 2, 3 = the block kernels of the wide decoder in front of and behind its tail kernels (k_wide_blocks<2> and
+ * k_wide_finish with a store of resolved blocks, the two parses k_wide_blocks<1> and <3> without; when its kernels are
+ * enqueued with the decode).
  * cds_timing_read_stage waits for the samples of one stage and returns their durations in milliseconds;
  * cds_timing_read does the same for stage 0 and then rearms (call it last). */
 int cds_timing_enable(cds_segment *seg, uint32_t max_samples);

@@ -6,7 +6,7 @@ for v in $1; do
 import sys,json
 d=json.loads(sys.stdin.read().strip().splitlines()[-1])
 st=d['roofline'].get('stages_ms',{})
-print('$v $w %.3f stage %.3f blocks %s e2e %.2f'%(d['ms_per_step'],st.get('pglz_stage') or 0,st.get('k_wide_blocks_1_plus_3 (rank 0)'),d['e2e']['ms_per_step']))"
+print('$v $w %.3f stage %.3f blocks %s e2e %.2f'%(d['ms_per_step'],st.get('pglz_stage') or 0,st.get('k_wide_blocks_and_finish (rank 0)'),d['e2e']['ms_per_step']))"
   done
 done
 done

@@ -8,3 +8,4 @@ ncu --set full --import-source on --clock-control none -k regex:k_toast_gather -
 ncu --set full --import-source on --clock-control none -k regex:k_toast_gather -s 4 -c 1 -f -o gpurun_out/r2_gather_pglz python bench.py --only --workload imagenet_pglz --steps 2 --warmup 3 --no-cpu --no-graph > /dev/null 2>&1; echo rc=$?
 ncu --set full --import-source on --clock-control none -k regex:k_pglz_decode -s 4 -c 1 -f -o gpurun_out/r2_pglz_img_final python bench.py --only --workload imagenet_pglz --steps 2 --warmup 3 --no-cpu --no-graph > /dev/null 2>&1; echo rc=$?
 ncu --set full --import-source on --clock-control none -k regex:k_pglz_decode -s 4 -c 1 -f -o gpurun_out/r2_pglz_criteo_final python bench.py --only --workload criteo --steps 2 --warmup 3 --no-cpu --no-graph > /dev/null 2>&1; echo rc=$?
+ncu --set full --import-source on --clock-control none -k regex:"k_wide_maps|k_wide_blocks|k_wide_finish" -s 25 -c 5 -f -o gpurun_out/r2_wide_final python bench.py --only --workload imagenet_packed --toast-mib 256 --images-per-buffer 400 --steps 2 --warmup 3 --no-cpu --no-graph > /dev/null 2>&1; echo rc=$?
