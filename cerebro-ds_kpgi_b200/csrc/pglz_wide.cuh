@@ -1004,16 +1004,39 @@ __global__ void __launch_bounds__(1024)
 k_wide_tails(WideArea wa)
 {
     __shared__ uint16_t tail[2][4096];                                       // 0x8000 | byte, or an index (phase 0 only)
-    __shared__ uint32_t sh_j;
+    __shared__ uint32_t work_u[1024], work_j[1024], n_work;
     const uint32_t n_jobs = wa.state->n_jobs, tid = threadIdx.x;
     if (n_jobs == 0) return;
     const uint32_t n_units = kPhase == 1 ? n_jobs : wa.state->n_blks;        // phase 1: values; phases 0, 2: group leaders
     const bool stored = wide_stored(wa);
-    for (uint32_t u = blockIdx.x; u < n_units; u += gridDim.x) {
-        __syncthreads();
-        if (tid == 0) sh_j = kPhase == 1 ? u : wide_find_blk(wa, n_jobs, u);
-        __syncthreads();
-        const WideJob wj = wa.jobs[sh_j];
+    // This CTA's units are blockIdx.x, + gridDim.x, ...  Only one block in 32 leads a group, and finding a block's value is a
+    // binary search: every thread looks one unit up, the units with work are listed, then the CTA goes through the list.
+    for (uint32_t u0 = blockIdx.x; u0 < n_units; u0 += 1024u * gridDim.x) {
+    __syncthreads();
+    if (tid == 0) n_work = 0;
+    __syncthreads();
+    {
+        const unsigned long long mine = (unsigned long long)u0 + (unsigned long long)tid * gridDim.x;
+        if (mine < n_units) {
+            const uint32_t u = (uint32_t)mine, j = kPhase == 1 ? u : wide_find_blk(wa, n_jobs, u);
+            const WideJob *pj = &wa.jobs[j];
+            bool work = pj->state == 0u && pj->nblk >= 2u;
+            if (work && kPhase != 1) {
+                const uint32_t k = u - pj->blk0;
+                work = k < pj->nblk - 1u && k % kTailGroup == 0u;
+            }
+            if (work) {
+                const uint32_t slot = atomicAdd(&n_work, 1u);
+                work_u[slot] = u;
+                work_j[slot] = j;
+            }
+        }
+    }
+    __syncthreads();
+    for (uint32_t wi = 0; wi < n_work; wi++) {
+        __syncthreads();                                                     // (the previous unit is done with `tail`)
+        const uint32_t u = work_u[wi];
+        const WideJob wj = wa.jobs[work_j[wi]];
         if (wj.state != 0u || wj.nblk < 2u) continue;
         const uint32_t nlinks = wj.nblk - 1u;                                // blocks 0 .. nblk-2 hand a tail on
         uint8_t *dst = reinterpret_cast<uint8_t *>(wj.dst);
@@ -1089,6 +1112,7 @@ k_wide_tails(WideArea wa)
             uint16_t *gm = const_cast<uint16_t *>(wide_u16_at(region(first) + kTailGmapOff));
             for (uint32_t i = tid; i < kWideWin; i += blockDim.x) gm[i] = tail[cur][i];
         }
+    }
     }
 }
 
