@@ -480,14 +480,15 @@ k_wide_maps(WideArea wa)
             if (lane >= 25u) {
                 e = kWideBad;
             } else {
-                for (;;) {
-                    const uint32_t a = coff + p;
-                    if (a >= slen) { e = a == slen ? kWideEnd : kWideBad; break; }
-                    if (p >= end) { e = p - end; break; }
+                // follow the groups while they start inside the segment and inside the stream (a group that cannot be: far away)
+                const uint32_t lim = min(end, slen - coff), kFar = 1u << 20;
+                while (p < lim) {
                     const uint32_t d = sdelta[p];
-                    if (d == 0u) { e = kWideBad; break; }
-                    p += d;
+                    p += d ? d : kFar;
                 }
+                if (p >= kFar) e = kWideBad;
+                else if (coff + p >= slen) e = coff + p == slen ? kWideEnd : kWideBad;
+                else e = p - end;
             }
             reinterpret_cast<uint8_t *>(wj.dst)[(size_t)(lseg + warp) * 32u + lane] = (uint8_t)e;
         }
