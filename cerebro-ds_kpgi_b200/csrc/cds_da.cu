@@ -644,6 +644,7 @@ static int launch_gather_and_pglz(cds_segment *s, cudaStream_t st)
     if (timed) CU(cudaEventRecordWithFlags(ev[2], st, ev_flags));
     if (wide_possible) {
         WideArea wa = s->wide;
+        if (s->wide_store_blks * (uint64_t)kWideBlock * sizeof(uint16_t) > g_wide_store_limit) { wa.store = nullptr; wa.store_blks = 0; }
         wa.threshold = g_wide_threshold;
         wa.force = (s->wide_mode == 1 || g_wide_force) ? 1u : 0u;
         wa.st = s->state;
@@ -843,6 +844,7 @@ static int launch_pglz_batch(cds_segment *s, uint32_t j, bool may_be_wide, cudaS
     const uint32_t *d_first = s->sargs.range_first + j;
     if (may_be_wide && s->wide_mem && g_wide_threshold && s->wide_mode != 0) {
         WideArea wa = s->wide;
+        if (s->wide_store_blks * (uint64_t)kWideBlock * sizeof(uint16_t) > g_wide_store_limit) { wa.store = nullptr; wa.store_blks = 0; }
         wa.threshold = g_wide_threshold;
         wa.force = (s->wide_mode == 1 || g_wide_force) ? 1u : 0u;
         wa.st = s->state;

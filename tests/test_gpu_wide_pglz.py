@@ -24,6 +24,7 @@ def torch_cuda():
 
 
 NO_LIMIT = 2 ** 64 - 1
+CURRENT_SHAPE = ["stored_blocks"]
 
 
 @pytest.fixture(params=["stored_blocks", "two_parses"])
@@ -32,6 +33,7 @@ def wide_threshold(request):
     of resolved blocks (each block parsed once) and without it (cds_set_wide_store_limit(0): each block parsed twice)."""
     from cerebro_ds_kpgi_b200 import _lib
     L = _lib.require_device()
+    CURRENT_SHAPE[0] = request.param
     _lib.check(L.cds_set_wide_store_limit(NO_LIMIT if request.param == "stored_blocks" else 0))
 
     def set_to(n, force=1):
@@ -396,5 +398,13 @@ def test_a_handle_gets_its_store_after_the_first_wide_decode(torch_cuda, coracle
                     assert out_ind[:ind_bytes].cpu().numpy().tobytes() == want["out_ind"].tobytes()
                 assert out_dep[:want["out_dep"].size].cpu().numpy().tobytes() == want["out_dep"].tobytes()
                 assert bool((out_ind[ind_bytes:] == 0xA5).all()) and bool((out_dep[want["out_dep"].size:] == 0xA5).all())
+                if sg is segs[-1][0]:
+                    # a limit lowered afterwards also keeps a handle from using the store it holds: same bytes again
+                    from cerebro_ds_kpgi_b200 import _lib
+                    _lib.check(_lib.load().cds_set_wide_store_limit(0))
+                    again = torch.full_like(out_ind, 0xA5)
+                    s = ds.decode_device(torch.from_numpy(sg.heap).cuda(), torch.from_numpy(sg.toast).cuda(), again, out_dep)
+                    assert s.status == 0 and torch.equal(again, out_ind)
+                    _lib.check(_lib.load().cds_set_wide_store_limit(NO_LIMIT if "stored" in CURRENT_SHAPE[0] else 0))
         finally:
             ds.close()
