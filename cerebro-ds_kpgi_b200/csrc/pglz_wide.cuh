@@ -109,6 +109,7 @@ struct WideArea {
     uint32_t *sub_entry;     // per flat sub-segment: (output position of its first group relative to the segment's) << 5 | its offset
                              // (31: no group starts here)
     uint32_t *blk_sub0;      // per flat block: local sub-segment holding the group that produces its first byte
+    uint32_t *blk_job;       // per flat block: slot of its value in `jobs`
     uint32_t cap_jobs, cap_segs, cap_blks;
     uint32_t zero_bytes;
     uint32_t threshold;      // values with rawsize >= threshold are candidates for this path
@@ -134,7 +135,7 @@ __host__ __device__ inline size_t wide_area_bytes(uint32_t cap_jobs, uint32_t ca
     const size_t tiles = wide_scan_tiles(cap_segs), nss = (size_t)cap_segs / kWideSuper + 1;
     return wide_align(256 + 4 * tiles + 4 * ((size_t)cap_blks + 1)) + wide_align(16 * tiles) + wide_align(sizeof(WideJob) * (size_t)cap_jobs) +
            wide_align((size_t)cap_segs) + wide_align(4 * (size_t)cap_segs) + wide_align(8 * ((size_t)cap_segs + 1)) +
-           wide_align(32 * nss) + wide_align(nss) + wide_align(4 * (size_t)cap_segs * kWideSubs) + wide_align(4 * ((size_t)cap_blks + 1));
+           wide_align(32 * nss) + wide_align(nss) + wide_align(4 * (size_t)cap_segs * kWideSubs) + 2 * wide_align(4 * ((size_t)cap_blks + 1));
 }
 
 // Carve the work area out of one 256-byte aligned allocation (host side).
@@ -158,7 +159,8 @@ inline WideArea wide_area_carve(uint8_t *base, uint32_t cap_jobs, uint32_t cap_s
     wa.supermap = p; p += wide_align(32 * nss);
     wa.sseg_e = p; p += wide_align(nss);
     wa.sub_entry = reinterpret_cast<uint32_t *>(p); p += wide_align(4 * (size_t)cap_segs * kWideSubs);
-    wa.blk_sub0 = reinterpret_cast<uint32_t *>(p);
+    wa.blk_sub0 = reinterpret_cast<uint32_t *>(p); p += wide_align(4 * ((size_t)cap_blks + 1));
+    wa.blk_job = reinterpret_cast<uint32_t *>(p);
     wa.cap_jobs = cap_jobs; wa.cap_segs = cap_segs; wa.cap_blks = cap_blks;
     wa.threshold = 0; wa.force = 0; wa.status = nullptr; wa.st = nullptr; wa.lut = nullptr; wa.lut_channels = 1;
     wa.store = nullptr; wa.store_blks = 0;
@@ -677,6 +679,7 @@ k_wide_blkmap(WideArea wa)
     if (n_jobs == 0) return;
     for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < n_blks; b += gridDim.x * blockDim.x) {
         const uint32_t jn = wide_find_blk(wa, n_jobs, b);
+        wa.blk_job[b] = jn;
         const WideJob *wjp = &wa.jobs[jn];
         const uint32_t k = b - wjp->blk0;
         if (wjp->state != 0u || k >= wjp->nblk) continue;
@@ -748,29 +751,57 @@ k_wide_blocks(WideArea wa)
     uint8_t *val = wide_smem + 2 * (size_t)kWideIdx;                         // [kWideIdx]
     uint32_t *heads = reinterpret_cast<uint32_t *>(wide_smem + 3 * (size_t)kWideIdx);   // [kWideIdx / 32]
     __shared__ uint32_t sh_b, sh_j, sh_bad;
+    __shared__ __align__(16) WideJob sh_wj[2];                               // mode 2: the value of this block and of the CTA's next one
+    __shared__ uint32_t sh_pre[2][4];                                        // ... their slots in `jobs`, blk_sub0[b], blk_sub0[b + 1]
     const uint32_t n_jobs = wa.state->n_jobs, n_blks = wa.state->n_blks, tid = threadIdx.x;
-    uint32_t *ticket = kMode == 1 ? &wa.state->t_l1 : kMode == 2 ? &wa.state->t_l2 : &wa.state->t_l3;
+    uint32_t *ticket = kMode == 1 ? &wa.state->t_l1 : &wa.state->t_l3;
     if (n_jobs == 0) return;
     if ((kMode == 2) != wide_stored(wa)) return;                             // one parse into the store, or two without it
+    // Mode 2 takes the blocks blockIdx.x, + gridDim.x, ... (no block waits for another one there).  What a block needs to
+    // start -- which value it belongs to, that value's record, where its source starts -- is three dependent loads; they are
+    // issued for the CTA's next block while this one is built, one step per phase, so that nobody waits for them.
+    uint32_t b_lin = blockIdx.x, cur = 0;
+    if (kMode == 2 && tid < 16 && b_lin < n_blks) {
+        const uint32_t j = wa.blk_job[b_lin];
+        reinterpret_cast<uint32_t *>(&sh_wj[0])[tid] = reinterpret_cast<const uint32_t *>(&wa.jobs[j])[tid];
+        if (tid == 0) sh_pre[0][0] = j;
+        if (tid < 2) sh_pre[0][1 + tid] = wa.blk_sub0[b_lin + tid];
+    }
     for (;;) {
         __syncthreads();
-        if (tid == 0) {
-            sh_b = atomicAdd(ticket, 1u);
-            sh_bad = 0;
-            if (sh_b < n_blks) sh_j = wide_find_blk(wa, n_jobs, kMode == 3 ? n_blks - 1u - sh_b : sh_b);
+        uint32_t b, jn, pre_j = 0, pre_w = 0, pre_s = 0, pre_stage = 3;
+        const uint32_t nb = b_lin + gridDim.x;
+        if (kMode == 2) {
+            if (b_lin >= n_blks) break;
+            b = b_lin;
+            jn = sh_pre[cur][0];
+            if (tid == 0) sh_bad = 0;
+            if (nb < n_blks) {
+                if (tid < 32) pre_j = wa.blk_job[nb];                        // (every lane of warp 0: the same word)
+                if (tid < 2) pre_s = wa.blk_sub0[nb + tid];
+                pre_stage = 1;
+            }
+            __syncthreads();
+        } else {
+            if (tid == 0) {
+                sh_b = atomicAdd(ticket, 1u);
+                sh_bad = 0;
+                if (sh_b < n_blks) sh_j = wide_find_blk(wa, n_jobs, kMode == 3 ? n_blks - 1u - sh_b : sh_b);
+            }
+            __syncthreads();
+            if (sh_b >= n_blks) break;
+            b = kMode == 3 ? n_blks - 1u - sh_b : sh_b;                      // pass 3 runs down the blocks (see the flags below)
+            jn = sh_j;
         }
-        __syncthreads();
-        if (sh_b >= n_blks) break;
-        const uint32_t b = kMode == 3 ? n_blks - 1u - sh_b : sh_b;           // pass 3 runs down the blocks (see the flags below)
-        const uint32_t jn = sh_j;
-        const WideJob wj = wa.jobs[jn];
+        const WideJob wj = kMode == 2 ? sh_wj[cur] : wa.jobs[jn];
+        do {                                                                 // (`break`: done with this block)
         const uint32_t k = b - wj.blk0;
         if (wj.state != 0u || k >= wj.nblk) {
             // (a block that is skipped still answers its predecessor, which may have started before the value was refused)
             if (kMode == 3 && tid == 0) *reinterpret_cast<volatile uint32_t *>(&wa.blk_flag[b]) = 1u;
-            continue;
+            break;
         }
-        if (kMode == 1 && k + 1u == wj.nblk) continue;                       // nobody needs the last block's tail
+        if (kMode == 1 && k + 1u == wj.nblk) break;                          // nobody needs the last block's tail
         const uint32_t o0 = k * kWideBlock, o1 = min(o0 + kWideBlock, wj.rawsize), n_out = o1 - o0;
         const uint8_t *src = reinterpret_cast<const uint8_t *>(wj.src);
         uint8_t *dst = reinterpret_cast<uint8_t *>(wj.dst);
@@ -799,7 +830,8 @@ k_wide_blocks(WideArea wa)
         //      offset is parked in the two unused value bytes, its entry is marked in the bitmap of long-match heads), the
         //      body keeps the "not written" value and is filled in below.
         const uint32_t floor_idx = k == 0u ? kWideWin : 0u;                  // nothing exists before the output start
-        const uint32_t sub0 = wa.blk_sub0[b], sub1 = k + 1u < wj.nblk ? wa.blk_sub0[b + 1] : (slen ? (slen - 1u) / kWideSub : 0u);
+        const uint32_t sub0 = kMode == 2 ? sh_pre[cur][1] : wa.blk_sub0[b];
+        const uint32_t sub1 = k + 1u < wj.nblk ? (kMode == 2 ? sh_pre[cur][2] : wa.blk_sub0[b + 1]) : (slen ? (slen - 1u) / kWideSub : 0u);
         const uint32_t *fine = wa.sub_entry + (size_t)wj.seg0 * kWideSubs;
         const unsigned long long value_base = wa.seg_base[wj.seg0];
         for (uint32_t sb = sub0 + tid; sb <= sub1; sb += kWideThreads) {
@@ -862,11 +894,15 @@ k_wide_blocks(WideArea wa)
             }
         }
         __syncthreads();
+        if (kMode == 2 && pre_stage == 1) {                                  // the next block's value: its record
+            if (tid < 16) pre_w = reinterpret_cast<const uint32_t *>(&wa.jobs[pre_j])[tid];
+            pre_stage = 2;
+        }
         if (sh_bad) {
             // A match with offset 0, or one that reaches before the start of the output (the group chain of such a stream
             // can still be well-formed).  Its bytes were not entered into the forest, so nothing below may run on it.
             if (tid == 0) wide_fail(wa, jn);
-            continue;
+            break;
         }
 
         // ---- bodies of long matches: point at the byte they copy (always before their own item)
@@ -936,7 +972,7 @@ k_wide_blocks(WideArea wa)
         }
         if (sh_bad) {                                                        // offset 0 or before the output start
             if (tid == 0) wide_fail(wa, jn);
-            continue;
+            break;
         }
 
         if (kMode == 2) {
@@ -951,7 +987,7 @@ k_wide_blocks(WideArea wa)
                 }
                 *reinterpret_cast<uint2 *>(map + 4u * f) = make_uint2(m[0] | (m[1] << 16), m[2] | (m[3] << 16));
             }
-            continue;
+            break;
         }
         if (kMode == 1) {
             // the block's last 4095 bytes, each as "value" or "index into the previous tail"
@@ -964,7 +1000,7 @@ k_wide_blocks(WideArea wa)
                     map[i] = (uint16_t)(r >= kWideWin ? 0x8000u | val[r] : r);
                 }
             }
-            continue;
+            break;
         }
         // Pass 3 overwrites the whole region, including the tail bytes the NEXT block's pass 3 reads: wait until it has
         // read them.  Blocks are handed out from the last to the first, so that block already runs (or is done).
@@ -977,6 +1013,21 @@ k_wide_blocks(WideArea wa)
         }
         wide_write_block(wj.fmt, region, o0, n_out, wa.lut, wa.lut_channels, tid, kWideThreads,
                          [&](uint32_t i) { return (uint32_t)val[ptr[kWideWin + i]]; });
+        } while (0);
+        if (kMode == 2) {
+            // the last steps of the next block's lookup (all of them here when this block ended early)
+            if (pre_stage == 1) {
+                if (tid < 16) pre_w = reinterpret_cast<const uint32_t *>(&wa.jobs[pre_j])[tid];
+                pre_stage = 2;
+            }
+            if (pre_stage == 2) {
+                if (tid < 16) reinterpret_cast<uint32_t *>(&sh_wj[cur ^ 1u])[tid] = pre_w;
+                if (tid == 0) sh_pre[cur ^ 1u][0] = pre_j;
+                if (tid < 2) sh_pre[cur ^ 1u][1 + tid] = pre_s;
+            }
+            b_lin = nb;
+            cur ^= 1u;
+        }
     }
 }
 
@@ -1130,7 +1181,7 @@ k_wide_finish(WideArea wa)
     if (n_jobs == 0 || !wide_stored(wa)) return;
     for (uint32_t b = blockIdx.x; b < n_blks; b += gridDim.x) {
         __syncthreads();
-        if (tid == 0) sh_j = wide_find_blk(wa, n_jobs, b);
+        if (tid == 0) sh_j = wa.blk_job[b];
         __syncthreads();
         const WideJob wj = wa.jobs[sh_j];
         const uint32_t k = b - wj.blk0;
