@@ -426,11 +426,8 @@ def run_reference_arm(args):
 
 
 def extra_workloads(args):
-    """The configurations that ride along with the headline one: configs[2], configs[3], and the packed layout at N = 1."""
-    out = [w for w in ("imagenet_raw", "imagenet_pglz", "criteo") if w != args.workload]
-    if args.gpus <= 1 and args.workload != "imagenet_packed":
-        out.append("imagenet_packed")
-    return out
+    """The configurations that ride along with the headline one: configs[2], configs[3] and the packed layout."""
+    return [w for w in ("imagenet_raw", "imagenet_pglz", "criteo", "imagenet_packed") if w != args.workload]
 
 
 # ------------------------------------------------------------------------------------------------
