@@ -948,24 +948,6 @@ k_wide_blocks(WideArea wa)
         //      previous tail; resolved entries leave the per-thread work mask
         // (pointers only ever point backwards, so the forest has no cycle and log2(kWideIdx) rounds suffice; the bound is a
         // safety net: a kernel must not spin on damaged input)
-        if (resolve_all) {
-            // first sweep, every entry once with its position known at compile time (no work-mask arithmetic): literals and
-            // bytes one or two hops from one -- most of a block -- leave the mask here
-#pragma unroll
-            for (uint32_t i = 0; i < kWidePer; i++) {
-                if (i >= i_lo && i < i_hi) {
-                    const uint32_t e = i * kWideThreads + tid;
-                    const uint32_t p = ptr[e];
-                    bool done = p == e;
-                    if (!done) {
-                        const uint32_t q = ptr[p];
-                        done = q == p;
-                        if (!done) ptr[e] = ptr[q];
-                    }
-                    if (done) act[i >> 5] &= ~(1u << (i & 31u));
-                }
-            }
-        }
         for (uint32_t round = 0; resolve_all; round++) {
             if (round > 24u) { sh_bad = 1u; break; }
             int changed = 0;
