@@ -220,6 +220,8 @@ static cudaError_t wide_prepare()
     cudaError_t e = cudaFuncSetAttribute(k_wide_blocks<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_blocks<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_blocks<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideBlockSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_tails<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideTailsSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wide_tails<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWideTailsSmem);
     return e;
 }
 
@@ -239,9 +241,9 @@ static cudaError_t wide_prepare()
         k_wide_blocks<2><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
         k_wide_blocks<1><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
         AFTER_B1;                                                                           \
-        k_wide_tails<0><<<(sms), 1024, 0, st>>>(wa);                                        \
+        k_wide_tails<0><<<(sms), 1024, kWideTailsSmem, st>>>(wa);                           \
         k_wide_tails<1><<<(sms), 1024, 0, st>>>(wa);                                        \
-        k_wide_tails<2><<<(sms), 1024, 0, st>>>(wa);                                        \
+        k_wide_tails<2><<<(sms), 1024, kWideTailsSmem, st>>>(wa);                           \
         BEFORE_B3;                                                                          \
         k_wide_blocks<3><<<(sms), kWideThreads, kWideBlockSmem, st>>>(wa);                  \
         k_wide_finish<<<(sms) * 4u, kFinishThreads, 0, st>>>(wa);                           \

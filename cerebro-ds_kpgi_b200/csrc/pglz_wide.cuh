@@ -1043,6 +1043,8 @@ k_wide_blocks(WideArea wa)
 // shared-memory gather.  Folded maps and entering tails live in the group's first block's output region (regions
 // are at least kWideBlock / 2 = 24576 bytes: float32 -> bfloat16 output halves them).
 constexpr uint32_t kTailGroup = 32, kTailAhead = 6;
+constexpr uint32_t kTailRing = 12;                                           // stored maps in flight per CTA (cp.async ring, 8 KB each)
+constexpr size_t kWideTailsSmem = (size_t)kTailRing * 8192;
 constexpr uint32_t kTailGmapOff = 8192, kTailGtailOff = 16384;               // inside the first block of a group
 static_assert(kTailGtailOff + 4096u <= kWideBlock / 2u, "the tail scratch must fit the smallest block region");
 
@@ -1051,10 +1053,19 @@ __device__ __forceinline__ const uint16_t *wide_u16_at(const uint8_t *p)
     return reinterpret_cast<const uint16_t *>((reinterpret_cast<uintptr_t>(p) + 1u) & ~(uintptr_t)1u);
 }
 
+__device__ __forceinline__ void cp_async_16(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory"); }
+
 template <int kPhase>
 __global__ void __launch_bounds__(1024)
 k_wide_tails(WideArea wa)
 {
+    extern __shared__ __align__(16) uint8_t tails_ring[];                    // phases 0, 2 with stored maps: kTailRing x 8192 bytes
     __shared__ uint16_t tail[2][4096];                                       // 0x8000 | byte, or an index (phase 0 only)
     __shared__ uint32_t work_u[1024], work_j[1024], n_work;
     const uint32_t n_jobs = wa.state->n_jobs, tid = threadIdx.x;
@@ -1118,6 +1129,43 @@ k_wide_tails(WideArea wa)
             else if (kPhase == 1) v = 0x8000u;
             else v = 0x8000u | region(first)[kTailGtailOff + i];
             tail[0][i] = (uint16_t)v;
+        }
+        if (kPhase != 1 && stored) {
+            // Stored maps: a block's last 4096 entries are 8192 aligned bytes; they arrive through a ring of asynchronous copies
+            // kTailRing - 1 steps ahead (the store is far larger than L2: a step would otherwise wait a DRAM round trip).
+            auto fetch = [&](uint32_t step) {
+                if (step < nsteps && tid < 512u) {
+                    const uint8_t *g = reinterpret_cast<const uint8_t *>(wa.store + (size_t)(wj.blk0 + first + step) * kWideBlock + (kWideBlock - 4096u));
+                    cp_async_16(tails_ring + (size_t)(step % kTailRing) * 8192u + tid * 16u, g + tid * 16u);
+                }
+                cp_async_commit();
+            };
+            for (uint32_t a = 0; a + 1u < kTailRing; a++) fetch(a);
+            uint32_t cur = 0;
+            for (uint32_t k = 0; k < nsteps; k++) {
+                cp_async_wait<(int)kTailRing - 2>();
+                __syncthreads();                                             // step k's map is here; everybody is done with step k - 1
+                fetch(k + kTailRing - 1u);                                   // (into the slot step k - 1 used)
+                const uint16_t *mp = reinterpret_cast<const uint16_t *>(tails_ring + (size_t)(k % kTailRing) * 8192u) + 1;
+#pragma unroll
+                for (uint32_t j = 0; j < 4; j++) {
+                    const uint32_t i = tid + 1024u * j;
+                    if (i < kWideWin) {
+                        const uint32_t mm = mp[i];
+                        const uint32_t v = (mm & 0x8000u) ? mm : tail[cur][mm & 4095u];
+                        tail[cur ^ 1u][i] = (uint16_t)v;
+                        if (kPhase == 2) stored_map(first + k)[i] = (uint16_t)(0x8000u | (v & 0xFFu));
+                    }
+                }
+                cur ^= 1u;
+            }
+            cp_async_wait<0>();
+            __syncthreads();
+            if (kPhase == 0) {                                               // the folded map of this group
+                uint16_t *gm = const_cast<uint16_t *>(wide_u16_at(region(first) + kTailGmapOff));
+                for (uint32_t i = tid; i < kWideWin; i += blockDim.x) gm[i] = tail[cur][i];
+            }
+            continue;
         }
         // thread t owns entries t, t + 1024, t + 2048, t + 3072 (the last one only below 4095)
         uint32_t m[kTailAhead][4];
