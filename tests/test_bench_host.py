@@ -47,6 +47,16 @@ def test_workload_meta_accounts_for_every_byte():
     assert meta["pglz_out_bytes"] == 0 and meta["pglz_in_bytes"] == 0
 
 
+def test_every_configuration_rides_along_at_every_n():
+    """The default run carries configs[2], configs[3] and the packed layout beside the headline workload, at N = 1 and N = 8 alike."""
+    import argparse
+    import bench
+    for gpus in (1, 2, 8):
+        got = bench.extra_workloads(argparse.Namespace(gpus=gpus, workload="imagenet_raw"))
+        assert got == ["imagenet_pglz", "criteo", "imagenet_packed"]
+    assert "criteo" not in bench.extra_workloads(argparse.Namespace(gpus=1, workload="criteo"))
+
+
 @pytest.mark.gpu
 def test_device_checksum_and_peer_copy_match_the_host():
     import ctypes
