@@ -512,6 +512,8 @@ def gpu_leg(ctx, name, steps, warmup, graph_wanted, with_cpu, sampler=None):
     bf16 = args.out_dtype == "bf16"
     ds.set_output_format(bf16)
     _lib.check(L.cds_set_wide_pglz(ds._h, {"off": 0, "force": 1, "auto": 2, "host": 3}[args.wide]))
+    if args.wide_store_limit >= 0:
+        _lib.check(L.cds_set_wide_store_limit(int(args.wide_store_limit)))
     d_heap = torch.from_numpy(seg.heap).cuda()
     d_toast = torch.from_numpy(seg.toast).cuda()
     out_ind = torch.empty(meta["ind_bytes"] // (2 if bf16 else 1), dtype=torch.uint8, device="cuda")
@@ -853,6 +855,8 @@ def main():
     ap.add_argument("--images-per-buffer", type=int, default=3210, help="imagenet_packed: images per packed buffer (the paper's tables: 3210)")
     ap.add_argument("--toast-mib", type=int, default=1024, help="TOAST file size per segment (config: 1 GiB)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
+    ap.add_argument("--wide-store-limit", type=int, default=-1,
+                    help="cds_set_wide_store_limit(bytes) before the run (0: the wide decoder always parses twice); default: the library's")
     ap.add_argument("--out-dtype", default="f32", choices=["f32", "bf16"],
                     help="independent_var output: f32 = the reference's bits (default); bf16 = fused conversion (extra, not the metric)")
     args = ap.parse_args()
