@@ -39,7 +39,8 @@
 //         kernels pass 3 (k_wide_blocks<3>) parses the block again with the previous tail known and writes
 //         the output, 128 contiguous bytes per warp store.
 //
-// Work memory: 4 bytes per 32 bytes of source + 13 bytes per 512-byte segment (+ the optional store).  The
+// Work memory: 4 bytes per 32 bytes of source + 13 bytes per 512-byte segment + 12 bytes per output block (+ the
+// optional store).  The
 // segment maps, and in the two-parse shape the tail maps and the resolved tails, live inside the value's own
 // (not yet written) output region and are overwritten by the last kernel; pass 3 therefore runs from the last
 // block to the first behind a flag per block.
